@@ -1,0 +1,809 @@
+// libcaribou_cuda C ABI (include/caribou_cuda.h): context, submit paths, state, utilities.
+#include <limits.h>
+#include <stdarg.h>
+#include <string.h>
+#include <algorithm>
+#include <new>
+#include "ctx.h"
+
+namespace cbl {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+bool cuda_ok(cudaError_t e, const char* what)
+{
+    if (e == cudaSuccess) return true;
+    set_error("CUDA error %s (%d) in %s", cudaGetErrorString(e), (int)e, what);
+    return false;
+}
+bool DevBuf::reserve(size_t n)
+{
+    if (n <= cap) return true;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    const size_t want = (n + 4095) & ~size_t(4095);
+    if (!cuda_ok(cudaMalloc(&p, want), "cudaMalloc")) return false;
+    cap = want;
+    return true;
+}
+void DevBuf::release()
+{
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda needed)
+typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static encode_tiled_fn get_encode()
+{
+    static encode_tiled_fn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<encode_tiled_fn>(p);
+    }
+    return fn;
+}
+
+// Tensor map over the runs of a batch of streams: [n_streams][n_runs][LT * elem_words] uint32,
+// box = 128 bytes x 32 runs x 1 stream, 128B swizzle (bank-conflict-free row reads).
+static bool make_run_tmap(CUtensorMap* tm, const void* base, int LT, int elem_words, uint64_t n_runs,
+                          uint32_t n_streams, uint64_t stream_stride_bytes)
+{
+    encode_tiled_fn enc = get_encode();
+    if (!enc) { set_error("cuTensorMapEncodeTiled not available"); return false; }
+    const cuuint64_t row_words = (cuuint64_t)LT * elem_words;
+    cuuint64_t dims[3] = {row_words, n_runs, n_streams};
+    cuuint64_t strides[2] = {row_words * 4, n_streams > 1 ? stream_stride_bytes : std::max<cuuint64_t>(row_words * 4 * n_runs, 16)};
+    cuuint32_t box[3] = {32, 32, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    if ((uintptr_t)base % 16 != 0 || strides[1] % 16 != 0) { set_error("input must be 16-byte aligned (base and stream stride)"); return false; }
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return false; }
+    return true;
+}
+
+static size_t in_elem_bytes(int in_kind) { return in_kind == IN_CF32 ? 8 : 4; }
+
+static bool resolve_out_mode(int parity, int fmt, int* mode, size_t* elem)
+{
+    if (parity == CARIBOU_CUDA_PARITY_F32) {
+        if (fmt == CARIBOU_CUDA_FMT_CF32) { *mode = OUT_F32; *elem = 8; return true; }
+        if (fmt == CARIBOU_CUDA_FMT_CF64) { *mode = OUT_F64; *elem = 16; return true; }
+        return false;
+    }
+    switch (fmt) {
+        case CARIBOU_CUDA_FMT_CS16: *mode = OUT_Q16_CS16; *elem = 4; return true;
+        case CARIBOU_CUDA_FMT_CF32: *mode = OUT_Q16_CF32; *elem = 8; return true;
+        case CARIBOU_CUDA_FMT_CF64: *mode = OUT_Q16_CF64; *elem = 16; return true;
+        case CARIBOU_CUDA_FMT_CS8:  *mode = OUT_Q16_CS8;  *elem = 2; return true;
+    }
+    return false;
+}
+
+// kernel-coordinate <-> reference-coordinate state conversion (s_ref = g[stage] * s_kernel)
+static void state_to_kernel(const FilterPlan& P, const double* ref, double* ker)
+{
+    for (int r = 0; r < 2; r++)
+        for (int i = 0; i < P.S; i++) ker[r * P.S + i] = (double)((long double)ref[r * P.S + i] / (long double)P.g[i / 2]);
+}
+static void state_to_ref(const FilterPlan& P, const double* ker, double* ref)
+{
+    for (int r = 0; r < 2; r++)
+        for (int i = 0; i < P.S; i++) ref[r * P.S + i] = (double)((long double)ker[r * P.S + i] * (long double)P.g[i / 2]);
+}
+
+// ------------------------------------------------------------------ the IIR launch sequence
+// Filters n samples per stream that sit in device memory.  `state_in_dev` is the state each stream starts
+// from (kernel coordinates); when commit is set the end state is written back to ctx->d_state.
+// max_tiles > 0 limits the launch to the first max_tiles tiles of every stream (multi-GPU fix-up).
+static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t in_stride,
+                   void* d_out, size_t out_stride, const int32_t* gate, bool commit, uint32_t max_tiles)
+{
+    const FilterPlan& P = c->plan;
+    const uint32_t ns = (uint32_t)c->cfg.n_streams;
+    const int LT = P.LT;
+    const uint64_t n_runs = n / LT;
+    const uint64_t n_main = n_runs * LT;
+    IirTables T = P.tables;
+    double scale = 1.0;
+    if (c->cfg.parity == CARIBOU_CUDA_PARITY_F32 && in_kind != IN_CF32) scale = 1.0 / 4096.0;   // x / 4096 first (exact)
+    T.gain = P.g[P.K] * scale;
+    const int layout = c->cfg.channel == CARIBOU_CUDA_CH_HIF ? 1 : 0;
+    const size_t es = in_elem_bytes(in_kind);
+
+    if (n_runs > 0) {
+        uint64_t tiles_ps = (n_runs + 31) / 32;
+        bool whole = true;
+        if (max_tiles > 0 && tiles_ps > max_tiles) { tiles_ps = max_tiles; whole = false; }
+        const uint64_t total = tiles_ps * ns;
+        if (total > 0xFFFFFFF0ull) { set_error("too many tiles"); return CARIBOU_CUDA_ERR; }
+        if (!c->desc_agg.reserve(total * 2 * P.S * 8) || !c->desc_incl.reserve(total * 2 * P.S * 8) ||
+            !c->desc_flag.reserve(total * 4)) return CARIBOU_CUDA_ERR;
+        CUtensorMap tm;
+        if (!make_run_tmap(&tm, d_in, LT, (int)(es / 4), n_runs, ns, (uint64_t)in_stride * es)) return CARIBOU_CUDA_ERR;
+        CBL_CHECK(cudaMemsetAsync(c->desc_flag.p, 0, total * 4, c->stream));
+        CBL_CHECK(cudaMemsetAsync(c->d_ticket, 0, 4, c->stream));
+        IirParams p;
+        memset(&p, 0, sizeof(p));
+        p.n_streams = ns;
+        p.n_runs = (uint32_t)n_runs;
+        p.tiles_per_stream = (uint32_t)tiles_ps;
+        p.total_tiles = (uint32_t)total;
+        p.last_tile_runs = (uint32_t)(n_runs - (tiles_ps - 1) * 32);
+        if (!whole) p.last_tile_runs = 32;
+        p.window = P.window;
+        p.chained = P.chained ? 1 : 0;
+        p.write_state = (commit && whole) ? 1 : 0;
+        p.layout = layout;
+        p.out_mode = c->out_mode;
+        p.mtile_pow = c->d_mtile_pow;
+        p.plane = c->d_plane;
+        p.desc_agg = c->desc_agg.as<double>();
+        p.desc_incl = c->desc_incl.as<double>();
+        p.desc_flag = c->desc_flag.as<uint32_t>();
+        p.ticket = c->d_ticket;
+        p.state_in = c->d_state;
+        p.state_out = c->d_state_next;
+        p.out = d_out;
+        p.out_stride = out_stride;
+        p.gate = gate;
+        static int occ_cache[kMaxK + 1][33][3];
+        int& occ = occ_cache[P.K][P.D][in_kind];
+        if (occ == 0) occ = std::max(1, iir_max_ctas_per_sm(P.K, P.D, in_kind));
+        const uint64_t want = (total + kIirWarpsPerCta - 1) / kIirWarpsPerCta;
+        const int grid = (int)std::min<uint64_t>(want, (uint64_t)occ * c->num_sms);
+        const int e = launch_iir(P.K, P.D, in_kind, tm, p, T, grid, c->stream);
+        if (e != 0) { cuda_ok((cudaError_t)e, "iir_scan_kernel launch"); return CARIBOU_CUDA_ERR; }
+        c->launches++;
+        if (p.write_state) {
+            launch_commit_state(c->d_state, c->d_state_next, (size_t)ns * 2 * P.S, gate, c->stream);
+            c->launches++;
+        }
+    }
+    if (n_main < n && max_tiles == 0) {
+        IirTailParams t;
+        memset(&t, 0, sizeof(t));
+        t.n_streams = ns;
+        t.in = d_in; t.in_stride = in_stride;
+        t.first = n_main; t.n = n;
+        t.out = d_out; t.out_stride = out_stride;
+        t.in_kind = in_kind; t.layout = layout; t.out_mode = c->out_mode; t.K = P.K; t.D = P.D;
+        for (int k = 0; k < P.K; k++) { t.a1[k] = T.a1[k]; t.a2[k] = T.a2[k]; t.c1[k] = T.c1[k]; t.c2[k] = T.c2[k]; }
+        t.gain = T.gain;
+        t.state = c->d_state;
+        t.gate = gate;
+        launch_iir_tail(t, c->stream);
+        c->launches++;
+    }
+    CBL_CHECK(cudaGetLastError());
+    return CARIBOU_CUDA_OK;
+}
+
+// ------------------------------------------------------------------ alignment search for a batch
+struct SubGeom { SubView sv; uint32_t n_chunks; };
+
+static int n_subs_of(const caribou_cuda_ctx* c) { return c->cfg.interleave_block_words ? 2 : 1; }
+
+static SubGeom sub_geom(const caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, int sub)
+{
+    SubGeom g;
+    const uint32_t B = c->cfg.interleave_block_words;
+    g.sv.words = reinterpret_cast<const uint32_t*>(d_bytes);
+    g.sv.B = B;
+    g.sv.sub = (uint32_t)sub;
+    if (B == 0) {
+        g.sv.nbytes = nbytes;
+    } else {
+        const uint64_t nw = nbytes / 4, per = 2ull * B;
+        const uint64_t full = nw / per, rem = nw % per;
+        uint64_t cnt = full * B;
+        if (sub == 0) cnt += std::min<uint64_t>(rem, B);
+        else cnt += rem > B ? rem - B : 0;
+        g.sv.nbytes = cnt * 4;
+    }
+    g.sv.n_sub_words = (g.sv.nbytes + 3) / 4;
+    g.n_chunks = (uint32_t)((g.sv.nbytes + c->cfg.chunk_bytes - 1) / c->cfg.chunk_bytes);
+    return g;
+}
+
+static int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes)
+{
+    const uint32_t ns = (uint32_t)c->cfg.n_streams;
+    const int nsub = n_subs_of(c);
+    uint32_t max_chunks = 0;
+    for (int s = 0; s < nsub; s++) max_chunks = std::max(max_chunks, sub_geom(c, d_bytes, nbytes, s).n_chunks);
+    if (!c->offs.reserve((size_t)ns * 2 * std::max<uint32_t>(max_chunks, 1) * 4)) return CARIBOU_CUDA_ERR;
+    // first_bad <- INT_MAX (0x7f7f7f7f is large enough), counters <- 0
+    CBL_CHECK(cudaMemsetAsync(c->d_first_bad, 0x7f, (size_t)ns * 2 * 4, c->stream));
+    CBL_CHECK(cudaMemsetAsync(c->d_counters, 0, sizeof(Counters), c->stream));
+    for (int s = 0; s < nsub; s++) {
+        const SubGeom g = sub_geom(c, d_bytes, nbytes, s);
+        OffsetsParams p;
+        p.sv = g.sv;
+        p.stream_stride_bytes = stride_bytes;
+        p.n_streams = ns;
+        p.chunk_bytes = (uint32_t)c->cfg.chunk_bytes;
+        p.n_chunks = g.n_chunks;
+        p.offs = c->offs.as<int32_t>() + (size_t)s * ns * max_chunks;
+        p.offs_stride = max_chunks;
+        p.first_bad = c->d_first_bad + s;
+        p.first_bad_stride = 2;
+        p.n_misaligned = &c->d_counters->n_misaligned;
+        p.any_misaligned = &c->d_counters->any_misaligned;
+        launch_find_offsets(p, c->stream);
+        if (g.n_chunks) c->launches++;
+    }
+    CBL_CHECK(cudaGetLastError());
+    return (int)max_chunks;
+}
+
+// unpack kernel for every stream of the batch; all pointers are device pointers
+static int run_unpack(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes,
+                      const caribou_cuda_unpack_out& o, uint32_t max_chunks, size_t out_stride_samples)
+{
+    const uint32_t ns = (uint32_t)c->cfg.n_streams;
+    const int nsub = n_subs_of(c);
+    const uint64_t n_raw_words = (nbytes + 3) / 4;
+    const uint64_t n_groups = (n_raw_words + 7) / 8;
+    const uint32_t n_tiles = (uint32_t)((n_groups + kUnpackTileGroups - 1) / kUnpackTileGroups);
+    if (n_tiles == 0) return CARIBOU_CUDA_OK;
+    const bool want_flags = o.invalid_idx || o.sync_idx || true;   // counts are always reported
+    if (!c->desc_inv.reserve((size_t)n_tiles * 8) || !c->desc_syn.reserve((size_t)n_tiles * 8)) return CARIBOU_CUDA_ERR;
+    for (uint32_t st = 0; st < ns; st++) {
+        UnpackParams p;
+        memset(&p, 0, sizeof(p));
+        const uint8_t* sb = reinterpret_cast<const uint8_t*>(d_bytes) + (size_t)st * stride_bytes;
+        p.words = reinterpret_cast<const uint32_t*>(sb);
+        p.nbytes = nbytes;
+        p.n_groups = n_groups;
+        p.B = c->cfg.interleave_block_words;
+        p.chunk_bytes = (uint32_t)c->cfg.chunk_bytes;
+        p.spc = p.chunk_bytes / 4;
+        p.n_subs = nsub;
+        void* cs16[2] = {o.cs16, o.cs16_b};
+        void* meta[2] = {o.meta, o.meta_b};
+        void* cf32[2] = {o.cf32, o.cf32_b};
+        int vec_ok = 1;
+        for (int s = 0; s < nsub; s++) {
+            const SubGeom g = sub_geom(c, sb, nbytes, s);
+            p.sv[s] = g.sv;
+            p.layout[s] = nsub == 2 ? s : (c->cfg.channel == CARIBOU_CUDA_CH_HIF ? 1 : 0);
+            p.offs[s] = c->offs.as<int32_t>() + ((size_t)s * ns + st) * max_chunks;
+            p.first_bad[s] = c->d_first_bad + (size_t)st * 2 + s;
+            p.cs16[s] = cs16[s] ? reinterpret_cast<uint32_t*>(cs16[s]) + (size_t)st * out_stride_samples : nullptr;
+            p.meta[s] = meta[s] ? reinterpret_cast<uint8_t*>(meta[s]) + (size_t)st * out_stride_samples : nullptr;
+            p.cf32[s] = cf32[s] ? reinterpret_cast<float2*>(cf32[s]) + (size_t)st * out_stride_samples : nullptr;
+            if ((uintptr_t)p.cs16[s] % 16 || (uintptr_t)p.meta[s] % 4 || (uintptr_t)p.cf32[s] % 16) vec_ok = 0;
+        }
+        if ((uintptr_t)p.words % 16) { set_error("SMI byte stream must be 16-byte aligned in device memory"); return CARIBOU_CUDA_ERR; }
+        p.vec_ok = vec_ok;
+        p.want_flags = want_flags ? 1 : 0;
+        p.inv_idx = o.invalid_idx; p.inv_cap = o.invalid_cap;
+        p.syn_idx = o.sync_idx; p.syn_cap = o.sync_cap;
+        p.index_base = (uint64_t)st * (nbytes / 4);
+        p.desc_inv = c->desc_inv.as<uint64_t>();
+        p.desc_syn = c->desc_syn.as<uint64_t>();
+        p.ticket = c->d_ticket + 1;
+        p.totals = c->d_counters->totals;
+        p.n_tiles = n_tiles;
+        CBL_CHECK(cudaMemsetAsync(c->desc_inv.p, 0, (size_t)n_tiles * 8, c->stream));
+        CBL_CHECK(cudaMemsetAsync(c->desc_syn.p, 0, (size_t)n_tiles * 8, c->stream));
+        CBL_CHECK(cudaMemsetAsync(c->d_ticket + 1, 0, 4, c->stream));
+        launch_unpack(p, c->stream);
+        c->launches++;
+    }
+    CBL_CHECK(cudaGetLastError());
+    return CARIBOU_CUDA_OK;
+}
+
+static int mirror_counters(caribou_cuda_ctx* c)
+{
+    CBL_CHECK(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+    CBL_CHECK(cudaMemcpyAsync(c->h_first_bad, c->d_first_bad, (size_t)c->cfg.n_streams * 2 * 4, cudaMemcpyDeviceToHost, c->stream));
+    return CARIBOU_CUDA_OK;
+}
+
+// samples the reference's read loop delivers for one sub-stream of `nbytes` given the first bad chunk
+static int64_t delivered_samples(const caribou_cuda_ctx* c, uint64_t sub_nbytes, int32_t first_bad)
+{
+    const uint64_t cb = c->cfg.chunk_bytes;
+    const uint64_t n_chunks = (sub_nbytes + cb - 1) / cb;
+    if (first_bad >= 0 && (uint64_t)first_bad < n_chunks) return CARIBOU_CUDA_ERR_SYNC;
+    // every full chunk gives cb/4 samples, the last partial one floor(len/4) (caribou_smi.c:677)
+    return (int64_t)((sub_nbytes / cb) * (cb / 4) + (sub_nbytes % cb) / 4);
+}
+
+}  // namespace cbl
+
+using namespace cbl;
+
+// ==================================================================== C ABI
+extern "C" {
+
+const char* caribou_cuda_last_error(void) { return g_err; }
+
+caribou_cuda_ctx* caribou_cuda_create(const caribou_cuda_config* cfg_in)
+{
+    if (!cfg_in) { set_error("null config"); return nullptr; }
+    caribou_cuda_ctx* c = new (std::nothrow) caribou_cuda_ctx();
+    if (!c) { set_error("out of memory"); return nullptr; }
+    c->cfg = *cfg_in;
+    caribou_cuda_config& cfg = c->cfg;
+    if (cfg.chunk_bytes == 0) cfg.chunk_bytes = CARIBOU_CUDA_NATIVE_BATCH_LEN;
+    if (cfg.n_streams <= 0) cfg.n_streams = 1;
+    if (cfg.decimation <= 0) cfg.decimation = 1;
+    auto fail = [&](void) -> caribou_cuda_ctx* { caribou_cuda_destroy(c); return nullptr; };
+    if (cfg.chunk_bytes % 16 != 0 || cfg.chunk_bytes < 32 || cfg.chunk_bytes > (1u << 30)) { set_error("chunk_bytes must be a multiple of 16 in [32, 2^30]"); return fail(); }
+    const uint32_t B = cfg.interleave_block_words;
+    if (!(B == 0 || B == 1 || B % 8 == 0)) { set_error("interleave_block_words must be 0, 1 or a multiple of 8"); return fail(); }
+    if (B && cfg.n_sos) { set_error("filtering a dual-channel capture is done per channel: demux first"); return fail(); }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { set_error("no CUDA device: libcaribou_cuda has no CPU fallback"); return fail(); }
+    if (cfg.device < 0 || cfg.device >= ndev) { set_error("bad device ordinal %d", cfg.device); return fail(); }
+    c->device = cfg.device;
+    if (!cuda_ok(cudaSetDevice(c->device), "cudaSetDevice")) return fail();
+    cudaDeviceProp prop;
+    if (!cuda_ok(cudaGetDeviceProperties(&prop, c->device), "cudaGetDeviceProperties")) return fail();
+    if (prop.major != 10) { set_error("libcaribou_cuda is built for sm_100a only (device is sm_%d%d)", prop.major, prop.minor); return fail(); }
+    c->num_sms = prop.multiProcessorCount;
+    if (cfg.cuda_stream) { c->stream = (cudaStream_t)cfg.cuda_stream; c->own_stream = false; }
+    else {
+        if (!cuda_ok(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "cudaStreamCreate")) return fail();
+        c->own_stream = true;
+    }
+    const size_t ns = (size_t)cfg.n_streams;
+    if (!cuda_ok(cudaMalloc(&c->d_ticket, 16), "cudaMalloc") ||
+        !cuda_ok(cudaMalloc(&c->d_counters, sizeof(Counters)), "cudaMalloc") ||
+        !cuda_ok(cudaMalloc(&c->d_first_bad, ns * 2 * 4), "cudaMalloc") ||
+        !cuda_ok(cudaMallocHost(&c->h_counters, sizeof(Counters)), "cudaMallocHost") ||
+        !cuda_ok(cudaMallocHost(&c->h_first_bad, ns * 2 * 4), "cudaMallocHost")) return fail();
+    cudaMemset(c->d_ticket, 0, 16);
+    cudaMemset(c->d_counters, 0, sizeof(Counters));
+    cudaMemset(c->d_first_bad, 0x7f, ns * 2 * 4);
+    memset(c->h_counters, 0, sizeof(Counters));
+    for (size_t i = 0; i < ns * 2; i++) c->h_first_bad[i] = INT_MAX;
+
+    if (cfg.n_sos > 0) {
+        const char* msg = "";
+        if (!make_filter_plan(cfg.n_sos, cfg.sos, cfg.decimation, &c->plan, &msg)) { set_error("%s", msg); return fail(); }
+        if (!resolve_out_mode(cfg.parity, cfg.out_format, &c->out_mode, &c->out_elem)) { set_error("unsupported parity/out_format combination"); return fail(); }
+        const FilterPlan& P = c->plan;
+        if (!cuda_ok(cudaMalloc(&c->d_plane, P.plane.size() * 8), "cudaMalloc") ||
+            !cuda_ok(cudaMalloc(&c->d_mtile_pow, P.mtile_pow.size() * 8), "cudaMalloc") ||
+            !cuda_ok(cudaMalloc(&c->d_state, ns * 2 * P.S * 8), "cudaMalloc") ||
+            !cuda_ok(cudaMalloc(&c->d_state_next, ns * 2 * P.S * 8), "cudaMalloc")) return fail();
+        cudaMemcpy(c->d_plane, P.plane.data(), P.plane.size() * 8, cudaMemcpyHostToDevice);
+        cudaMemcpy(c->d_mtile_pow, P.mtile_pow.data(), P.mtile_pow.size() * 8, cudaMemcpyHostToDevice);
+        cudaMemset(c->d_state, 0, ns * 2 * P.S * 8);
+        cudaMemset(c->d_state_next, 0, ns * 2 * P.S * 8);
+        c->has_filter = true;
+    }
+    if (!cuda_ok(cudaDeviceSynchronize(), "context set-up")) return fail();
+    return c;
+}
+
+void caribou_cuda_destroy(caribou_cuda_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    DevBuf* bufs[] = {&c->desc_agg, &c->desc_incl, &c->desc_flag, &c->offs, &c->desc_inv, &c->desc_syn, &c->stage_in,
+                      &c->stage_cs16[0], &c->stage_cs16[1], &c->stage_meta[0], &c->stage_meta[1], &c->stage_cf32[0],
+                      &c->stage_cf32[1], &c->stage_filt, &c->stage_inv, &c->stage_syn, &c->scratch_cs16};
+    for (DevBuf* b : bufs) b->release();
+    if (c->d_plane) cudaFree(c->d_plane);
+    if (c->d_mtile_pow) cudaFree(c->d_mtile_pow);
+    if (c->d_state) cudaFree(c->d_state);
+    if (c->d_state_next) cudaFree(c->d_state_next);
+    if (c->d_ticket) cudaFree(c->d_ticket);
+    if (c->d_counters) cudaFree(c->d_counters);
+    if (c->d_first_bad) cudaFree(c->d_first_bad);
+    if (c->d_tone) cudaFree(c->d_tone);
+    if (c->h_counters) cudaFreeHost(c->h_counters);
+    if (c->h_first_bad) cudaFreeHost(c->h_first_bad);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+void* caribou_cuda_get_stream(caribou_cuda_ctx* c) { return c ? (void*)c->stream : nullptr; }
+uint64_t caribou_cuda_launch_count(const caribou_cuda_ctx* c) { return c ? c->launches : 0; }
+
+void* caribou_cuda_host_alloc(size_t nbytes)
+{
+    void* p = nullptr;
+    if (!cuda_ok(cudaMallocHost(&p, nbytes), "cudaMallocHost")) return nullptr;
+    return p;
+}
+void caribou_cuda_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int caribou_cuda_butter_lowpass(int order, double fs, double fc, double* sos)
+{
+    return butter_lowpass_sos(order, fs, fc, sos);
+}
+
+// ------------------------------------------------------------------ unpack
+static int unpack_device(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes,
+                         const caribou_cuda_unpack_out& o, size_t out_stride_samples)
+{
+    const int mc = run_find_offsets(c, d_bytes, nbytes, stride_bytes);
+    if (mc < 0) return mc;
+    return run_unpack(c, d_bytes, nbytes, stride_bytes, o, (uint32_t)mc, out_stride_samples);
+}
+
+int caribou_cuda_unpack_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes, size_t stream_stride_bytes,
+                               int mem, const caribou_cuda_unpack_out* out)
+{
+    if (!c || !out || (!bytes && nbytes)) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    CBL_CHECK(cudaSetDevice(c->device));
+    const size_t ns = (size_t)c->cfg.n_streams;
+    if (ns > 1 && stream_stride_bytes < nbytes) { set_error("stream stride smaller than the stream"); return CARIBOU_CUDA_ERR; }
+    if (ns == 1) stream_stride_bytes = (nbytes + 15) & ~size_t(15);
+    c->pending.active = false;
+    c->last_is_unpack = true;
+    c->last_nbytes = nbytes;
+    c->last_n_filtered = 0;
+    const int nsub = n_subs_of(c);
+    // per-sub-stream output capacity in samples
+    size_t sub_samples[2];
+    for (int s = 0; s < nsub; s++) sub_samples[s] = (size_t)(sub_geom(c, bytes, nbytes, s).sv.nbytes / 4);
+    if (mem == CARIBOU_CUDA_MEM_DEVICE) {
+        if (ns > 1 && (stream_stride_bytes % 16)) { set_error("stream stride must be a multiple of 16 bytes"); return CARIBOU_CUDA_ERR; }
+        const size_t ostride = (sub_samples[0] + 3) & ~size_t(3);
+        if (unpack_device(c, bytes, nbytes, stream_stride_bytes, *out, ns > 1 ? ostride : 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        return mirror_counters(c);
+    }
+    // host memory: stage through device buffers (single stream only)
+    if (ns != 1) { set_error("host-memory unpack supports n_streams == 1"); return CARIBOU_CUDA_ERR; }
+    if (!c->stage_in.reserve(nbytes + 64)) return CARIBOU_CUDA_ERR;
+    CBL_CHECK(cudaMemcpyAsync(c->stage_in.p, bytes, nbytes, cudaMemcpyHostToDevice, c->stream));
+    const int mc = run_find_offsets(c, c->stage_in.p, nbytes, stream_stride_bytes);
+    if (mc < 0) return mc;
+    if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    CBL_CHECK(cudaStreamSynchronize(c->stream));   // need the alignment verdict to know which slots get written
+    const bool clean = c->h_counters->any_misaligned == 0;
+    caribou_cuda_unpack_out d = *out;
+    void* hcs16[2] = {out->cs16, out->cs16_b};
+    void* hmeta[2] = {out->meta, out->meta_b};
+    void* hcf32[2] = {out->cf32, out->cf32_b};
+    void** dcs16[2] = {&d.cs16, &d.cs16_b};
+    void** dmeta[2] = {&d.meta, &d.meta_b};
+    void** dcf32[2] = {&d.cf32, &d.cf32_b};
+    for (int s = 0; s < 2; s++) {
+        *dcs16[s] = *dmeta[s] = *dcf32[s] = nullptr;
+        if (s >= nsub) continue;
+        const size_t n = sub_samples[s];
+        if (hcs16[s]) { if (!c->stage_cs16[s].reserve(n * 4 + 64)) return CARIBOU_CUDA_ERR; *dcs16[s] = c->stage_cs16[s].p; }
+        if (hmeta[s]) { if (!c->stage_meta[s].reserve(n + 64)) return CARIBOU_CUDA_ERR; *dmeta[s] = c->stage_meta[s].p; }
+        if (hcf32[s]) { if (!c->stage_cf32[s].reserve(n * 8 + 64)) return CARIBOU_CUDA_ERR; *dcf32[s] = c->stage_cf32[s].p; }
+        if (!clean) {   // some slots stay untouched: start from the caller's buffer contents
+            if (hcs16[s]) CBL_CHECK(cudaMemcpyAsync(*dcs16[s], hcs16[s], n * 4, cudaMemcpyHostToDevice, c->stream));
+            if (hmeta[s]) CBL_CHECK(cudaMemcpyAsync(*dmeta[s], hmeta[s], n, cudaMemcpyHostToDevice, c->stream));
+            if (hcf32[s]) CBL_CHECK(cudaMemcpyAsync(*dcf32[s], hcf32[s], n * 8, cudaMemcpyHostToDevice, c->stream));
+        }
+    }
+    if (out->invalid_idx && out->invalid_cap) { if (!c->stage_inv.reserve(out->invalid_cap * 4)) return CARIBOU_CUDA_ERR; d.invalid_idx = c->stage_inv.as<uint32_t>(); }
+    if (out->sync_idx && out->sync_cap) { if (!c->stage_syn.reserve(out->sync_cap * 4)) return CARIBOU_CUDA_ERR; d.sync_idx = c->stage_syn.as<uint32_t>(); }
+    if (run_unpack(c, c->stage_in.p, nbytes, stream_stride_bytes, d, (uint32_t)mc, 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    for (int s = 0; s < nsub; s++) {
+        const size_t n = sub_samples[s];
+        if (hcs16[s]) CBL_CHECK(cudaMemcpyAsync(hcs16[s], *dcs16[s], n * 4, cudaMemcpyDeviceToHost, c->stream));
+        if (hmeta[s]) CBL_CHECK(cudaMemcpyAsync(hmeta[s], *dmeta[s], n, cudaMemcpyDeviceToHost, c->stream));
+        if (hcf32[s]) CBL_CHECK(cudaMemcpyAsync(hcf32[s], *dcf32[s], n * 8, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (mem == CARIBOU_CUDA_MEM_HOST || out->invalid_idx || out->sync_idx) {
+        CBL_CHECK(cudaStreamSynchronize(c->stream));
+        const size_t ni = (size_t)std::min<uint64_t>(c->h_counters->totals[0], out->invalid_cap);
+        const size_t nsy = (size_t)std::min<uint64_t>(c->h_counters->totals[1], out->sync_cap);
+        if (out->invalid_idx && ni) CBL_CHECK(cudaMemcpy(out->invalid_idx, d.invalid_idx, ni * 4, cudaMemcpyDeviceToHost));
+        if (out->sync_idx && nsy) CBL_CHECK(cudaMemcpy(out->sync_idx, d.sync_idx, nsy * 4, cudaMemcpyDeviceToHost));
+    }
+    return CARIBOU_CUDA_OK;
+}
+
+// ------------------------------------------------------------------ filter
+static int check_filter_args(caribou_cuda_ctx* c, size_t n)
+{
+    if (!c->has_filter) { set_error("context has no filter (n_sos == 0)"); return CARIBOU_CUDA_ERR; }
+    if (n % (size_t)c->plan.D != 0) { set_error("n_samples must be a multiple of the decimation factor"); return CARIBOU_CUDA_ERR; }
+    return CARIBOU_CUDA_OK;
+}
+
+int caribou_cuda_filter_submit(caribou_cuda_ctx* c, int in_kind, const void* in, size_t n, size_t in_stride,
+                               int mem, void* out, size_t out_stride)
+{
+    if (!c || (!in && n) || (!out && n) || in_kind < 0 || in_kind > 2) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    CBL_CHECK(cudaSetDevice(c->device));
+    if (check_filter_args(c, n) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    const size_t ns = (size_t)c->cfg.n_streams;
+    const size_t es = in_elem_bytes(in_kind);
+    const size_t nout = n / c->plan.D;
+    c->pending.active = false;
+    c->last_is_unpack = false;
+    c->last_ret = (int64_t)n;
+    c->last_n_filtered = (int64_t)nout;
+    if (n == 0) return CARIBOU_CUDA_OK;
+    if (ns == 1) { in_stride = (n + 3) & ~size_t(3); out_stride = nout; }
+    if (mem == CARIBOU_CUDA_MEM_DEVICE) {
+        if (run_iir(c, in_kind, in, n, in_stride, out, out_stride, nullptr, true, 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        c->pos += n;
+        return CARIBOU_CUDA_OK;
+    }
+    if (ns != 1) { set_error("host-memory filter supports n_streams == 1"); return CARIBOU_CUDA_ERR; }
+    if (!c->stage_in.reserve(n * es + 64) || !c->stage_filt.reserve(nout * c->out_elem + 64)) return CARIBOU_CUDA_ERR;
+    CBL_CHECK(cudaMemcpyAsync(c->stage_in.p, in, n * es, cudaMemcpyHostToDevice, c->stream));
+    if (run_iir(c, in_kind, c->stage_in.p, n, in_stride, c->stage_filt.p, out_stride, nullptr, true, 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    CBL_CHECK(cudaMemcpyAsync(out, c->stage_filt.p, nout * c->out_elem, cudaMemcpyDeviceToHost, c->stream));
+    c->pos += n;
+    if (mem == CARIBOU_CUDA_MEM_HOST) CBL_CHECK(cudaStreamSynchronize(c->stream));
+    return CARIBOU_CUDA_OK;
+}
+
+int caribou_cuda_filter_fixup(caribou_cuda_ctx* c, int in_kind, const void* in, size_t n, size_t in_stride, int mem,
+                              void* out, size_t out_stride, const double* state_in)
+{
+    if (!c || !in || !out || !state_in || in_kind < 0 || in_kind > 2) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    if (mem != CARIBOU_CUDA_MEM_DEVICE) { set_error("fix-up works on device memory"); return CARIBOU_CUDA_ERR; }
+    CBL_CHECK(cudaSetDevice(c->device));
+    if (check_filter_args(c, n) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    const FilterPlan& P = c->plan;
+    const size_t ns = (size_t)c->cfg.n_streams;
+    if (ns == 1) { in_stride = (n + 3) & ~size_t(3); out_stride = n / P.D; }
+    // the shard was filtered from zero state and left f in d_state; its true end state is M_shard s_in + f
+    std::vector<double> f(ns * 2 * P.S), ker(ns * 2 * P.S), m((size_t)P.S * P.S);
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
+    CBL_CHECK(cudaMemcpy(f.data(), c->d_state, f.size() * 8, cudaMemcpyDeviceToHost));
+    for (size_t s = 0; s < ns; s++) state_to_kernel(P, state_in + s * 2 * P.S, ker.data() + s * 2 * P.S);
+    // A^n in kernel coordinates
+    {
+        std::vector<double> mref((size_t)P.S * P.S);
+        plan_shard_matrix(P, n, mref.data());
+        for (int i = 0; i < P.S; i++)
+            for (int j = 0; j < P.S; j++)
+                m[(size_t)i * P.S + j] = (double)((long double)mref[(size_t)i * P.S + j] * (long double)P.g[j / 2] / (long double)P.g[i / 2]);
+    }
+    std::vector<double> end(f);
+    for (size_t s = 0; s < ns; s++)
+        for (int r = 0; r < 2; r++)
+            for (int i = 0; i < P.S; i++) {
+                long double acc = f[s * 2 * P.S + r * P.S + i];
+                for (int j = 0; j < P.S; j++) acc += (long double)m[(size_t)i * P.S + j] * ker[s * 2 * P.S + r * P.S + j];
+                end[s * 2 * P.S + r * P.S + i] = (double)acc;
+            }
+    // re-run the leading tiles from the true incoming state
+    CBL_CHECK(cudaMemcpy(c->d_state, ker.data(), ker.size() * 8, cudaMemcpyHostToDevice));
+    const size_t fix = caribou_cuda_fixup_samples(c, n);
+    const uint32_t tile_samples = 32u * (uint32_t)P.LT;
+    uint32_t max_tiles = (uint32_t)((fix + tile_samples - 1) / tile_samples);
+    const uint64_t tiles_ps = (n / P.LT + 31) / 32;
+    if (max_tiles == 0 || max_tiles >= tiles_ps) {
+        // no useful contraction (or a short shard): filter the whole shard again from the true state;
+        // the kernels then leave the true end state in d_state themselves
+        if (run_iir(c, in_kind, in, n, in_stride, out, out_stride, nullptr, true, 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        CBL_CHECK(cudaStreamSynchronize(c->stream));
+        return CARIBOU_CUDA_OK;
+    }
+    if (run_iir(c, in_kind, in, n, in_stride, out, out_stride, nullptr, false, max_tiles) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    CBL_CHECK(cudaMemcpyAsync(c->d_state, end.data(), end.size() * 8, cudaMemcpyHostToDevice, c->stream));
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
+    return CARIBOU_CUDA_OK;
+}
+
+size_t caribou_cuda_fixup_samples(caribou_cuda_ctx* c, size_t n_samples)
+{
+    if (!c || !c->has_filter) return 0;
+    if (c->plan.chained || c->plan.decay_samples == 0) return n_samples;
+    return (size_t)std::min<uint64_t>(c->plan.decay_samples, n_samples);
+}
+
+int caribou_cuda_shard_matrix(caribou_cuda_ctx* c, uint64_t n_samples, double* m)
+{
+    if (!c || !c->has_filter || !m) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    plan_shard_matrix(c->plan, n_samples, m);
+    return CARIBOU_CUDA_OK;
+}
+
+// ------------------------------------------------------------------ fused rx path
+static int rx_fallback(caribou_cuda_ctx* c);
+
+int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes, size_t stride_bytes, int mem,
+                           const caribou_cuda_unpack_out* uo, void* filt_out, size_t filt_stride)
+{
+    if (!c || (!bytes && nbytes)) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    CBL_CHECK(cudaSetDevice(c->device));
+    if (!c->has_filter || !filt_out) { set_error("rx_submit needs a filter and an output buffer; use unpack_submit otherwise"); return CARIBOU_CUDA_ERR; }
+    const size_t n = nbytes / 4;
+    if (check_filter_args(c, n) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    const FilterPlan& P = c->plan;
+    const size_t ns = (size_t)c->cfg.n_streams;
+    const size_t nout = n / P.D;
+    if (ns == 1) { stride_bytes = (nbytes + 15) & ~size_t(15); filt_stride = nout; }
+    if (stride_bytes % 16) { set_error("stream stride must be a multiple of 16 bytes"); return CARIBOU_CUDA_ERR; }
+    c->last_is_unpack = false;
+    c->last_nbytes = nbytes;
+    c->last_ret = (int64_t)n;
+    c->last_n_filtered = (int64_t)nout;
+    c->pending.active = false;
+    if (n == 0) return CARIBOU_CUDA_OK;
+
+    const void* d_bytes = bytes;
+    void* d_out = filt_out;
+    if (mem != CARIBOU_CUDA_MEM_DEVICE) {
+        if (ns != 1) { set_error("host-memory rx supports n_streams == 1 (shard captures across contexts)"); return CARIBOU_CUDA_ERR; }
+        if (!c->stage_in.reserve(nbytes + 64) || !c->stage_filt.reserve(nout * c->out_elem + 64)) return CARIBOU_CUDA_ERR;
+        CBL_CHECK(cudaMemcpyAsync(c->stage_in.p, bytes, nbytes, cudaMemcpyHostToDevice, c->stream));
+        d_bytes = c->stage_in.p;
+        d_out = c->stage_filt.p;
+    }
+    const int mc = run_find_offsets(c, d_bytes, nbytes, stride_bytes);
+    if (mc < 0) return mc;
+    // optimistic fused launch, a no-op on the device if any chunk turned out misaligned
+    if (run_iir(c, IN_WORDS, d_bytes, n, stride_bytes / 4, d_out, filt_stride, &c->d_counters->any_misaligned, true, 0) != CARIBOU_CUDA_OK)
+        return CARIBOU_CUDA_ERR;
+    if (uo) {
+        if (mem != CARIBOU_CUDA_MEM_DEVICE) { set_error("rx_submit with unpack outputs needs device memory"); return CARIBOU_CUDA_ERR; }
+        const size_t ostride = ns > 1 ? ((n + 3) & ~size_t(3)) : 0;
+        if (run_unpack(c, d_bytes, nbytes, stride_bytes, *uo, (uint32_t)mc, ostride) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    }
+    if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (mem != CARIBOU_CUDA_MEM_DEVICE)
+        CBL_CHECK(cudaMemcpyAsync(filt_out, d_out, nout * c->out_elem, cudaMemcpyDeviceToHost, c->stream));
+    c->pending.active = true;
+    c->pending.bytes = bytes; c->pending.nbytes = nbytes; c->pending.stride = stride_bytes; c->pending.mem = mem;
+    c->pending.filt_out = filt_out; c->pending.filt_stride = filt_stride;
+    c->pending.d_bytes = d_bytes; c->pending.d_out = d_out;
+    c->pos += n;
+    if (mem == CARIBOU_CUDA_MEM_HOST) return caribou_cuda_wait(c, nullptr) < 0 ? CARIBOU_CUDA_ERR : CARIBOU_CUDA_OK;
+    return CARIBOU_CUDA_OK;
+}
+
+// Misaligned capture: the fused launch did nothing.  Decode into a zero-filled CS16 scratch with the
+// reference's chunk semantics, then filter the delivered samples.
+static int rx_fallback(caribou_cuda_ctx* c)
+{
+    PendingRx& q = c->pending;
+    const FilterPlan& P = c->plan;
+    const size_t ns = (size_t)c->cfg.n_streams;
+    const size_t n = q.nbytes / 4;
+    const size_t sstride = (n + 3) & ~size_t(3);
+    if (!c->scratch_cs16.reserve(ns * sstride * 4 + 64)) return CARIBOU_CUDA_ERR;
+    CBL_CHECK(cudaMemsetAsync(c->scratch_cs16.p, 0, ns * sstride * 4, c->stream));
+    caribou_cuda_unpack_out o;
+    memset(&o, 0, sizeof(o));
+    o.cs16 = c->scratch_cs16.p;
+    const int mc = run_find_offsets(c, q.d_bytes, q.nbytes, q.stride);
+    if (mc < 0) return mc;
+    if (run_unpack(c, q.d_bytes, q.nbytes, q.stride, o, (uint32_t)mc, ns > 1 ? sstride : 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
+    // samples delivered before a lost sync (all streams must agree for a batched filter launch)
+    int64_t deliver = (int64_t)n;
+    bool lost = false;
+    for (size_t s = 0; s < ns; s++) {
+        const int32_t fb = c->h_first_bad[s * 2];
+        const uint64_t cb = c->cfg.chunk_bytes;
+        if (fb != INT_MAX && (uint64_t)fb < (q.nbytes + cb - 1) / cb) {
+            lost = true;
+            deliver = std::min<int64_t>(deliver, (int64_t)fb * (int64_t)(cb / 4));
+        }
+    }
+    deliver -= deliver % P.D;
+    if (deliver > 0) {
+        if (run_iir(c, IN_CS16, c->scratch_cs16.p, (size_t)deliver, sstride, q.d_out, q.filt_stride, nullptr, true, 0) != CARIBOU_CUDA_OK)
+            return CARIBOU_CUDA_ERR;
+        if (q.mem != CARIBOU_CUDA_MEM_DEVICE)
+            CBL_CHECK(cudaMemcpyAsync(q.filt_out, q.d_out, (size_t)deliver / P.D * c->out_elem, cudaMemcpyDeviceToHost, c->stream));
+    }
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
+    c->pos -= n;
+    c->pos += (uint64_t)deliver;
+    c->last_ret = lost ? CARIBOU_CUDA_ERR_SYNC : deliver;
+    c->last_n_filtered = deliver / P.D;
+    return CARIBOU_CUDA_OK;
+}
+
+int64_t caribou_cuda_wait(caribou_cuda_ctx* c, caribou_cuda_result* res)
+{
+    if (!c) { set_error("null context"); return CARIBOU_CUDA_ERR; }
+    if (!cuda_ok(cudaSetDevice(c->device), "cudaSetDevice") || !cuda_ok(cudaStreamSynchronize(c->stream), "cudaStreamSynchronize"))
+        return CARIBOU_CUDA_ERR;
+    if (c->pending.active) {
+        c->pending.active = false;
+        if (c->h_counters->any_misaligned != 0) {
+            if (rx_fallback(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        }
+    }
+    int64_t ret = c->last_ret, ret_b = 0;
+    if (c->last_is_unpack) {
+        const int nsub = n_subs_of(c);
+        int64_t r[2] = {0, 0};
+        for (int s = 0; s < nsub; s++) {
+            const SubGeom g = sub_geom(c, nullptr, c->last_nbytes, s);
+            int32_t fb = INT_MAX;
+            for (int st = 0; st < c->cfg.n_streams; st++) fb = std::min(fb, c->h_first_bad[st * 2 + s]);
+            r[s] = delivered_samples(c, g.sv.nbytes, fb == INT_MAX ? -1 : fb);
+        }
+        ret = r[0]; ret_b = r[1];
+        if (nsub == 2 && ret_b < 0) ret = ret_b;
+        c->last_ret = ret;
+    }
+    if (res) {
+        memset(res, 0, sizeof(*res));
+        res->n_samples = ret;
+        res->n_samples_b = ret_b;
+        res->n_filtered = c->last_n_filtered;
+        res->n_invalid = c->h_counters->totals[0];
+        res->n_sync = c->h_counters->totals[1];
+        int32_t fb = INT_MAX;
+        for (int i = 0; i < c->cfg.n_streams * 2; i++) fb = std::min(fb, c->h_first_bad[i]);
+        const uint64_t cb = c->cfg.chunk_bytes;
+        res->first_bad_chunk = (fb != INT_MAX && (uint64_t)fb < (c->last_nbytes + cb - 1) / cb) ? fb : -1;
+        res->n_misaligned_chunks = c->h_counters->n_misaligned;
+    }
+    return ret;
+}
+
+// ------------------------------------------------------------------ state
+int caribou_cuda_get_state(caribou_cuda_ctx* c, int stream, double* state)
+{
+    if (!c || !c->has_filter || !state || stream < 0 || stream >= c->cfg.n_streams) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    if (caribou_cuda_wait(c, nullptr) == CARIBOU_CUDA_ERR) return CARIBOU_CUDA_ERR;
+    const FilterPlan& P = c->plan;
+    double ker[2 * kMaxS];
+    CBL_CHECK(cudaMemcpy(ker, c->d_state + (size_t)stream * 2 * P.S, (size_t)2 * P.S * 8, cudaMemcpyDeviceToHost));
+    state_to_ref(P, ker, state);
+    return CARIBOU_CUDA_OK;
+}
+
+int caribou_cuda_set_state(caribou_cuda_ctx* c, int stream, const double* state)
+{
+    if (!c || !c->has_filter || !state || stream < 0 || stream >= c->cfg.n_streams) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    if (caribou_cuda_wait(c, nullptr) == CARIBOU_CUDA_ERR) return CARIBOU_CUDA_ERR;
+    const FilterPlan& P = c->plan;
+    double ker[2 * kMaxS];
+    state_to_kernel(P, state, ker);
+    CBL_CHECK(cudaMemcpy(c->d_state + (size_t)stream * 2 * P.S, ker, (size_t)2 * P.S * 8, cudaMemcpyHostToDevice));
+    return CARIBOU_CUDA_OK;
+}
+
+int caribou_cuda_reset(caribou_cuda_ctx* c)
+{
+    if (!c) { set_error("null context"); return CARIBOU_CUDA_ERR; }
+    CBL_CHECK(cudaSetDevice(c->device));
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
+    c->pending.active = false;
+    if (c->has_filter) CBL_CHECK(cudaMemset(c->d_state, 0, (size_t)c->cfg.n_streams * 2 * c->plan.S * 8));
+    c->pos = 0;
+    return CARIBOU_CUDA_OK;
+}
+
+// ------------------------------------------------------------------ synthetic words
+int caribou_cuda_synth_words(caribou_cuda_ctx* c, void* dev_words, uint64_t n0, size_t n, int hif_layout, uint64_t seed,
+                             const int16_t* tone_i, const int16_t* tone_q)
+{
+    if (!c || !dev_words || !tone_i || !tone_q) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    CBL_CHECK(cudaSetDevice(c->device));
+    if (!c->d_tone) CBL_CHECK(cudaMalloc(&c->d_tone, 1600 * sizeof(int16_t)));
+    CBL_CHECK(cudaMemcpyAsync(c->d_tone, tone_i, 800 * 2, cudaMemcpyHostToDevice, c->stream));
+    CBL_CHECK(cudaMemcpyAsync(c->d_tone + 800, tone_q, 800 * 2, cudaMemcpyHostToDevice, c->stream));
+    launch_synth(reinterpret_cast<uint32_t*>(dev_words), n0, n, hif_layout, seed, c->d_tone, c->d_tone + 800, c->stream);
+    c->launches++;
+    CBL_CHECK(cudaGetLastError());
+    return CARIBOU_CUDA_OK;
+}
+
+}  // extern "C"

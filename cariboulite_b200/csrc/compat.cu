@@ -1,0 +1,301 @@
+// Drop-in shims: caribou_smi_read / caribou_smi_get_native_batch_samples shaped entry points fed from a
+// file descriptor, and the RX half of SoapySDR::Stream (format switch, MTU clamp, never-reset filters).
+// All sample arithmetic runs in the CUDA kernels; the host side only moves bytes and keeps the
+// reference's control flow (LC/caribou_smi/caribou_smi.c:396-492,624-682; LC/soapy_api/CaribouliteStream.cpp).
+#include <errno.h>
+#include <limits.h>
+#include <poll.h>
+#include <string.h>
+#include <unistd.h>
+#include <functional>
+#include <new>
+#include "ctx.h"
+
+using namespace cbl;
+
+struct caribou_cuda_smi {
+    int fd = -1;
+    size_t native_batch_len = CARIBOU_CUDA_NATIVE_BATCH_LEN;
+    int device = 0;
+    uint32_t sample_rate = 4000000;            // CARIBOU_SMI_SAMPLE_RATE
+    caribou_cuda_ctx* ctx[2] = {nullptr, nullptr};   // one unpack context per channel layout
+    uint8_t* h_stage = nullptr;                 // pinned
+    size_t h_cap = 0;
+};
+
+namespace {
+
+// caribou_smi_calc_read_timeout, caribou_smi.c:624-629
+int calc_read_timeout(uint32_t sample_rate, size_t len)
+{
+    uint32_t to = (uint32_t)((2 * len * 1000) / sample_rate);
+    if (to < 1) to = 1;
+    return (int)(to * 2);
+}
+
+// caribou_smi_poll + caribou_smi_timeout_read, caribou_smi.c:396-441,466-492
+int timeout_read(int fd, uint8_t* buf, size_t len, int timeout_ms)
+{
+    int ret = (int)read(fd, buf, len);
+    if (ret <= 0) {
+        struct pollfd fds;
+        fds.fd = fd; fds.events = POLLIN; fds.revents = 0;
+        int pr;
+        do { pr = poll(&fds, 1, timeout_ms); } while (pr == -1 && (errno == EINTR || errno == EAGAIN));
+        if (pr < 0) return -1;
+        if (pr == 0) return 0;
+        if (!((fds.revents & POLLIN) || (fds.revents & POLLOUT))) return 0;
+        return (int)read(fd, buf, len);
+    }
+    return ret;
+}
+
+caribou_cuda_ctx* smi_ctx(caribou_cuda_smi* d, int channel)
+{
+    const int ch = channel == CARIBOU_CUDA_CH_HIF ? 1 : 0;
+    if (!d->ctx[ch]) {
+        caribou_cuda_config cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.device = d->device;
+        cfg.channel = ch;
+        cfg.chunk_bytes = d->native_batch_len;
+        d->ctx[ch] = caribou_cuda_create(&cfg);
+    }
+    return d->ctx[ch];
+}
+
+bool stage_reserve(caribou_cuda_smi* d, size_t n)
+{
+    if (n <= d->h_cap) return true;
+    uint8_t* p = nullptr;
+    const size_t want = (n + 65535) & ~size_t(65535);
+    if (!cuda_ok(cudaMallocHost(&p, want), "cudaMallocHost")) return false;
+    if (d->h_stage) { memcpy(p, d->h_stage, d->h_cap); cudaFreeHost(d->h_stage); }
+    d->h_stage = p; d->h_cap = want;
+    return true;
+}
+
+// The reference's read loop (caribou_smi.c:632-682).  read(2) results are gathered into segments
+// (a run of full chunks closed by at most one short chunk) and each segment is handed to `flush`
+// (segment bytes, byte count, index of its first output sample), which returns 0 or an error code.
+int read_loop(caribou_cuda_smi* d, size_t length_samples,
+              const std::function<int(const uint8_t*, size_t, size_t)>& flush)
+{
+    size_t left = length_samples * CARIBOU_CUDA_BYTES_PER_SAMPLE;
+    size_t read_so_far = 0, seg_bytes = 0, seg_first = 0;
+    const size_t nbl = d->native_batch_len;
+    while (left) {
+        const size_t cur = left > nbl ? nbl : left;
+        if (!stage_reserve(d, seg_bytes + cur + 64)) return CARIBOU_CUDA_ERR;
+        const int to = calc_read_timeout(d->sample_rate, cur);
+        const int ret = timeout_read(d->fd, d->h_stage + seg_bytes, cur, to);
+        if (ret < 0) return CARIBOU_CUDA_ERR;
+        if (ret == 0) break;                                   // timeout: deliver what we have
+        seg_bytes += (size_t)ret;
+        read_so_far += (size_t)ret / CARIBOU_CUDA_BYTES_PER_SAMPLE;
+        left -= (size_t)ret;
+        if ((size_t)ret != nbl) {                              // short chunk closes the segment
+            const int rc = flush(d->h_stage, seg_bytes, seg_first);
+            if (rc < 0) return rc;
+            seg_bytes = 0; seg_first = read_so_far;
+        }
+    }
+    if (seg_bytes) {
+        const int rc = flush(d->h_stage, seg_bytes, seg_first);
+        if (rc < 0) return rc;
+    }
+    return (int)read_so_far;
+}
+
+// segment -> device CS16 (+meta) at sample offset `first`; returns 0 / -1 / -3
+int unpack_segment_to_device(caribou_cuda_ctx* c, const uint8_t* h, size_t nbytes, uint32_t* d_cs16, uint8_t* d_meta, size_t first)
+{
+    // vector stores need 16-byte aligned slots; a segment that starts at an odd sample offset falls back to scalar stores
+    caribou_cuda_unpack_out o;
+    memset(&o, 0, sizeof(o));
+    o.cs16 = d_cs16 ? d_cs16 + first : nullptr;
+    o.meta = d_meta ? d_meta + first : nullptr;
+    if (!c->stage_in.reserve(nbytes + 64)) return CARIBOU_CUDA_ERR;
+    if (!cuda_ok(cudaMemcpyAsync(c->stage_in.p, h, nbytes, cudaMemcpyHostToDevice, c->stream), "H2D")) return CARIBOU_CUDA_ERR;
+    if (caribou_cuda_unpack_submit(c, c->stage_in.p, nbytes, 0, CARIBOU_CUDA_MEM_DEVICE, &o) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    const int64_t r = caribou_cuda_wait(c, nullptr);   // also guarantees the pinned segment buffer can be reused
+    if (r == CARIBOU_CUDA_ERR_SYNC) return CARIBOU_CUDA_ERR_SYNC;
+    return r < 0 ? CARIBOU_CUDA_ERR : 0;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ format conversion kernel
+// LC/soapy_api/CaribouliteStream.cpp:315-321 (CF32), :337-343 (CF64), :360-364 (CS8)
+__global__ void convert_cs16_kernel(const uint32_t* __restrict__ in, void* __restrict__ out, size_t n, int fmt)
+{
+    for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t w = in[k];
+        const int i = (int)(int16_t)(w & 0xFFFFu), q = (int32_t)w >> 16;
+        if (fmt == CARIBOU_CUDA_FMT_CF32)
+            reinterpret_cast<float2*>(out)[k] = make_float2((float)i / 4096.0f, (float)q / 4096.0f);
+        else if (fmt == CARIBOU_CUDA_FMT_CF64)
+            reinterpret_cast<double2*>(out)[k] = make_double2((double)i / 4096.0, (double)q / 4096.0);
+        else
+            reinterpret_cast<uint16_t*>(out)[k] = (uint16_t)(((uint32_t)(i >> 5) & 0xFFu) | (((uint32_t)(q >> 5) & 0xFFu) << 8));
+    }
+}
+
+struct caribou_cuda_rxstream {
+    caribou_cuda_smi* dev = nullptr;
+    int channel = 0;
+    int format = CARIBOU_CUDA_FMT_CS16;      // CaribouliteStream.cpp:77
+    int filter_type = 0;                     // DigitalFilter_None
+    size_t mtu = 0;
+    caribou_cuda_ctx* filt[4] = {nullptr, nullptr, nullptr, nullptr};   // [1..3]: 20k/50k/100k, never reset
+    DevBuf interm;                           // interm_native_buffer2: MTU+1 CS16, persistent
+    DevBuf user;                             // device image of the caller's CS16 buffer
+    DevBuf conv;                             // converted output
+};
+
+extern "C" {
+
+caribou_cuda_smi* caribou_cuda_smi_open(int fd, size_t native_batch_len, int device)
+{
+    caribou_cuda_smi* d = new (std::nothrow) caribou_cuda_smi();
+    if (!d) { set_error("out of memory"); return nullptr; }
+    d->fd = fd;
+    d->native_batch_len = native_batch_len ? native_batch_len : CARIBOU_CUDA_NATIVE_BATCH_LEN;
+    d->device = device;
+    if (!smi_ctx(d, CARIBOU_CUDA_CH_S1G)) { delete d; return nullptr; }     // fails loudly without a B200
+    return d;
+}
+
+void caribou_cuda_smi_close(caribou_cuda_smi* d)
+{
+    if (!d) return;
+    for (int i = 0; i < 2; i++) if (d->ctx[i]) caribou_cuda_destroy(d->ctx[i]);
+    if (d->h_stage) cudaFreeHost(d->h_stage);
+    delete d;
+}
+
+size_t caribou_cuda_smi_get_native_batch_samples(caribou_cuda_smi* d)
+{
+    return d ? d->native_batch_len / CARIBOU_CUDA_BYTES_PER_SAMPLE : 0;
+}
+
+int caribou_cuda_smi_read(caribou_cuda_smi* d, int channel, caribou_cuda_sample_complex_int16* buffer,
+                          caribou_cuda_sample_meta* metadata, size_t length_samples)
+{
+    if (!d) { set_error("null device"); return CARIBOU_CUDA_ERR; }
+    caribou_cuda_ctx* c = smi_ctx(d, channel);
+    if (!c) return CARIBOU_CUDA_ERR;
+    auto flush = [&](const uint8_t* h, size_t nbytes, size_t first) -> int {
+        caribou_cuda_unpack_out o;
+        memset(&o, 0, sizeof(o));
+        o.cs16 = buffer ? (void*)(buffer + first) : nullptr;
+        o.meta = metadata ? (void*)(metadata + first) : nullptr;
+        if (caribou_cuda_unpack_submit(c, h, nbytes, 0, CARIBOU_CUDA_MEM_HOST, &o) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        const int64_t r = caribou_cuda_wait(c, nullptr);
+        if (r == CARIBOU_CUDA_ERR_SYNC) return CARIBOU_CUDA_ERR_SYNC;
+        return r < 0 ? CARIBOU_CUDA_ERR : 0;
+    };
+    return read_loop(d, length_samples, flush);
+}
+
+// ------------------------------------------------------------------ Stream
+caribou_cuda_rxstream* caribou_cuda_rxstream_create(caribou_cuda_smi* dev, int channel)
+{
+    if (!dev) { set_error("null device"); return nullptr; }
+    caribou_cuda_rxstream* s = new (std::nothrow) caribou_cuda_rxstream();
+    if (!s) { set_error("out of memory"); return nullptr; }
+    s->dev = dev;
+    s->channel = channel;
+    s->mtu = caribou_cuda_smi_get_native_batch_samples(dev);           // CaribouliteStream.cpp:66,118-121
+    // filt20/50/100: LowPass<6>.setup(4e6, {20e3,50e3,100e3}/2), CaribouliteStream.cpp:85-91
+    const double fc[4] = {0, 20e3 / 2, 50e3 / 2, 100e3 / 2};
+    for (int t = 1; t <= 3; t++) {
+        caribou_cuda_config cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.device = dev->device;
+        cfg.n_sos = caribou_cuda_butter_lowpass(6, 4e6, fc[t], &cfg.sos[0][0]);
+        cfg.decimation = 1;
+        cfg.parity = CARIBOU_CUDA_PARITY_Q16;
+        cfg.out_format = CARIBOU_CUDA_FMT_CS16;       // filtered in place as int16, CaribouliteStream.cpp:291-298
+        s->filt[t] = caribou_cuda_create(&cfg);
+        if (!s->filt[t]) { caribou_cuda_rxstream_destroy(s); return nullptr; }
+    }
+    cudaSetDevice(dev->device);
+    if (!s->interm.reserve((s->mtu + 4) * 4)) { caribou_cuda_rxstream_destroy(s); return nullptr; }
+    cudaMemset(s->interm.p, 0, (s->mtu + 4) * 4);
+    return s;
+}
+
+void caribou_cuda_rxstream_destroy(caribou_cuda_rxstream* s)
+{
+    if (!s) return;
+    for (int t = 0; t < 4; t++) if (s->filt[t]) caribou_cuda_destroy(s->filt[t]);
+    s->interm.release(); s->user.release(); s->conv.release();
+    delete s;
+}
+
+int caribou_cuda_rxstream_set_format(caribou_cuda_rxstream* s, const char* fmt)
+{
+    if (!s || !fmt) return -1;                                             // CaribouliteStream.cpp:158-173
+    if (!strcmp(fmt, "CS16")) s->format = CARIBOU_CUDA_FMT_CS16;
+    else if (!strcmp(fmt, "CS8")) s->format = CARIBOU_CUDA_FMT_CS8;
+    else if (!strcmp(fmt, "CF32")) s->format = CARIBOU_CUDA_FMT_CF32;
+    else if (!strcmp(fmt, "CF64")) s->format = CARIBOU_CUDA_FMT_CF64;
+    else return -1;
+    return 0;
+}
+
+void caribou_cuda_rxstream_set_filter(caribou_cuda_rxstream* s, int type)
+{
+    if (!s) return;
+    s->filter_type = (type >= 1 && type <= 3) ? type : 0;                  // CaribouliteStream.cpp:127-141 (200 kHz has no case)
+}
+
+size_t caribou_cuda_rxstream_mtu(caribou_cuda_rxstream* s) { return s ? s->mtu : 0; }
+
+// Stream::ReadSamples(cs16*) on a device buffer: read + unpack into d_buf, then the in-place int16 filter.
+static int stream_read_cs16_device(caribou_cuda_rxstream* s, uint32_t* d_buf, size_t n)
+{
+    caribou_cuda_smi* d = s->dev;
+    caribou_cuda_ctx* c = smi_ctx(d, s->channel);
+    if (!c) return 0;
+    auto flush = [&](const uint8_t* h, size_t nbytes, size_t first) -> int {
+        return unpack_segment_to_device(c, h, nbytes, d_buf, nullptr, first);
+    };
+    int res = read_loop(d, n, flush);
+    if (res < 0) res = 0;                                                  // CaribouliteStream.cpp:266-276
+    if (res > 0 && s->filter_type != 0) {
+        caribou_cuda_ctx* f = s->filt[s->filter_type];
+        // the unpack ran on another stream: it has been waited for in flush(), so ordering is safe
+        if (caribou_cuda_filter_submit(f, CARIBOU_CUDA_IN_CS16, d_buf, (size_t)res, 0, CARIBOU_CUDA_MEM_DEVICE, d_buf, 0) != CARIBOU_CUDA_OK)
+            return 0;
+        if (caribou_cuda_wait(f, nullptr) < 0) return 0;
+    }
+    return res;
+}
+
+int caribou_cuda_rxstream_read(caribou_cuda_rxstream* s, void* buffer, size_t num_elements, long timeout_us)
+{
+    (void)timeout_us;                                                      // unused by the reference as well
+    if (!s || !buffer) { set_error("bad argument"); return 0; }
+    cudaSetDevice(s->dev->device);
+    if (s->format == CARIBOU_CUDA_FMT_CS16) {
+        // no MTU clamp for CS16 (CaribouliteStream.cpp:282-301); slots the read leaves untouched keep the caller's bytes
+        if (!s->user.reserve((num_elements + 4) * 4)) return 0;
+        if (!cuda_ok(cudaMemcpy(s->user.p, buffer, num_elements * 4, cudaMemcpyHostToDevice), "H2D")) return 0;
+        const int res = stream_read_cs16_device(s, s->user.as<uint32_t>(), num_elements);
+        if (res > 0 && !cuda_ok(cudaMemcpy(buffer, s->user.p, (size_t)res * 4, cudaMemcpyDeviceToHost), "D2H")) return 0;
+        return res;
+    }
+    if (num_elements > s->mtu) num_elements = s->mtu;                     // CaribouliteStream.cpp:306,328,351
+    const int res = stream_read_cs16_device(s, s->interm.as<uint32_t>(), num_elements);
+    if (res <= 0) return res;
+    const size_t es = s->format == CARIBOU_CUDA_FMT_CF32 ? 8 : (s->format == CARIBOU_CUDA_FMT_CF64 ? 16 : 2);
+    if (!s->conv.reserve((size_t)res * es + 64)) return 0;
+    convert_cs16_kernel<<<(unsigned)std::min<size_t>(((size_t)res + 255) / 256, 1184), 256>>>(s->interm.as<uint32_t>(), s->conv.p, (size_t)res, s->format);
+    if (!cuda_ok(cudaGetLastError(), "convert_cs16_kernel")) return 0;
+    if (!cuda_ok(cudaMemcpy(buffer, s->conv.p, (size_t)res * es, cudaMemcpyDeviceToHost), "D2H")) return 0;
+    return res;
+}
+
+}  // extern "C"

@@ -1,0 +1,129 @@
+// Kernel (b) dispatch + the sequential tail kernel (samples that do not fill a whole run).
+#include "iir_kernel.cuh"
+
+namespace cbl {
+
+iir_launch_fn iir_launch_k1(int, int); iir_launch_fn iir_launch_k2(int, int);
+iir_launch_fn iir_launch_k3(int, int); iir_launch_fn iir_launch_k4(int, int);
+iir_occ_fn iir_occ_k1(int, int); iir_occ_fn iir_occ_k2(int, int);
+iir_occ_fn iir_occ_k3(int, int); iir_occ_fn iir_occ_k4(int, int);
+
+size_t iir_smem_bytes(int K, int D, int in_kind)
+{
+    const int LT = iir_run_len(D), NK = LT / D, SPS = in_kind == IN_CF32 ? 16 : 32;
+    const int nstep = LT / SPS, stages = nstep < kIirRingStages ? nstep : kIirRingStages;
+    const int warp_bytes = stages * 4096 + NK * 2 * 32 * 8 + 2 * (2 * K) * 8 * 2;
+    return (size_t)kIirWarpsPerCta * warp_bytes + kIirWarpsPerCta * stages * 8 + 1024;
+}
+
+int launch_iir(int K, int D, int in_kind, const CUtensorMap& tmap, const IirParams& p, const IirTables& t,
+               int grid_ctas, cudaStream_t st)
+{
+    iir_launch_fn fn = nullptr;
+    switch (K) {
+        case 1: fn = iir_launch_k1(D, in_kind); break;
+        case 2: fn = iir_launch_k2(D, in_kind); break;
+        case 3: fn = iir_launch_k3(D, in_kind); break;
+        case 4: fn = iir_launch_k4(D, in_kind); break;
+    }
+    if (!fn) return (int)cudaErrorInvalidValue;
+    return fn(tmap, p, t, grid_ctas, st);
+}
+
+int iir_max_ctas_per_sm(int K, int D, int in_kind)
+{
+    iir_occ_fn fn = nullptr;
+    switch (K) {
+        case 1: fn = iir_occ_k1(D, in_kind); break;
+        case 2: fn = iir_occ_k2(D, in_kind); break;
+        case 3: fn = iir_occ_k3(D, in_kind); break;
+        case 4: fn = iir_occ_k4(D, in_kind); break;
+    }
+    return fn ? fn() : 0;
+}
+
+// ------------------------------------------------------------------ sequential tail
+// One thread per stream walks samples [first, n) with the same (normalised) arithmetic, starting
+// from and updating the stream state.  Used for the < one-run remainder of a submit.
+__global__ void iir_tail_kernel(const __grid_constant__ IirTailParams P)
+{
+    const uint32_t stream = blockIdx.x * blockDim.x + threadIdx.x;
+    if (stream >= P.n_streams) return;
+    if (P.gate != nullptr && *P.gate != 0) return;
+    const int K = P.K, S = 2 * K;
+    double vi[kMaxK][2], vq[kMaxK][2];
+    double* sp = P.state + (size_t)stream * (2 * S);
+    for (int k = 0; k < K; k++) {
+        vi[k][0] = sp[2 * k]; vi[k][1] = sp[2 * k + 1];
+        vq[k][0] = sp[S + 2 * k]; vq[k][1] = sp[S + 2 * k + 1];
+    }
+    for (uint64_t n = P.first; n < P.n; n++) {
+        const uint64_t e = (uint64_t)stream * P.in_stride + n;
+        double xi, xq;
+        if (P.in_kind == IN_WORDS) {
+            const uint32_t w = reinterpret_cast<const uint32_t*>(P.in)[e];
+            const int h = hi13(w), l = lo13(w);
+            xi = (double)(P.layout ? l : h); xq = (double)(P.layout ? h : l);
+        } else if (P.in_kind == IN_CS16) {
+            const uint32_t w = reinterpret_cast<const uint32_t*>(P.in)[e];
+            xi = (double)(int)(int16_t)(w & 0xFFFFu); xq = (double)((int32_t)w >> 16);
+        } else {
+            const float2 v = reinterpret_cast<const float2*>(P.in)[e];
+            xi = (double)v.x; xq = (double)v.y;
+        }
+        double ii = xi, iq = xq;
+        for (int k = 0; k < K; k++) {
+            const double ti = fma(-P.a2[k], vi[k][1], ii), wi = fma(-P.a1[k], vi[k][0], ti);
+            const double tq = fma(-P.a2[k], vq[k][1], iq), wq = fma(-P.a1[k], vq[k][0], tq);
+            ii = fma(P.c2[k], vi[k][1], fma(P.c1[k], vi[k][0], wi));
+            iq = fma(P.c2[k], vq[k][1], fma(P.c1[k], vq[k][0], wq));
+            vi[k][1] = vi[k][0]; vi[k][0] = wi;
+            vq[k][1] = vq[k][0]; vq[k][0] = wq;
+        }
+        if (n % P.D == 0) {
+            const double yi = ii * P.gain, yq = iq * P.gain;
+            const uint64_t o = (uint64_t)stream * P.out_stride + n / P.D;
+            if (P.out_mode == OUT_F32) {
+                reinterpret_cast<float2*>(P.out)[o] = make_float2((float)yi, (float)yq);
+            } else if (P.out_mode == OUT_F64) {
+                reinterpret_cast<double2*>(P.out)[o] = make_double2(yi, yq);
+            } else {
+                const int qi = (int)(int16_t)__float2int_rz((float)yi);
+                const int qq = (int)(int16_t)__float2int_rz((float)yq);
+                if (P.out_mode == OUT_Q16_CS16)
+                    reinterpret_cast<uint32_t*>(P.out)[o] = ((uint32_t)qi & 0xFFFFu) | ((uint32_t)qq << 16);
+                else if (P.out_mode == OUT_Q16_CF32)
+                    reinterpret_cast<float2*>(P.out)[o] = make_float2((float)qi * (1.0f / 4096.0f), (float)qq * (1.0f / 4096.0f));
+                else if (P.out_mode == OUT_Q16_CF64)
+                    reinterpret_cast<double2*>(P.out)[o] = make_double2((double)qi * (1.0 / 4096.0), (double)qq * (1.0 / 4096.0));
+                else
+                    reinterpret_cast<uint16_t*>(P.out)[o] =
+                        (uint16_t)(((uint32_t)(qi >> 5) & 0xFFu) | (((uint32_t)(qq >> 5) & 0xFFu) << 8));
+            }
+        }
+    }
+    for (int k = 0; k < K; k++) {
+        sp[2 * k] = vi[k][0]; sp[2 * k + 1] = vi[k][1];
+        sp[S + 2 * k] = vq[k][0]; sp[S + 2 * k + 1] = vq[k][1];
+    }
+}
+
+void launch_iir_tail(const IirTailParams& p, cudaStream_t st)
+{
+    if (p.n_streams == 0 || p.first >= p.n) return;
+    iir_tail_kernel<<<(p.n_streams + 31) / 32, 32, 0, st>>>(p);
+}
+
+__global__ void commit_state_kernel(double* state, const double* next, size_t n, const int32_t* gate)
+{
+    if (gate != nullptr && *gate != 0) return;
+    for (size_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) state[i] = next[i];
+}
+
+void launch_commit_state(double* state, const double* state_next, size_t n, const int32_t* gate, cudaStream_t st)
+{
+    if (n == 0) return;
+    commit_state_kernel<<<(unsigned)((n + 255) / 256 > 64 ? 64 : (n + 255) / 256), 256, 0, st>>>(state, state_next, n, gate);
+}
+
+}  // namespace cbl

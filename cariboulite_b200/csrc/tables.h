@@ -1,0 +1,33 @@
+// Host-side filter design and scan tables for kernel (b).
+#pragma once
+#include <stdint.h>
+#include <vector>
+#include "iir.cuh"
+
+namespace cbl {
+
+// Butterworth low-pass as iir1 designs it (LC/iir/iir/Butterworth.cpp:49-68, PoleFilter.cpp:47-90,
+// Biquad.cpp:123-201, Cascade.cpp:94-118).  sos rows (b0,b1,b2,a0,a1,a2). Returns stages or -1.
+int butter_lowpass_sos(int order, double fs, double fc, double* sos);
+
+// Everything the kernels need for one (cascade, decimation) pair.
+struct FilterPlan {
+    int K = 0, D = 1, LT = 32, NK = 32, S = 0;
+    double g[kMaxK + 1];          // g[k] = prod_{j<k} b0_j ; g[K] = overall gain G
+    IirTables tables;             // constant-bank tables (gain left at G; the caller applies the output scale)
+    std::vector<double> plane;    // [S*S][33]  (M^t)[e] at plane[e*33 + t]
+    std::vector<double> mtile_pow;// [window+1][S*S]
+    int window = 1;               // look-back window J (tiles)
+    bool chained = false;         // no useful contraction: serial inclusive chain
+    long double A[kMaxS][kMaxS];  // one-sample transition, kernel coordinates
+    uint64_t decay_samples = 0;   // n with |A^n| (scaled) < 2^-60 for all larger n (0 if chained)
+    std::vector<long double> scale;  // typical magnitude of each state component
+};
+
+// false (with msg) if the cascade cannot be handled (b0 == 0, non-finite coefficients, ...)
+bool make_filter_plan(int K, const double (*sos)[6], int D, FilterPlan* plan, const char** msg);
+
+// A^n in REFERENCE state coordinates (row-major S x S doubles)
+void plan_shard_matrix(const FilterPlan& plan, uint64_t n, double* m);
+
+}  // namespace cbl

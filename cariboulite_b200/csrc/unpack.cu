@@ -1,0 +1,350 @@
+// Kernel (a) of libcaribou_cuda: per-chunk alignment search and the fused
+// unpack / demux / sync-check / sign-extend / CS16 / CF32 kernel with ordered
+// warp-ballot compaction of flagged words.
+//
+// What it computes is fixed by the reference (LC/caribou_smi/caribou_smi.c:235-393); how it
+// is computed is not: one thread owns 8 consecutive raw words (two 128-bit loads), emits one
+// 128-bit CS16 store, two 128-bit CF32 stores and one 32-bit meta store per 4 samples, and the
+// ascending index lists come from a single-pass chained scan over tiles (decoupled look-back).
+#include "unpack.cuh"
+#include <limits.h>
+
+namespace cbl {
+
+// ------------------------------------------------------------------ alignment search (A2)
+// One CTA per chunk.  Candidate 0 is tested first (the aligned common case); otherwise the CTA
+// sweeps the chunk 1024 candidates at a time and stops at the first hit.
+__global__ void __launch_bounds__(256) find_offsets_kernel(OffsetsParams p)
+{
+    __shared__ int s_found;
+    const uint32_t c = blockIdx.x;
+    p.sv.words = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(p.sv.words) +
+                                                   (uint64_t)blockIdx.y * p.stream_stride_bytes);
+    const uint64_t start = (uint64_t)c * p.chunk_bytes;
+    const uint64_t rem = p.sv.nbytes - start;
+    const uint32_t len = rem < p.chunk_bytes ? (uint32_t)rem : p.chunk_bytes;
+    int result;
+    if (len <= 16) {                       // caribou_smi.c:240-243
+        result = 0;
+    } else {
+        if (threadIdx.x == 0) {
+            bool ok = true;
+            for (int k = 0; k < 4; k++) ok = ok && hdr_ok(sv_u32_at(p.sv, start + 4 * k));
+            s_found = ok ? 0 : INT_MAX;
+        }
+        __syncthreads();
+        result = s_found;
+        if (result != 0) {
+            const uint32_t ncand = len - 16;        // candidates offs in [0, len-16), caribou_smi.c:248
+            for (uint32_t base = 0; base < ncand; base += 1024) {
+                // this thread: candidates base + 4*tid + {0,1,2,3}; they share aligned words w[0..4]
+                const uint32_t o0 = base + 4 * threadIdx.x;
+                if (o0 < ncand) {
+                    uint32_t w[5];
+                    const uint64_t wi = (start + o0) >> 2;   // start is a multiple of 4 (chunk_bytes % 16 == 0)
+#pragma unroll
+                    for (int k = 0; k < 5; k++) w[k] = sv_word(p.sv, wi + k);
+#pragma unroll
+                    for (int b = 0; b < 4; b++) {
+                        if (o0 + b < ncand) {
+                            bool ok = true;
+#pragma unroll
+                            for (int k = 0; k < 4; k++) {
+                                const uint32_t u = b ? __funnelshift_r(w[k], w[k + 1], 8 * b) : w[k];
+                                ok = ok && hdr_ok(u);
+                            }
+                            if (ok) { atomicMin(&s_found, (int)(o0 + b)); break; }
+                        }
+                    }
+                }
+                __syncthreads();
+                result = s_found;
+                __syncthreads();
+                if (result != INT_MAX) break;
+            }
+            if (result == INT_MAX) result = -1;    // caribou_smi.c:285-289
+        }
+    }
+    if (threadIdx.x == 0) {
+        p.offs[(size_t)blockIdx.y * p.offs_stride + c] = result;
+        if (result < 0) atomicMin(p.first_bad + (size_t)blockIdx.y * p.first_bad_stride, (int)c);
+        if (result > 0) atomicAdd(p.n_misaligned, 1);
+        if (result != 0) *p.any_misaligned = 1;
+    }
+}
+
+void launch_find_offsets(const OffsetsParams& p, cudaStream_t st)
+{
+    if (p.n_chunks == 0 || p.n_streams == 0) return;
+    find_offsets_kernel<<<dim3(p.n_chunks, p.n_streams), 256, 0, st>>>(p);
+}
+
+// ------------------------------------------------------------------ decode helpers (A3)
+__device__ __forceinline__ void decode_iq(uint32_t w, int layout, int& i, int& q)
+{
+    const int h = hi13(w), l = lo13(w);
+    i = layout ? l : h;      // S1G: i = bits 29:17 (caribou_smi.c:351-354); HiF: i = bits 13:1 (:371-373)
+    q = layout ? h : l;
+}
+__device__ __forceinline__ uint32_t pack_cs16(int i, int q)
+{
+    return ((uint32_t)i & 0xFFFFu) | ((uint32_t)q << 16);
+}
+__device__ __forceinline__ float2 to_cf32(int i, int q)
+{
+    // (float)v / 4096.0f, exact for |v| <= 4096 (LC/CaribouLiteRadioCpp.cpp:91)
+    return make_float2((float)i * (1.0f / 4096.0f), (float)q * (1.0f / 4096.0f));
+}
+
+// Four consecutive output slots j0..j0+3 of sub-stream `s` whose aligned source words are w[0..3].
+__device__ __forceinline__ void emit_group(const UnpackParams& p, int s, uint64_t j0, const uint32_t (&w)[4])
+{
+    const SubView& sv = p.sv[s];
+    if (j0 * 4 >= sv.nbytes) return;
+    const uint32_t c = (uint32_t)(j0 / p.spc);
+    if ((int)c >= *p.first_bad[s]) return;                 // caribou_smi.c:665-668: nothing after a lost sync
+    const uint32_t l0 = (uint32_t)(j0 - (uint64_t)c * p.spc);
+    const int offs = p.offs[s][c];
+    const uint64_t cstart = (uint64_t)c * p.chunk_bytes;
+    const uint64_t rem = sv.nbytes - cstart;
+    const uint32_t len = rem < p.chunk_bytes ? (uint32_t)rem : p.chunk_bytes;
+    const uint32_t nfull = len >> 2;
+    const int layout = p.layout[s];
+    if (offs == 0 && l0 + 4 <= nfull && p.vec_ok) {
+        int i[4], q[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) decode_iq(w[e], layout, i[e], q[e]);
+        if (p.cs16[s]) {
+            uint4 v = make_uint4(pack_cs16(i[0], q[0]), pack_cs16(i[1], q[1]), pack_cs16(i[2], q[2]), pack_cs16(i[3], q[3]));
+            __stcs(reinterpret_cast<uint4*>(p.cs16[s] + j0), v);
+        }
+        if (p.meta[s]) {
+            const uint32_t m = (w[0] & 1u) | ((w[1] & 1u) << 8) | ((w[2] & 1u) << 16) | ((w[3] & 1u) << 24);
+            __stcs(reinterpret_cast<uint32_t*>(p.meta[s] + j0), m);
+        }
+        if (p.cf32[s]) {
+            const float2 a = to_cf32(i[0], q[0]), b = to_cf32(i[1], q[1]);
+            const float2 cc = to_cf32(i[2], q[2]), d = to_cf32(i[3], q[3]);
+            float4* o = reinterpret_cast<float4*>(p.cf32[s] + j0);
+            __stcs(o, make_float4(a.x, a.y, b.x, b.y));
+            __stcs(o + 1, make_float4(cc.x, cc.y, d.x, d.y));
+        }
+        return;
+    }
+    // general path: misaligned chunk, chunk tail, or unaligned output pointers
+    const uint32_t shorten = offs > 0 ? (uint32_t)offs / 4 + 1 : 0;        // caribou_smi.c:323
+    const uint32_t nvalid = nfull - shorten;
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+        const uint32_t l = l0 + e;
+        const uint64_t j = j0 + e;
+        if (l < nvalid) {
+            const uint32_t u = offs == 0 ? w[e] : sv_u32_at(sv, cstart + offs + 4ull * l);
+            int i, q;
+            decode_iq(u, layout, i, q);
+            if (p.cs16[s]) p.cs16[s][j] = pack_cs16(i, q);
+            if (p.meta[s]) p.meta[s][j] = (uint8_t)(u & 1u);
+            if (p.cf32[s]) p.cf32[s][j] = to_cf32(i, q);
+        } else if (l == nvalid && shorten > 0 && nvalid >= 2 && (p.cs16[s] || p.cf32[s])) {
+            // caribou_smi.c:382-389: one extrapolated sample, C int arithmetic, narrowed to int16;
+            // its meta slot is not written
+            int i1, q1, i2, q2;
+            decode_iq(sv_u32_at(sv, cstart + offs + 4ull * (l - 1)), layout, i1, q1);
+            decode_iq(sv_u32_at(sv, cstart + offs + 4ull * (l - 2)), layout, i2, q2);
+            const int i = (int)(int16_t)(110 * i1 / 100 - i2 / 10);
+            const int q = (int)(int16_t)(110 * q1 / 100 - q2 / 10);
+            if (p.cs16[s]) p.cs16[s][j] = pack_cs16(i, q);
+            if (p.cf32[s]) p.cf32[s][j] = to_cf32(i, q);
+        }
+        // l > nvalid: slot left untouched, as the reference leaves it
+    }
+}
+
+// ------------------------------------------------------------------ chained scan of flag counts
+__device__ __forceinline__ uint64_t ld_acquire_u64(const uint64_t* p)
+{
+    uint64_t v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u64(uint64_t* p, uint64_t v)
+{
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+constexpr uint64_t kDescAgg  = 1ull << 62;
+constexpr uint64_t kDescIncl = 2ull << 62;
+constexpr uint64_t kDescVal  = (1ull << 62) - 1;
+
+// exclusive prefix of `mine` over tiles [0, tile) (+ base for tile 0); publishes this tile's inclusive value
+__device__ uint64_t lookback_count(uint64_t* desc, uint32_t tile, uint64_t mine, uint64_t base)
+{
+    if (tile == 0) {
+        st_release_u64(desc, kDescIncl | (base + mine));
+        return base;
+    }
+    st_release_u64(desc + tile, kDescAgg | mine);
+    uint64_t excl = 0;
+    for (int64_t j = (int64_t)tile - 1; j >= 0; j--) {
+        uint64_t d;
+        do { d = ld_acquire_u64(desc + j); } while ((d >> 62) == 0);
+        excl += d & kDescVal;
+        if ((d >> 62) == 2) break;
+    }
+    st_release_u64(desc + tile, kDescIncl | (excl + mine));
+    return excl;
+}
+
+__global__ void __launch_bounds__(kUnpackThreads) unpack_kernel(const __grid_constant__ UnpackParams p)
+{
+    __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_cnt[kUnpackIters][kUnpackThreads / 32][2];
+    __shared__ uint64_t s_excl[2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    // tiles are handed out in launch order so that a tile's predecessors are always resident
+    if (threadIdx.x == 0) s_tile = p.want_flags ? atomicAdd(p.ticket, 1u) : blockIdx.x;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+
+    const uint64_t n_raw = p.nbytes >> 2;            // whole raw words
+    uint32_t inv8[kUnpackIters], syn8[kUnpackIters], pre[kUnpackIters];
+
+#pragma unroll
+    for (int it = 0; it < kUnpackIters; it++) {
+        const uint64_t g = ((uint64_t)tile * kUnpackIters + it) * kUnpackThreads + threadIdx.x;
+        const uint64_t k0 = g * 8;
+        uint32_t w[8];
+        inv8[it] = syn8[it] = 0; pre[it] = 0;
+        if (g < p.n_groups) {
+            if (k0 + 8 <= n_raw) {
+                const uint4 a = __ldcs(reinterpret_cast<const uint4*>(p.words + k0));
+                const uint4 b = __ldcs(reinterpret_cast<const uint4*>(p.words + k0 + 4));
+                w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
+                w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; e++) w[e] = (k0 + e < n_raw) ? p.words[k0 + e] : 0u;
+            }
+            if (p.want_flags) {
+#pragma unroll
+                for (int e = 0; e < 8; e++) {
+                    if (k0 + e < n_raw) {
+                        inv8[it] |= (hdr_ok(w[e]) ? 0u : 1u) << e;
+                        syn8[it] |= (w[e] & 1u) << e;
+                    }
+                }
+            }
+            // decode + store
+            if (p.B == 0) {
+                // the (possibly partial) tail word still has to reach sv_word's byte-wise path
+                if (k0 + 8 > n_raw) {
+#pragma unroll
+                    for (int e = 0; e < 8; e++) w[e] = sv_word(p.sv[0], k0 + e);
+                }
+                const uint32_t lo[4] = {w[0], w[1], w[2], w[3]}, hi[4] = {w[4], w[5], w[6], w[7]};
+                emit_group(p, 0, k0, lo);
+                emit_group(p, 0, k0 + 4, hi);
+            } else if (p.B == 1) {
+                const uint32_t ev[4] = {w[0], w[2], w[4], w[6]}, od[4] = {w[1], w[3], w[5], w[7]};
+                emit_group(p, 0, k0 >> 1, ev);
+                emit_group(p, 1, k0 >> 1, od);
+            } else {   // B % 8 == 0: the whole group belongs to one sub-stream
+                const int s = (int)((k0 / p.B) & 1u);
+                const uint64_t j0 = (k0 / (2ull * p.B)) * p.B + k0 % p.B;
+                const uint32_t lo[4] = {w[0], w[1], w[2], w[3]}, hi[4] = {w[4], w[5], w[6], w[7]};
+                emit_group(p, s, j0, lo);
+                emit_group(p, s, j0 + 4, hi);
+            }
+        }
+        if (p.want_flags) {
+            // warp-ballot: is anything flagged in this warp-iteration at all?
+            const uint32_t any = __ballot_sync(0xffffffffu, (inv8[it] | syn8[it]) != 0);
+            uint32_t ci = 0, cs = 0;
+            if (any) {
+                // packed inclusive warp scan of (invalid, sync) counts: 16 bits each (max 256)
+                uint32_t v = __popc(inv8[it]) | (__popc(syn8[it]) << 16);
+                const uint32_t own = v;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const uint32_t u = __shfl_up_sync(0xffffffffu, v, d);
+                    if (lane >= d) v += u;
+                }
+                pre[it] = v - own;                               // exclusive, this thread
+                const uint32_t tot = __shfl_sync(0xffffffffu, v, 31);
+                ci = tot & 0xFFFFu; cs = tot >> 16;
+            }
+            if (lane == 0) { s_cnt[it][warp][0] = ci; s_cnt[it][warp][1] = cs; }
+        }
+    }
+    if (!p.want_flags) return;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t ti = 0, ts = 0;
+        for (int it = 0; it < kUnpackIters; it++)
+            for (int wv = 0; wv < kUnpackThreads / 32; wv++) {
+                const uint32_t a = s_cnt[it][wv][0], b = s_cnt[it][wv][1];
+                s_cnt[it][wv][0] = ti; s_cnt[it][wv][1] = ts;       // exclusive base within the tile
+                ti += a; ts += b;
+            }
+        const uint64_t bi = tile == 0 ? p.totals[0] : 0, bs = tile == 0 ? p.totals[1] : 0;
+        const uint64_t ei = lookback_count(p.desc_inv, tile, ti, bi);
+        const uint64_t es = lookback_count(p.desc_syn, tile, ts, bs);
+        s_excl[0] = ei; s_excl[1] = es;
+        if (tile == p.n_tiles - 1) { p.totals[0] = ei + ti; p.totals[1] = es + ts; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < kUnpackIters; it++) {
+        if ((inv8[it] | syn8[it]) == 0) continue;
+        const uint64_t g = ((uint64_t)tile * kUnpackIters + it) * kUnpackThreads + threadIdx.x;
+        const uint64_t k0 = p.index_base + g * 8;
+        uint64_t pi = s_excl[0] + s_cnt[it][warp][0] + (pre[it] & 0xFFFFu);
+        uint64_t ps = s_excl[1] + s_cnt[it][warp][1] + (pre[it] >> 16);
+        for (int e = 0; e < 8; e++) {
+            if ((inv8[it] >> e) & 1u) { if (p.inv_idx && pi < p.inv_cap) p.inv_idx[pi] = (uint32_t)(k0 + e); pi++; }
+            if ((syn8[it] >> e) & 1u) { if (p.syn_idx && ps < p.syn_cap) p.syn_idx[ps] = (uint32_t)(k0 + e); ps++; }
+        }
+    }
+}
+
+void launch_unpack(const UnpackParams& p, cudaStream_t st)
+{
+    if (p.n_tiles == 0) return;
+    unpack_kernel<<<p.n_tiles, kUnpackThreads, 0, st>>>(p);
+}
+
+// ------------------------------------------------------------------ synthetic words
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x)
+{
+    uint64_t z = x + 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+__global__ void synth_kernel(uint32_t* out, uint64_t n0, uint64_t n, int hif_layout, uint64_t seed,
+                             const int16_t* __restrict__ tone_i, const int16_t* __restrict__ tone_q)
+{
+    for (uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t g = n0 + k;
+        const int ph = (int)(g % 800u);
+        const int ui = (int)(splitmix64(seed ^ (g * 2 + 0)) & 127u) - 64;
+        const int uq = (int)(splitmix64(seed ^ (g * 2 + 1)) & 127u) - 64;
+        int I = tone_i[ph] + ui, Q = tone_q[ph] + uq;
+        I = max(-4096, min(4095, I));
+        Q = max(-4096, min(4095, Q));
+        const uint32_t S = (g % 4000000u) == 0;
+        const uint32_t hi = (uint32_t)(hif_layout ? Q : I) & 0x1FFFu;
+        const uint32_t lo = (uint32_t)(hif_layout ? I : Q) & 0x1FFFu;
+        out[k] = 0x80004000u | (hi << 17) | (lo << 1) | S;
+    }
+}
+
+void launch_synth(uint32_t* out, uint64_t n0, uint64_t n, int hif_layout, uint64_t seed,
+                  const int16_t* tone_i, const int16_t* tone_q, cudaStream_t st)
+{
+    if (n == 0) return;
+    synth_kernel<<<148 * 8, 256, 0, st>>>(out, n0, n, hif_layout, seed, tone_i, tone_q);
+}
+
+}  // namespace cbl

@@ -1,0 +1,221 @@
+/* libcaribou_cuda - B200 (sm_100a) implementation of CaribouLite's receive-side sample path.
+ *
+ * Plain C ABI: pointers, sizes and PODs only.  Every entry point names the reference
+ * interface it stands in for ("LC/" = software/libcariboulite/src/ of Habraken/cariboulite).
+ *
+ *   raw SMI words -> (alignment search per chunk) -> demux -> 13-bit sign-extend -> CS16 / meta
+ *                 -> CF32 -> Butterworth biquad cascade (iir1 DF-II semantics, FP64) -> decimate
+ *
+ * There is no CPU fallback: every compute entry point launches CUDA kernels and fails with
+ * CARIBOU_CUDA_ERR (-1) if the device or the kernels are unavailable.
+ *
+ * Return convention (same as LC/caribou_smi/caribou_smi.c:632-682 and
+ * LC/cariboulite_radio.c:1258-1285): >= 0 number of samples delivered, 0 = nothing to
+ * read ("timeout"), -1 = I/O / CUDA failure, -2 = reserved (debug mode, never produced),
+ * -3 = a chunk had no word alignment ("sync lost").
+ */
+#ifndef CARIBOU_CUDA_H
+#define CARIBOU_CUDA_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CARIBOU_CUDA_OK            0
+#define CARIBOU_CUDA_ERR          (-1)
+#define CARIBOU_CUDA_ERR_DEBUG    (-2)
+#define CARIBOU_CUDA_ERR_SYNC     (-3)
+
+#define CARIBOU_CUDA_BYTES_PER_SAMPLE  4        /* LC/caribou_smi/caribou_smi.h:42 */
+#define CARIBOU_CUDA_NATIVE_BATCH_LEN  524288   /* LC/caribou_smi/caribou_smi.c:74-79 */
+#define CARIBOU_CUDA_MAX_SOS           4
+
+/* caribou_smi_channel_en, LC/caribou_smi/caribou_smi.h:45-49: the channel only selects
+ * which 13-bit field is I and which is Q (LC/caribou_smi/caribou_smi.c:342-379). */
+typedef enum { CARIBOU_CUDA_CH_S1G = 0, CARIBOU_CUDA_CH_HIF = 1 } caribou_cuda_channel;
+
+typedef enum { CARIBOU_CUDA_MEM_DEVICE = 0,        /* pointers are device memory */
+               CARIBOU_CUDA_MEM_HOST_PINNED = 1,   /* page-locked host memory: async copies */
+               CARIBOU_CUDA_MEM_HOST = 2           /* pageable host memory: staged, synchronous */
+} caribou_cuda_mem;
+
+/* Sample formats of SoapyCariboulite's setupStream (LC/soapy_api/CaribouliteStreamFunctions.cpp:11-19). */
+typedef enum { CARIBOU_CUDA_FMT_CF32 = 0, CARIBOU_CUDA_FMT_CS16 = 1,
+               CARIBOU_CUDA_FMT_CS8 = 2,  CARIBOU_CUDA_FMT_CF64 = 3 } caribou_cuda_format;
+
+/* Where the int16 truncation sits relative to the filter.
+ * Q16: reference ordering, LC/soapy_api/CaribouliteStream.cpp:291-298 then :315-321:
+ *      y = (int16)(float)cascade((float)x_int16); out = y / 4096.
+ * F32: CS16 -> CF32 first, cascade on the float, no integer truncation:
+ *      out = (float)cascade((float)x_int16 / 4096). */
+typedef enum { CARIBOU_CUDA_PARITY_Q16 = 0, CARIBOU_CUDA_PARITY_F32 = 1 } caribou_cuda_parity;
+
+/* Input element type of caribou_cuda_filter_submit / rx path. */
+typedef enum { CARIBOU_CUDA_IN_WORDS = 0,   /* raw 32-bit SMI words (fused unpack) */
+               CARIBOU_CUDA_IN_CS16 = 1,    /* packed (int16 i, int16 q)           */
+               CARIBOU_CUDA_IN_CF32 = 2     /* packed (float i, float q)            */
+} caribou_cuda_input;
+
+typedef struct caribou_cuda_ctx caribou_cuda_ctx;
+
+typedef struct {
+    int      device;                  /* CUDA device ordinal */
+    int      channel;                 /* caribou_cuda_channel (single-channel captures) */
+    uint32_t interleave_block_words;  /* 0: single channel.  B > 0: dual-channel capture, word k belongs to
+                                         S1G if (k / B) % 2 == 0 else HiF */
+    size_t   chunk_bytes;             /* read(2) granularity = caribou_smi_st.native_batch_len; 0 -> 524288.
+                                         Must be a multiple of 16. */
+    int      n_streams;               /* independent captures per submit (equal length); 0 -> 1 */
+    /* digital filter: cascade of n_sos biquads, rows (b0,b1,b2,a0,a1,a2) as Iir::Custom::SOSCascade
+     * takes them (LC/iir/iir/Custom.h:90-112).  n_sos == 0: no filter. */
+    int      n_sos;
+    double   sos[CARIBOU_CUDA_MAX_SOS][6];
+    int      decimation;              /* keep every D-th filtered sample (phase 0); 0 -> 1.  D in {1,2,4,8,16,32} */
+    int      parity;                  /* caribou_cuda_parity */
+    int      out_format;              /* caribou_cuda_format of the filtered output */
+    void*    cuda_stream;             /* cudaStream_t to run on; NULL -> the library creates one */
+} caribou_cuda_config;
+
+/* Output buffers of the unpack stage.  Any pointer may be NULL (= not wanted), as in
+ * LC/caribou_smi/caribou_smi.c:348-349.  Slots the reference leaves unwritten (tail of a
+ * misaligned chunk, everything from the first un-alignable chunk on) are left untouched.
+ * In dual-channel mode the *_b members receive the HiF sub-stream and the plain members
+ * the S1G sub-stream; each sub-stream is chunked on its own. */
+typedef struct {
+    void*     cs16;          /* [n] (int16 i, int16 q): caribou_smi_sample_complex_int16 */
+    void*     meta;          /* [n] uint8 sync bit:     caribou_smi_sample_meta          */
+    void*     cf32;          /* [n] (float i, float q) = cs16 / 4096 (LC/CaribouLiteRadioCpp.cpp:91) */
+    void*     cs16_b;
+    void*     meta_b;
+    void*     cf32_b;
+    uint32_t* invalid_idx;   /* ascending indices of words failing (w & 0xC001C000) == 0x80004000 */
+    size_t    invalid_cap;
+    uint32_t* sync_idx;      /* ascending indices of words with S == 1 */
+    size_t    sync_cap;
+} caribou_cuda_unpack_out;
+
+typedef struct {
+    int64_t  n_samples;      /* samples delivered (per sub-stream in dual-channel mode: S1G) */
+    int64_t  n_samples_b;    /* HiF sub-stream */
+    int64_t  n_filtered;     /* filtered/decimated samples written per stream */
+    uint64_t n_invalid;      /* exact, even when the index list is capped */
+    uint64_t n_sync;
+    int32_t  first_bad_chunk;    /* first chunk with no alignment, -1 if none */
+    int32_t  n_misaligned_chunks;/* chunks with offs > 0 */
+} caribou_cuda_result;
+
+/* ---------------------------------------------------------------- lifecycle */
+/* Replaces caribou_smi_init's buffer/stream set-up (LC/caribou_smi/caribou_smi.c:513-581) and the
+ * filter objects of SoapySDR::Stream (LC/soapy_api/CaribouliteStream.cpp:51-97). */
+caribou_cuda_ctx* caribou_cuda_create(const caribou_cuda_config* cfg);
+void        caribou_cuda_destroy(caribou_cuda_ctx* ctx);
+const char* caribou_cuda_last_error(void);                 /* thread-local message of the last failure */
+void*       caribou_cuda_get_stream(caribou_cuda_ctx* ctx); /* cudaStream_t the context launches on */
+/* Block until everything submitted on the context has finished; fills *res (may be NULL) with the
+ * counters of the last submit.  Returns the last submit's sample count or error code. */
+int64_t     caribou_cuda_wait(caribou_cuda_ctx* ctx, caribou_cuda_result* res);
+/* Number of kernels this context has launched so far (bench.py's gpu_launches). */
+uint64_t    caribou_cuda_launch_count(const caribou_cuda_ctx* ctx);
+
+/* page-locked host buffers for CARIBOU_CUDA_MEM_HOST_PINNED */
+void* caribou_cuda_host_alloc(size_t nbytes);
+void  caribou_cuda_host_free(void* p);
+
+/* ---------------------------------------------------------------- kernel (a): unpack
+ * caribou_smi_rx_data_analyze + caribou_smi_find_buffer_offset for every chunk of the byte
+ * stream (LC/caribou_smi/caribou_smi.c:235-393) driven like caribou_smi_read's loop (:632-682),
+ * with the byte stream handed over in one piece instead of read(2) by read(2).
+ * `bytes` holds nbytes of raw SMI data per stream (streams `stream_stride_bytes` apart).
+ * Asynchronous for DEVICE / HOST_PINNED memory; call caribou_cuda_wait for the result. */
+int caribou_cuda_unpack_submit(caribou_cuda_ctx* ctx, const void* bytes, size_t nbytes,
+                               size_t stream_stride_bytes, int mem,
+                               const caribou_cuda_unpack_out* out);
+
+/* ---------------------------------------------------------------- kernel (b): IIR + decimate
+ * SoapySDR::Stream::ReadSamples' filter loop and format conversion
+ * (LC/soapy_api/CaribouliteStream.cpp:282-367) on `n_samples` per stream, as a block-parallel
+ * scan; persistent per-stream filter state like the never-reset filter objects of the Stream.
+ * in_kind = WORDS fuses kernel (a)'s decode (aligned chunks only: offs == 0 everywhere; use
+ * caribou_cuda_rx_submit for arbitrary input).  With decimation D, n_samples must be a
+ * multiple of D.  out receives n_samples / D elements of cfg.out_format per stream
+ * (streams `out_stride_elems` elements apart). */
+int caribou_cuda_filter_submit(caribou_cuda_ctx* ctx, int in_kind, const void* in, size_t n_samples,
+                               size_t in_stride_elems, int mem, void* out, size_t out_stride_elems);
+
+/* ---------------------------------------------------------------- fused path
+ * raw SMI bytes -> filtered, decimated output (the north-star path): alignment search, then the
+ * fused unpack+IIR kernel when every chunk is aligned, else unpack -> CS16 scratch -> IIR.
+ * `unpack_out` may be NULL (filtered output only). */
+int caribou_cuda_rx_submit(caribou_cuda_ctx* ctx, const void* bytes, size_t nbytes,
+                           size_t stream_stride_bytes, int mem,
+                           const caribou_cuda_unpack_out* unpack_out,
+                           void* filt_out, size_t filt_stride_elems);
+
+/* ---------------------------------------------------------------- filter state
+ * The reference's only persistent state: DirectFormII (v1, v2) per biquad per rail
+ * (LC/iir/iir/State.h:102-131).  Layout per stream: [rail I: v1_0,v2_0,v1_1,v2_1,...][rail Q: ...],
+ * 4 * n_sos doubles.  These calls synchronise the context. */
+int caribou_cuda_get_state(caribou_cuda_ctx* ctx, int stream, double* state);
+int caribou_cuda_set_state(caribou_cuda_ctx* ctx, int stream, const double* state);
+int caribou_cuda_reset(caribou_cuda_ctx* ctx);   /* zero state, decimation phase and sample position */
+
+/* Multi-GPU time sharding: a shard is filtered from zero state; its end state f
+ * (caribou_cuda_get_state) travels to the next rank; the receiving rank then re-runs the first
+ * few tiles of its shard from the true incoming state with caribou_cuda_filter_fixup.
+ * caribou_cuda_shard_matrix returns A^n_samples (row-major, (2*n_sos)^2 doubles, reference
+ * state coordinates) so that s_end = M * s_in + f.  caribou_cuda_fixup_samples returns how many
+ * leading samples a non-zero incoming state can influence above 2^-60 (bounded by n_samples). */
+int    caribou_cuda_shard_matrix(caribou_cuda_ctx* ctx, uint64_t n_samples, double* m);
+size_t caribou_cuda_fixup_samples(caribou_cuda_ctx* ctx, size_t n_samples);
+int    caribou_cuda_filter_fixup(caribou_cuda_ctx* ctx, int in_kind, const void* in, size_t n_samples,
+                                 size_t in_stride_elems, int mem, void* out, size_t out_stride_elems,
+                                 const double* state_in /* 4*n_sos doubles per stream, host */);
+
+/* ---------------------------------------------------------------- host-side filter design
+ * Iir::Butterworth::LowPass<order>::setup(fs, fc) (LC/iir/iir/Butterworth.cpp:49-68,107-117,
+ * PoleFilter.cpp:47-90, Cascade.cpp:94-118).  Writes (order+1)/2 rows of (b0,b1,b2,a0,a1,a2);
+ * returns the row count or -1. */
+int caribou_cuda_butter_lowpass(int order, double fs, double fc, double* sos);
+
+/* ---------------------------------------------------------------- synthetic input (bench/test utility)
+ * Device-side generator of the deterministic SMI word pattern of SURVEY 8(d); bit-identical to
+ * oracle/oracle.c::orc_gen_words given the same 800-entry tone tables. */
+int caribou_cuda_synth_words(caribou_cuda_ctx* ctx, void* dev_words, uint64_t n0, size_t n,
+                             int hif_layout, uint64_t seed,
+                             const int16_t* tone_i_host, const int16_t* tone_q_host);
+
+/* ---------------------------------------------------------------- drop-in shims
+ * Same signatures and struct layouts as the reference, fed from a file descriptor
+ * (/dev/smi, a capture file or a memfd).  See INTEGRATION.md. */
+#pragma pack(push, 1)
+typedef struct { int16_t i; int16_t q; } caribou_cuda_sample_complex_int16;   /* caribou_smi.h:53-59 */
+typedef struct { uint8_t sync; } caribou_cuda_sample_meta;                      /* caribou_smi.h:61-64 */
+#pragma pack(pop)
+
+typedef struct caribou_cuda_smi caribou_cuda_smi;   /* stands in for caribou_smi_st */
+caribou_cuda_smi* caribou_cuda_smi_open(int fd, size_t native_batch_len, int device);
+void              caribou_cuda_smi_close(caribou_cuda_smi* dev);
+/* int caribou_smi_read(caribou_smi_st*, caribou_smi_channel_en, caribou_smi_sample_complex_int16*,
+ *                      caribou_smi_sample_meta*, size_t)            LC/caribou_smi/caribou_smi.h:96-97 */
+int caribou_cuda_smi_read(caribou_cuda_smi* dev, int channel,
+                          caribou_cuda_sample_complex_int16* buffer,
+                          caribou_cuda_sample_meta* metadata, size_t length_samples);
+/* size_t caribou_smi_get_native_batch_samples(caribou_smi_st*)     LC/caribou_smi/caribou_smi.c:765-769 */
+size_t caribou_cuda_smi_get_native_batch_samples(caribou_cuda_smi* dev);
+
+/* SoapySDR::Stream's RX half (LC/soapy_api/CaribouliteStream.hpp:64-137): format switch, MTU clamp,
+ * three never-reset order-6 Butterworth filter pairs, Q16 ordering. */
+typedef struct caribou_cuda_rxstream caribou_cuda_rxstream;
+caribou_cuda_rxstream* caribou_cuda_rxstream_create(caribou_cuda_smi* dev, int channel);
+void   caribou_cuda_rxstream_destroy(caribou_cuda_rxstream* s);
+int    caribou_cuda_rxstream_set_format(caribou_cuda_rxstream* s, const char* fmt);  /* Stream::setFormat */
+void   caribou_cuda_rxstream_set_filter(caribou_cuda_rxstream* s, int type);         /* Stream::setDigitalFilter: 0 none,1 20k,2 50k,3 100k */
+size_t caribou_cuda_rxstream_mtu(caribou_cuda_rxstream* s);                          /* Stream::getMTUSizeElements */
+int    caribou_cuda_rxstream_read(caribou_cuda_rxstream* s, void* buffer, size_t num_elements,
+                                  long timeout_us);                                  /* Stream::ReadSamplesGen */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CARIBOU_CUDA_H */
