@@ -4,6 +4,7 @@
 #include <string.h>
 #include <algorithm>
 #include <new>
+#include <vector>
 #include "ctx.h"
 
 namespace cbl {
@@ -106,6 +107,26 @@ static void state_to_ref(const FilterPlan& P, const double* ker, double* ref)
         for (int i = 0; i < P.S; i++) ref[r * P.S + i] = (double)((long double)ker[r * P.S + i] * (long double)P.g[i / 2]);
 }
 
+static double scale_of(const caribou_cuda_ctx* c, int in_kind)
+{
+    return (c->cfg.parity == CARIBOU_CUDA_PARITY_F32 && in_kind != IN_CF32) ? 1.0 / 4096.0 : 1.0;
+}
+// The kernels filter the raw sample values and fold the input scale into the output gain (exact: a power
+// of two).  If the input kind of a stream changes mid-life, its state is rescaled to the new raw units.
+static int ensure_scale(caribou_cuda_ctx* c, int in_kind)
+{
+    const double sc = scale_of(c, in_kind);
+    if (sc == c->in_scale) return CARIBOU_CUDA_OK;
+    const size_t n = (size_t)c->cfg.n_streams * 2 * c->plan.S;
+    std::vector<double> st(n);
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
+    CBL_CHECK(cudaMemcpy(st.data(), c->d_state, n * 8, cudaMemcpyDeviceToHost));
+    for (double& v : st) v *= c->in_scale / sc;
+    CBL_CHECK(cudaMemcpy(c->d_state, st.data(), n * 8, cudaMemcpyHostToDevice));
+    c->in_scale = sc;
+    return CARIBOU_CUDA_OK;
+}
+
 // ------------------------------------------------------------------ the IIR launch sequence
 // Filters n samples per stream that sit in device memory.  `state_in_dev` is the state each stream starts
 // from (kernel coordinates); when commit is set the end state is written back to ctx->d_state.
@@ -119,9 +140,7 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
     const uint64_t n_runs = n / LT;
     const uint64_t n_main = n_runs * LT;
     IirTables T = P.tables;
-    double scale = 1.0;
-    if (c->cfg.parity == CARIBOU_CUDA_PARITY_F32 && in_kind != IN_CF32) scale = 1.0 / 4096.0;   // x / 4096 first (exact)
-    T.gain = P.g[P.K] * scale;
+    T.gain = P.g[P.K] * scale_of(c, in_kind);   // x / 4096 first == y / 4096 last (exact)
     const int layout = c->cfg.channel == CARIBOU_CUDA_CH_HIF ? 1 : 0;
     const size_t es = in_elem_bytes(in_kind);
 
@@ -529,6 +548,7 @@ int caribou_cuda_filter_submit(caribou_cuda_ctx* c, int in_kind, const void* in,
     if (!c || (!in && n) || (!out && n) || in_kind < 0 || in_kind > 2) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
     CBL_CHECK(cudaSetDevice(c->device));
     if (check_filter_args(c, n) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (ensure_scale(c, in_kind) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     const size_t ns = (size_t)c->cfg.n_streams;
     const size_t es = in_elem_bytes(in_kind);
     const size_t nout = n / c->plan.D;
@@ -560,6 +580,7 @@ int caribou_cuda_filter_fixup(caribou_cuda_ctx* c, int in_kind, const void* in, 
     if (mem != CARIBOU_CUDA_MEM_DEVICE) { set_error("fix-up works on device memory"); return CARIBOU_CUDA_ERR; }
     CBL_CHECK(cudaSetDevice(c->device));
     if (check_filter_args(c, n) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (ensure_scale(c, in_kind) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     const FilterPlan& P = c->plan;
     const size_t ns = (size_t)c->cfg.n_streams;
     if (ns == 1) { in_stride = (n + 3) & ~size_t(3); out_stride = n / P.D; }
@@ -568,6 +589,7 @@ int caribou_cuda_filter_fixup(caribou_cuda_ctx* c, int in_kind, const void* in, 
     CBL_CHECK(cudaStreamSynchronize(c->stream));
     CBL_CHECK(cudaMemcpy(f.data(), c->d_state, f.size() * 8, cudaMemcpyDeviceToHost));
     for (size_t s = 0; s < ns; s++) state_to_kernel(P, state_in + s * 2 * P.S, ker.data() + s * 2 * P.S);
+    for (double& v : ker) v /= c->in_scale;
     // A^n in kernel coordinates
     {
         std::vector<double> mref((size_t)P.S * P.S);
@@ -628,6 +650,7 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
     if (!c->has_filter || !filt_out) { set_error("rx_submit needs a filter and an output buffer; use unpack_submit otherwise"); return CARIBOU_CUDA_ERR; }
     const size_t n = nbytes / 4;
     if (check_filter_args(c, n) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (ensure_scale(c, IN_WORDS) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     const FilterPlan& P = c->plan;
     const size_t ns = (size_t)c->cfg.n_streams;
     const size_t nout = n / P.D;
@@ -766,6 +789,7 @@ int caribou_cuda_get_state(caribou_cuda_ctx* c, int stream, double* state)
     double ker[2 * kMaxS];
     CBL_CHECK(cudaMemcpy(ker, c->d_state + (size_t)stream * 2 * P.S, (size_t)2 * P.S * 8, cudaMemcpyDeviceToHost));
     state_to_ref(P, ker, state);
+    for (int i = 0; i < 2 * P.S; i++) state[i] *= c->in_scale;
     return CARIBOU_CUDA_OK;
 }
 
@@ -776,6 +800,7 @@ int caribou_cuda_set_state(caribou_cuda_ctx* c, int stream, const double* state)
     const FilterPlan& P = c->plan;
     double ker[2 * kMaxS];
     state_to_kernel(P, state, ker);
+    for (int i = 0; i < 2 * P.S; i++) ker[i] /= c->in_scale;
     CBL_CHECK(cudaMemcpy(c->d_state + (size_t)stream * 2 * P.S, ker, (size_t)2 * P.S * 8, cudaMemcpyHostToDevice));
     return CARIBOU_CUDA_OK;
 }

@@ -63,6 +63,8 @@ struct caribou_cuda_ctx {
     double* d_state = nullptr;        // [n_streams][2S] kernel coordinates
     double* d_state_next = nullptr;
     uint64_t pos = 0;                 // samples consumed per stream since create/reset
+    double in_scale = 1.0;            // notional filter input = raw sample value * in_scale (1/4096 for integer
+                                      // input under F32 parity); the state API speaks in notional units
     cbl::DevBuf desc_agg, desc_incl, desc_flag;
     uint32_t* d_ticket = nullptr;     // [4] tickets (iir, unpack, spare)
 

@@ -1,0 +1,173 @@
+"""Parity of kernel (b) (IIR block scan + fused decimation) and of the fused rx path with the CPU
+oracle.  Tolerance (BASELINE.json north_star): rms(gpu - ref) / rms(ref) <= 1e-5 per rail for the
+filtered CF32 output.  Runs through the C ABI."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5          # relative to signal RMS, per rail (north_star)
+FILTERS = {         # name -> (order, fs, fc)
+    "ref20k": (6, 4e6, 10e3), "ref50k": (6, 4e6, 25e3), "ref100k": (6, 4e6, 50e3),
+    "c3": (4, 4e6, 250e3), "o2": (2, 4e6, 100e3), "o8": (8, 4e6, 400e3),
+}
+
+
+def rel_rms(a, b):
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    return np.sqrt(np.mean((a - b) ** 2, axis=0)) / np.sqrt(np.mean(b ** 2, axis=0))
+
+
+def _dev(torch, a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to("cuda:0")
+
+
+def _words_to_cs16(po, w, channel=0):
+    _, cs16, _, _ = po.smi_read(w.view(np.uint8), w.size, channel)
+    return cs16[: w.size]
+
+
+@pytest.mark.parametrize("name,D", [("c3", 8), ("c3", 1), ("ref20k", 8), ("ref50k", 16), ("ref100k", 32),
+                                    ("o2", 2), ("o8", 4), ("ref20k", 1)])
+def test_fused_words_f32(cb, po, torch_cuda, name, D):
+    """raw SMI words -> filtered, decimated CF32 (north-star ordering) vs oracle filter<float>(x/4096)[::D]."""
+    torch = torch_cuda
+    n = 1 << 19
+    sos = po.butter_lowpass_sos(*FILTERS[name])
+    w = po.gen_words(n)
+    ref = po.filter_cf32_f32(sos, po.cs16_to_cf32(_words_to_cs16(po, w)))[::D]
+    d_w = _dev(torch, w.view(np.int32))
+    out = torch.zeros((n // D, 2), dtype=torch.float32, device="cuda:0")
+    with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32, out_format=cb.FMT_CF32) as ctx:
+        ctx.filter_submit(cb.IN_WORDS, d_w, n, out)
+        ret, res = ctx.wait()
+        assert ret == n and res.n_filtered == n // D
+    err = rel_rms(out.cpu().numpy(), ref)
+    assert np.all(err <= TOL), err
+
+
+@pytest.mark.parametrize("name", ["ref20k", "c3"])
+def test_cf32_input(cb, po, torch_cuda, name):
+    """C3 shape: CF32 stream in, filtered + decimate-by-8 CF32 out."""
+    torch = torch_cuda
+    n, D = 1 << 19, 8
+    sos = po.butter_lowpass_sos(*FILTERS[name])
+    x = po.cs16_to_cf32(_words_to_cs16(po, po.gen_words(n)))
+    ref = po.filter_cf32_f32(sos, x)[::D]
+    out = torch.zeros((n // D, 2), dtype=torch.float32, device="cuda:0")
+    with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32) as ctx:
+        ctx.filter_submit(cb.IN_CF32, _dev(torch, x), n, out)
+        ctx.wait()
+    err = rel_rms(out.cpu().numpy(), ref)
+    assert np.all(err <= TOL), err
+
+
+@pytest.mark.parametrize("fmt", ["CS16", "CF32", "CF64", "CS8"])
+def test_q16_reference_ordering(cb, po, torch_cuda, fmt):
+    """Reference ordering (int16 truncation after the filter, CaribouliteStream.cpp:291-298)."""
+    torch = torch_cuda
+    n = 1 << 18
+    sos = po.butter_lowpass_sos(6, 4e6, 25e3)
+    cs16 = _words_to_cs16(po, po.gen_words(n))
+    q = po.filter_cs16_q16(sos, cs16)
+    code = {"CS16": cb.FMT_CS16, "CF32": cb.FMT_CF32, "CF64": cb.FMT_CF64, "CS8": cb.FMT_CS8}[fmt]
+    ref = {"CS16": q, "CF32": po.cs16_to_cf32(q), "CF64": po.cs16_to_cf64(q), "CS8": po.cs16_to_cs8(q)}[fmt]
+    out = torch.zeros((n, 2), dtype=getattr(torch, np.dtype(cb.FMT_DTYPE[code]).name), device="cuda:0")
+    with cb.Context(sos=sos, decimation=1, parity=cb.PARITY_Q16, out_format=code) as ctx:
+        ctx.filter_submit(cb.IN_CS16, _dev(torch, cs16), n, out)
+        ctx.wait()
+    got = out.cpu().numpy()
+    # post-filter integers are tolerance-checked (an LSB may flip when y is within ~1e-10 of an integer)
+    diff = np.abs(got.astype(np.float64) - ref.astype(np.float64))
+    lsb = {"CS16": 1, "CF32": 1 / 4096, "CF64": 1 / 4096, "CS8": 1}[fmt]
+    assert diff.max() <= lsb * 1.0001
+    assert np.mean(diff > 0) < 1e-4
+    assert np.all(rel_rms(got, ref) <= TOL)
+
+
+def test_state_carries_across_calls_and_matches_reference(cb, po, torch_cuda):
+    """Chunking never changes results; get_state returns the reference's DF-II (v1,v2) values."""
+    torch = torch_cuda
+    n, D = 1 << 18, 8
+    sos = po.butter_lowpass_sos(6, 4e6, 10e3)
+    w = po.gen_words(n)
+    x = po.cs16_to_cf32(_words_to_cs16(po, w))
+    ci, cq = po.Cascade(sos), po.Cascade(sos)
+    ref = po.filter_cf32_f32(sos, x, ci, cq)[::D]
+    d_w = _dev(torch, w.view(np.int32))
+    out = torch.zeros((n // D, 2), dtype=torch.float32, device="cuda:0")
+    cuts = [0, 4096, 4096 + 1000 * 8, 100000, 100000 + 8 * 77, n]      # odd lengths: tail kernel + partial tiles
+    with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32) as ctx:
+        for a, b in zip(cuts[:-1], cuts[1:]):
+            ctx.filter_submit(cb.IN_WORDS, d_w[a:b], b - a, out[a // D: b // D])
+        ctx.wait()
+        st = ctx.get_state()
+        assert np.all(rel_rms(out.cpu().numpy(), ref) <= TOL)
+        ref_state = np.concatenate([ci.state, cq.state])
+        np.testing.assert_allclose(st, ref_state, rtol=1e-9, atol=0)
+        # set_state round trip
+        ctx.set_state(st * 0.5)
+        np.testing.assert_allclose(ctx.get_state(), st * 0.5, rtol=1e-15)
+
+
+def test_batch_of_streams(cb, po, torch_cuda):
+    """C4 shape in small: independent captures, one launch, no state leaks between them."""
+    torch = torch_cuda
+    ns, n, D = 5, 3 * 4096 + 640, 8
+    sos = po.butter_lowpass_sos(4, 4e6, 250e3)
+    ws = [po.gen_words(n, seed=s) for s in range(ns)]
+    d_w = _dev(torch, np.stack(ws).view(np.int32))
+    out = torch.zeros((ns, n // D, 2), dtype=torch.float32, device="cuda:0")
+    with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32, n_streams=ns) as ctx:
+        ctx.rx_submit(d_w, n * 4, out, stride_bytes=n * 4, filt_stride=n // D)
+        ret, res = ctx.wait()
+        assert ret == n
+        states = [ctx.get_state(s) for s in range(ns)]
+    for s in range(ns):
+        ci, cq = po.Cascade(sos), po.Cascade(sos)
+        ref = po.filter_cf32_f32(sos, po.cs16_to_cf32(_words_to_cs16(po, ws[s])), ci, cq)[::D]
+        assert np.all(rel_rms(out[s].cpu().numpy(), ref) <= TOL)
+        np.testing.assert_allclose(states[s], np.concatenate([ci.state, cq.state]), rtol=1e-9)
+
+
+def test_rx_misaligned_falls_back(cb, po, torch_cuda):
+    """A capture with a misaligned chunk takes the unpack -> CS16 -> IIR route; oracle = the reference's
+    read into a zeroed buffer, then the filter."""
+    torch = torch_cuda
+    n, D = 1 << 16, 8
+    sos = po.butter_lowpass_sos(4, 4e6, 250e3)
+    w = po.gen_words(n)
+    w[16384] ^= 0x80000000                    # chunk 1 (65536-byte chunks) starts with a bad header
+    _, cs16, _, _ = po.smi_read(w.view(np.uint8), n, 0, 65536)
+    ref = po.filter_cf32_f32(sos, po.cs16_to_cf32(cs16[:n]))[::D]
+    out = torch.zeros((n // D, 2), dtype=torch.float32, device="cuda:0")
+    with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32, chunk_bytes=65536) as ctx:
+        ctx.rx_submit(_dev(torch, w.view(np.int32)), n * 4, out)
+        ret, res = ctx.wait()
+    assert ret == n and res.n_misaligned_chunks == 1
+    assert np.all(rel_rms(out.cpu().numpy(), ref) <= TOL)
+
+
+def test_shard_handoff_matches_single_stream(cb, po, torch_cuda):
+    """Time-chunk sharding (C5 in small, ranks emulated one after the other on one GPU): every shard is
+    filtered from zero state, end states are chained with the shard matrix, leading tiles are re-run."""
+    torch = torch_cuda
+    n, D, G = 1 << 19, 8, 4
+    sos = po.butter_lowpass_sos(6, 4e6, 10e3)
+    w = po.gen_words(n)
+    ref = po.filter_cf32_f32(sos, po.cs16_to_cf32(_words_to_cs16(po, w)))[::D]
+    d_w = _dev(torch, w.view(np.int32))
+    out = torch.zeros((n // D, 2), dtype=torch.float32, device="cuda:0")
+    sh = n // G
+    s_in = np.zeros(12)
+    for g in range(G):
+        with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32) as ctx:
+            xs, os_ = d_w[g * sh:(g + 1) * sh], out[g * sh // D:(g + 1) * sh // D]
+            ctx.filter_submit(cb.IN_WORDS, xs, sh, os_)
+            ctx.wait()
+            assert ctx.fixup_samples(sh) < sh
+            if g > 0:
+                ctx.filter_fixup(cb.IN_WORDS, xs, sh, os_, s_in)
+            s_in = ctx.get_state()          # = M_shard s_in + f
+    assert np.all(rel_rms(out.cpu().numpy(), ref) <= TOL)
