@@ -12,7 +12,8 @@ import numpy as np
 from . import build as _build
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libcaribou_cuda.so")
+# CARIBOU_CUDA_LIB: an alternative build of the same library (kernel tuning experiments); never a fallback
+LIB_PATH = os.environ.get("CARIBOU_CUDA_LIB") or os.path.join(HERE, "libcaribou_cuda.so")
 HEADER_PATH = os.path.join(HERE, "..", "include", "caribou_cuda.h")
 
 OK, ERR, ERR_DEBUG, ERR_SYNC = 0, -1, -2, -3
@@ -20,6 +21,7 @@ CH_S1G, CH_HIF = 0, 1
 MEM_DEVICE, MEM_HOST_PINNED, MEM_HOST = 0, 1, 2
 FMT_CF32, FMT_CS16, FMT_CS8, FMT_CF64 = 0, 1, 2, 3
 PARITY_Q16, PARITY_F32 = 0, 1
+FORM_AUTO, FORM_CASCADE, FORM_PARALLEL = 0, 1, 2
 IN_WORDS, IN_CS16, IN_CF32 = 0, 1, 2
 NATIVE_BATCH_LEN = 524288
 MAX_SOS = 4
@@ -36,7 +38,13 @@ class Config(C.Structure):
     _fields_ = [("device", C.c_int), ("channel", C.c_int), ("interleave_block_words", C.c_uint32),
                 ("chunk_bytes", C.c_size_t), ("n_streams", C.c_int), ("n_sos", C.c_int),
                 ("sos", (C.c_double * 6) * MAX_SOS), ("decimation", C.c_int), ("parity", C.c_int),
-                ("out_format", C.c_int), ("cuda_stream", C.c_void_p)]
+                ("out_format", C.c_int), ("cuda_stream", C.c_void_p), ("kernel_form", C.c_int)]
+
+
+class FilterInfo(C.Structure):
+    _fields_ = [("n_sos", C.c_int), ("decimation", C.c_int), ("form", C.c_int), ("run_len", C.c_int),
+                ("tile_samples", C.c_int), ("lookback_window", C.c_int), ("chained", C.c_int),
+                ("decay_samples", C.c_uint64), ("parallel_form_error", C.c_double), ("note", C.c_char * 96)]
 
 
 class UnpackOut(C.Structure):
@@ -72,6 +80,8 @@ def lib():
         "caribou_cuda_get_stream": (vp, [vp]),
         "caribou_cuda_wait": (i64, [vp, C.POINTER(Result)]),
         "caribou_cuda_launch_count": (u64, [vp]),
+        "caribou_cuda_set_profiling": (i, [vp, i]),
+        "caribou_cuda_read_profile": (i, [vp, vp, i]),
         "caribou_cuda_host_alloc": (vp, [sz]),
         "caribou_cuda_host_free": (None, [vp]),
         "caribou_cuda_unpack_submit": (i, [vp, vp, sz, sz, i, C.POINTER(UnpackOut)]),
@@ -80,6 +90,7 @@ def lib():
         "caribou_cuda_get_state": (i, [vp, i, vp]),
         "caribou_cuda_set_state": (i, [vp, i, vp]),
         "caribou_cuda_reset": (i, [vp]),
+        "caribou_cuda_filter_info": (i, [vp, C.POINTER(FilterInfo)]),
         "caribou_cuda_shard_matrix": (i, [vp, u64, vp]),
         "caribou_cuda_fixup_samples": (sz, [vp, sz]),
         "caribou_cuda_filter_fixup": (i, [vp, i, vp, sz, sz, i, vp, sz, vp]),
@@ -106,9 +117,11 @@ def lib():
 
 EXPORTED_SYMBOLS = [
     "caribou_cuda_create", "caribou_cuda_destroy", "caribou_cuda_last_error", "caribou_cuda_get_stream",
-    "caribou_cuda_wait", "caribou_cuda_launch_count", "caribou_cuda_host_alloc", "caribou_cuda_host_free",
+    "caribou_cuda_wait", "caribou_cuda_launch_count", "caribou_cuda_set_profiling",
+    "caribou_cuda_read_profile", "caribou_cuda_host_alloc", "caribou_cuda_host_free",
     "caribou_cuda_unpack_submit", "caribou_cuda_filter_submit", "caribou_cuda_rx_submit",
-    "caribou_cuda_get_state", "caribou_cuda_set_state", "caribou_cuda_reset", "caribou_cuda_shard_matrix",
+    "caribou_cuda_get_state", "caribou_cuda_set_state", "caribou_cuda_reset", "caribou_cuda_filter_info",
+    "caribou_cuda_shard_matrix",
     "caribou_cuda_fixup_samples", "caribou_cuda_filter_fixup", "caribou_cuda_butter_lowpass",
     "caribou_cuda_synth_words", "caribou_cuda_smi_open", "caribou_cuda_smi_close", "caribou_cuda_smi_read",
     "caribou_cuda_smi_get_native_batch_samples", "caribou_cuda_rxstream_create",
@@ -155,7 +168,8 @@ class Context:
     """One stream of the RX sample path (or a batch of n_streams equal-length captures)."""
 
     def __init__(self, device=0, channel=CH_S1G, interleave_block_words=0, chunk_bytes=0, n_streams=1,
-                 sos=None, decimation=1, parity=PARITY_Q16, out_format=FMT_CF32, cuda_stream=None):
+                 sos=None, decimation=1, parity=PARITY_Q16, out_format=FMT_CF32, cuda_stream=None,
+                 kernel_form=FORM_AUTO):
         cfg = Config()
         cfg.device = device
         cfg.channel = channel
@@ -166,6 +180,7 @@ class Context:
         cfg.parity = parity
         cfg.out_format = out_format
         cfg.cuda_stream = cuda_stream
+        cfg.kernel_form = kernel_form
         self.n_sos = 0
         if sos is not None:
             sos = np.ascontiguousarray(sos, dtype=np.float64).reshape(-1, 6)
@@ -213,6 +228,15 @@ class Context:
     @property
     def launch_count(self):
         return lib().caribou_cuda_launch_count(self.h)
+
+    def set_profiling(self, enable=True):
+        return self._check(lib().caribou_cuda_set_profiling(self.h, int(enable)))
+
+    def read_profile(self, cap=256):
+        """Device milliseconds of every dominant-kernel launch since the last read (waits for the context)."""
+        ms = np.zeros(cap, dtype=np.float32)
+        k = self._check(lib().caribou_cuda_read_profile(self.h, ms.ctypes.data, cap))
+        return ms[:k].astype(np.float64)
 
     def wait(self):
         r = Result()
@@ -267,6 +291,11 @@ class Context:
 
     def reset(self):
         self._check(lib().caribou_cuda_reset(self.h))
+
+    def filter_info(self):
+        fi = FilterInfo()
+        self._check(lib().caribou_cuda_filter_info(self.h, C.byref(fi)))
+        return fi
 
     def shard_matrix(self, n_samples):
         s = 2 * self.n_sos

@@ -6,8 +6,10 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OBJ = os.path.join(HERE, "_obj")
-LIB = os.path.join(HERE, "libcaribou_cuda.so")
+# CBL_VARIANT=<tag> (+ CBL_NVCC_EXTRA="-D...") builds libcaribou_cuda_<tag>.so beside the product library
+VARIANT = os.environ.get("CBL_VARIANT", "")
+OBJ = os.path.join(HERE, "_obj" + ("_" + VARIANT if VARIANT else ""))
+LIB = os.path.join(HERE, "libcaribou_cuda%s.so" % ("_" + VARIANT if VARIANT else ""))
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 CU = ["unpack.cu", "iir.cu", "iir_k1.cu", "iir_k2.cu", "iir_k3.cu", "iir_k4.cu", "api.cu", "compat.cu"]

@@ -95,16 +95,14 @@ static bool resolve_out_mode(int parity, int fmt, int* mode, size_t* elem)
     return false;
 }
 
-// kernel-coordinate <-> reference-coordinate state conversion (s_ref = g[stage] * s_kernel)
+// kernel-coordinate <-> reference-coordinate state conversion, both rails (tables.cpp: Tkr / Trk)
 static void state_to_kernel(const FilterPlan& P, const double* ref, double* ker)
 {
-    for (int r = 0; r < 2; r++)
-        for (int i = 0; i < P.S; i++) ker[r * P.S + i] = (double)((long double)ref[r * P.S + i] / (long double)P.g[i / 2]);
+    for (int r = 0; r < 2; r++) plan_state_to_kernel(P, ref + r * P.S, ker + r * P.S);
 }
 static void state_to_ref(const FilterPlan& P, const double* ker, double* ref)
 {
-    for (int r = 0; r < 2; r++)
-        for (int i = 0; i < P.S; i++) ref[r * P.S + i] = (double)((long double)ker[r * P.S + i] * (long double)P.g[i / 2]);
+    for (int r = 0; r < 2; r++) plan_state_to_ref(P, ker + r * P.S, ref + r * P.S);
 }
 
 static double scale_of(const caribou_cuda_ctx* c, int in_kind)
@@ -127,6 +125,15 @@ static int ensure_scale(caribou_cuda_ctx* c, int in_kind)
     return CARIBOU_CUDA_OK;
 }
 
+constexpr size_t kProfRing = 256;
+// which = 0: start of the dominant kernel, 1: its end (closes the pair)
+static void prof_mark(caribou_cuda_ctx* c, int which)
+{
+    if (!c->profiling || c->prof_ev.empty()) return;
+    cudaEventRecord(c->prof_ev[2 * (c->prof_n % kProfRing) + which], c->stream);
+    if (which == 1) c->prof_n++;
+}
+
 // ------------------------------------------------------------------ the IIR launch sequence
 // Filters n samples per stream that sit in device memory.  `state_in_dev` is the state each stream starts
 // from (kernel coordinates); when commit is set the end state is written back to ctx->d_state.
@@ -141,6 +148,10 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
     const uint64_t n_main = n_runs * LT;
     IirTables T = P.tables;
     T.gain = P.g[P.K] * scale_of(c, in_kind);   // x / 4096 first == y / 4096 last (exact)
+    // integer inputs of the parallel form enter as x + bias (mantissa injection, iir.cuh)
+    const double bias = !P.par ? 0.0 : (in_kind == IN_WORDS ? kBiasWords : (in_kind == IN_CS16 ? kBiasCs16 : 0.0));
+    for (int i = 0; i < P.S; i++) T.sbias[i] = bias * P.sstar[i];
+    T.out_bias = -bias * P.hn1 * T.gain;
     const int layout = c->cfg.channel == CARIBOU_CUDA_CH_HIF ? 1 : 0;
     const size_t es = in_elem_bytes(in_kind);
 
@@ -150,11 +161,12 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
         if (max_tiles > 0 && tiles_ps > max_tiles) { tiles_ps = max_tiles; whole = false; }
         const uint64_t total = tiles_ps * ns;
         if (total > 0xFFFFFFF0ull) { set_error("too many tiles"); return CARIBOU_CUDA_ERR; }
-        if (!c->desc_agg.reserve(total * 2 * P.S * 8) || !c->desc_incl.reserve(total * 2 * P.S * 8) ||
-            !c->desc_flag.reserve(total * 4)) return CARIBOU_CUDA_ERR;
+        DevBuf& desc = P.chained ? c->desc_incl : c->desc_agg;     // the one the look-back reads
+        if (!desc.reserve(total * 2 * P.S * 8) || !c->desc_incl.reserve(2 * P.S * 8) || !c->desc_agg.reserve(2 * P.S * 8))
+            return CARIBOU_CUDA_ERR;
         CUtensorMap tm;
         if (!make_run_tmap(&tm, d_in, LT, (int)(es / 4), n_runs, ns, (uint64_t)in_stride * es)) return CARIBOU_CUDA_ERR;
-        CBL_CHECK(cudaMemsetAsync(c->desc_flag.p, 0, total * 4, c->stream));
+        CBL_CHECK(cudaMemsetAsync(desc.p, 0xFF, total * 2 * P.S * 8, c->stream));      // kDescEmpty everywhere
         CBL_CHECK(cudaMemsetAsync(c->d_ticket, 0, 4, c->stream));
         IirParams p;
         memset(&p, 0, sizeof(p));
@@ -173,19 +185,20 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
         p.plane = c->d_plane;
         p.desc_agg = c->desc_agg.as<double>();
         p.desc_incl = c->desc_incl.as<double>();
-        p.desc_flag = c->desc_flag.as<uint32_t>();
         p.ticket = c->d_ticket;
         p.state_in = c->d_state;
         p.state_out = c->d_state_next;
         p.out = d_out;
         p.out_stride = out_stride;
         p.gate = gate;
-        static int occ_cache[kMaxK + 1][33][3];
-        int& occ = occ_cache[P.K][P.D][in_kind];
-        if (occ == 0) occ = std::max(1, iir_max_ctas_per_sm(P.K, P.D, in_kind));
+        static int occ_cache[kMaxK + 1][33][3][2];
+        int& occ = occ_cache[P.K][P.D][in_kind][P.par ? 1 : 0];
+        if (occ == 0) occ = std::max(1, iir_max_ctas_per_sm(P.K, P.D, in_kind, P.par));
         const uint64_t want = (total + kIirWarpsPerCta - 1) / kIirWarpsPerCta;
         const int grid = (int)std::min<uint64_t>(want, (uint64_t)occ * c->num_sms);
-        const int e = launch_iir(P.K, P.D, in_kind, tm, p, T, grid, c->stream);
+        prof_mark(c, 0);
+        const int e = launch_iir(P.K, P.D, in_kind, P.par, tm, p, T, grid, c->stream);
+        prof_mark(c, 1);
         if (e != 0) { cuda_ok((cudaError_t)e, "iir_scan_kernel launch"); return CARIBOU_CUDA_ERR; }
         c->launches++;
         if (p.write_state) {
@@ -200,7 +213,7 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
         t.in = d_in; t.in_stride = in_stride;
         t.first = n_main; t.n = n;
         t.out = d_out; t.out_stride = out_stride;
-        t.in_kind = in_kind; t.layout = layout; t.out_mode = c->out_mode; t.K = P.K; t.D = P.D;
+        t.in_kind = in_kind; t.layout = layout; t.out_mode = c->out_mode; t.K = P.K; t.D = P.D; t.par = P.par ? 1 : 0;
         for (int k = 0; k < P.K; k++) { t.a1[k] = T.a1[k]; t.a2[k] = T.a2[k]; t.c1[k] = T.c1[k]; t.c2[k] = T.c2[k]; }
         t.gain = T.gain;
         t.state = c->d_state;
@@ -282,6 +295,8 @@ static int run_unpack(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, s
     if (n_tiles == 0) return CARIBOU_CUDA_OK;
     const bool want_flags = o.invalid_idx || o.sync_idx || true;   // counts are always reported
     if (!c->desc_inv.reserve((size_t)n_tiles * 8) || !c->desc_syn.reserve((size_t)n_tiles * 8)) return CARIBOU_CUDA_ERR;
+    const bool prof = c->profiling && !c->has_filter;
+    if (prof) prof_mark(c, 0);
     for (uint32_t st = 0; st < ns; st++) {
         UnpackParams p;
         memset(&p, 0, sizeof(p));
@@ -325,6 +340,7 @@ static int run_unpack(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, s
         launch_unpack(p, c->stream);
         c->launches++;
     }
+    if (prof) prof_mark(c, 1);
     CBL_CHECK(cudaGetLastError());
     return CARIBOU_CUDA_OK;
 }
@@ -398,7 +414,7 @@ caribou_cuda_ctx* caribou_cuda_create(const caribou_cuda_config* cfg_in)
 
     if (cfg.n_sos > 0) {
         const char* msg = "";
-        if (!make_filter_plan(cfg.n_sos, cfg.sos, cfg.decimation, &c->plan, &msg)) { set_error("%s", msg); return fail(); }
+        if (!make_filter_plan(cfg.n_sos, cfg.sos, cfg.decimation, cfg.kernel_form == CARIBOU_CUDA_FORM_CASCADE, &c->plan, &msg)) { set_error("%s", msg); return fail(); }
         if (!resolve_out_mode(cfg.parity, cfg.out_format, &c->out_mode, &c->out_elem)) { set_error("unsupported parity/out_format combination"); return fail(); }
         const FilterPlan& P = c->plan;
         if (!cuda_ok(cudaMalloc(&c->d_plane, P.plane.size() * 8), "cudaMalloc") ||
@@ -420,7 +436,7 @@ void caribou_cuda_destroy(caribou_cuda_ctx* c)
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    DevBuf* bufs[] = {&c->desc_agg, &c->desc_incl, &c->desc_flag, &c->offs, &c->desc_inv, &c->desc_syn, &c->stage_in,
+    DevBuf* bufs[] = {&c->desc_agg, &c->desc_incl, &c->offs, &c->desc_inv, &c->desc_syn, &c->stage_in,
                       &c->stage_cs16[0], &c->stage_cs16[1], &c->stage_meta[0], &c->stage_meta[1], &c->stage_cf32[0],
                       &c->stage_cf32[1], &c->stage_filt, &c->stage_inv, &c->stage_syn, &c->scratch_cs16};
     for (DevBuf* b : bufs) b->release();
@@ -434,12 +450,43 @@ void caribou_cuda_destroy(caribou_cuda_ctx* c)
     if (c->d_tone) cudaFree(c->d_tone);
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->h_first_bad) cudaFreeHost(c->h_first_bad);
+    for (cudaEvent_t e : c->prof_ev) if (e) cudaEventDestroy(e);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
 
 void* caribou_cuda_get_stream(caribou_cuda_ctx* c) { return c ? (void*)c->stream : nullptr; }
 uint64_t caribou_cuda_launch_count(const caribou_cuda_ctx* c) { return c ? c->launches : 0; }
+
+int caribou_cuda_set_profiling(caribou_cuda_ctx* c, int enable)
+{
+    if (!c) { set_error("null context"); return CARIBOU_CUDA_ERR; }
+    CBL_CHECK(cudaSetDevice(c->device));
+    if (enable && c->prof_ev.empty()) {
+        c->prof_ev.resize(2 * kProfRing, nullptr);
+        for (cudaEvent_t& e : c->prof_ev) CBL_CHECK(cudaEventCreate(&e));
+    }
+    c->profiling = enable != 0;
+    c->prof_n = 0;
+    return CARIBOU_CUDA_OK;
+}
+
+int caribou_cuda_read_profile(caribou_cuda_ctx* c, float* ms, int cap)
+{
+    if (!c || !c->profiling || (!ms && cap > 0)) { set_error("profiling is not enabled"); return CARIBOU_CUDA_ERR; }
+    CBL_CHECK(cudaSetDevice(c->device));
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
+    const uint64_t have = std::min<uint64_t>(c->prof_n, kProfRing);
+    const uint64_t first = c->prof_n - have;
+    int n = 0;
+    for (uint64_t k = first; k < c->prof_n && n < cap; k++, n++) {
+        float t = 0;
+        CBL_CHECK(cudaEventElapsedTime(&t, c->prof_ev[2 * (k % kProfRing)], c->prof_ev[2 * (k % kProfRing) + 1]));
+        ms[n] = t;
+    }
+    c->prof_n = 0;
+    return n;
+}
 
 void* caribou_cuda_host_alloc(size_t nbytes)
 {
@@ -590,14 +637,7 @@ int caribou_cuda_filter_fixup(caribou_cuda_ctx* c, int in_kind, const void* in, 
     CBL_CHECK(cudaMemcpy(f.data(), c->d_state, f.size() * 8, cudaMemcpyDeviceToHost));
     for (size_t s = 0; s < ns; s++) state_to_kernel(P, state_in + s * 2 * P.S, ker.data() + s * 2 * P.S);
     for (double& v : ker) v /= c->in_scale;
-    // A^n in kernel coordinates
-    {
-        std::vector<double> mref((size_t)P.S * P.S);
-        plan_shard_matrix(P, n, mref.data());
-        for (int i = 0; i < P.S; i++)
-            for (int j = 0; j < P.S; j++)
-                m[(size_t)i * P.S + j] = (double)((long double)mref[(size_t)i * P.S + j] * (long double)P.g[j / 2] / (long double)P.g[i / 2]);
-    }
+    plan_power_kernel(P, n, m.data());     // A^n in kernel coordinates
     std::vector<double> end(f);
     for (size_t s = 0; s < ns; s++)
         for (int r = 0; r < 2; r++)
@@ -666,9 +706,12 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
     const void* d_bytes = bytes;
     void* d_out = filt_out;
     if (mem != CARIBOU_CUDA_MEM_DEVICE) {
-        if (ns != 1) { set_error("host-memory rx supports n_streams == 1 (shard captures across contexts)"); return CARIBOU_CUDA_ERR; }
-        if (!c->stage_in.reserve(nbytes + 64) || !c->stage_filt.reserve(nout * c->out_elem + 64)) return CARIBOU_CUDA_ERR;
-        CBL_CHECK(cudaMemcpyAsync(c->stage_in.p, bytes, nbytes, cudaMemcpyHostToDevice, c->stream));
+        if (uo) { set_error("rx_submit with unpack outputs needs device memory"); return CARIBOU_CUDA_ERR; }
+        if (ns > 1 && (stride_bytes < nbytes || filt_stride < nout)) { set_error("stream stride smaller than the stream"); return CARIBOU_CUDA_ERR; }
+        if (!c->stage_in.reserve(ns * stride_bytes + 64) || !c->stage_filt.reserve(ns * filt_stride * c->out_elem + 64)) return CARIBOU_CUDA_ERR;
+        // the batch keeps its host layout (same strides) in the device staging buffers
+        const size_t in_span = (ns - 1) * stride_bytes + nbytes;
+        CBL_CHECK(cudaMemcpyAsync(c->stage_in.p, bytes, in_span, cudaMemcpyHostToDevice, c->stream));
         d_bytes = c->stage_in.p;
         d_out = c->stage_filt.p;
     }
@@ -684,7 +727,7 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
     }
     if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     if (mem != CARIBOU_CUDA_MEM_DEVICE)
-        CBL_CHECK(cudaMemcpyAsync(filt_out, d_out, nout * c->out_elem, cudaMemcpyDeviceToHost, c->stream));
+        CBL_CHECK(cudaMemcpyAsync(filt_out, d_out, ((ns - 1) * filt_stride + nout) * c->out_elem, cudaMemcpyDeviceToHost, c->stream));
     c->pending.active = true;
     c->pending.bytes = bytes; c->pending.nbytes = nbytes; c->pending.stride = stride_bytes; c->pending.mem = mem;
     c->pending.filt_out = filt_out; c->pending.filt_stride = filt_stride;
@@ -729,7 +772,7 @@ static int rx_fallback(caribou_cuda_ctx* c)
         if (run_iir(c, IN_CS16, c->scratch_cs16.p, (size_t)deliver, sstride, q.d_out, q.filt_stride, nullptr, true, 0) != CARIBOU_CUDA_OK)
             return CARIBOU_CUDA_ERR;
         if (q.mem != CARIBOU_CUDA_MEM_DEVICE)
-            CBL_CHECK(cudaMemcpyAsync(q.filt_out, q.d_out, (size_t)deliver / P.D * c->out_elem, cudaMemcpyDeviceToHost, c->stream));
+            CBL_CHECK(cudaMemcpyAsync(q.filt_out, q.d_out, ((ns - 1) * q.filt_stride + (size_t)deliver / P.D) * c->out_elem, cudaMemcpyDeviceToHost, c->stream));
     }
     CBL_CHECK(cudaStreamSynchronize(c->stream));
     c->pos -= n;
@@ -778,6 +821,21 @@ int64_t caribou_cuda_wait(caribou_cuda_ctx* c, caribou_cuda_result* res)
         res->n_misaligned_chunks = c->h_counters->n_misaligned;
     }
     return ret;
+}
+
+int caribou_cuda_filter_info(caribou_cuda_ctx* c, caribou_cuda_filter_info_t* info)
+{
+    if (!c || !info) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    memset(info, 0, sizeof(*info));
+    if (!c->has_filter) return CARIBOU_CUDA_OK;
+    const FilterPlan& P = c->plan;
+    info->n_sos = P.K; info->decimation = P.D; info->run_len = P.LT; info->tile_samples = 32 * P.LT;
+    info->form = P.par ? CARIBOU_CUDA_FORM_PARALLEL : CARIBOU_CUDA_FORM_CASCADE;
+    info->lookback_window = P.window; info->chained = P.chained ? 1 : 0;
+    info->decay_samples = P.decay_samples;
+    info->parallel_form_error = P.par_err;
+    snprintf(info->note, sizeof(info->note), "%s", P.form_note);
+    return CARIBOU_CUDA_OK;
 }
 
 // ------------------------------------------------------------------ state

@@ -52,6 +52,9 @@ struct caribou_cuda_ctx {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     uint64_t launches = 0;
+    bool profiling = false;
+    std::vector<cudaEvent_t> prof_ev;   // ring of (start, stop) pairs around the dominant kernel
+    uint64_t prof_n = 0;                // pairs recorded since the last read
 
     // filter
     bool has_filter = false;

@@ -3,10 +3,10 @@
 
 namespace cbl {
 
-iir_launch_fn iir_launch_k1(int, int); iir_launch_fn iir_launch_k2(int, int);
-iir_launch_fn iir_launch_k3(int, int); iir_launch_fn iir_launch_k4(int, int);
-iir_occ_fn iir_occ_k1(int, int); iir_occ_fn iir_occ_k2(int, int);
-iir_occ_fn iir_occ_k3(int, int); iir_occ_fn iir_occ_k4(int, int);
+iir_launch_fn iir_launch_k1(int, int, bool); iir_launch_fn iir_launch_k2(int, int, bool);
+iir_launch_fn iir_launch_k3(int, int, bool); iir_launch_fn iir_launch_k4(int, int, bool);
+iir_occ_fn iir_occ_k1(int, int, bool); iir_occ_fn iir_occ_k2(int, int, bool);
+iir_occ_fn iir_occ_k3(int, int, bool); iir_occ_fn iir_occ_k4(int, int, bool);
 
 size_t iir_smem_bytes(int K, int D, int in_kind)
 {
@@ -16,28 +16,28 @@ size_t iir_smem_bytes(int K, int D, int in_kind)
     return (size_t)kIirWarpsPerCta * warp_bytes + kIirWarpsPerCta * stages * 8 + 1024;
 }
 
-int launch_iir(int K, int D, int in_kind, const CUtensorMap& tmap, const IirParams& p, const IirTables& t,
+int launch_iir(int K, int D, int in_kind, bool par, const CUtensorMap& tmap, const IirParams& p, const IirTables& t,
                int grid_ctas, cudaStream_t st)
 {
     iir_launch_fn fn = nullptr;
     switch (K) {
-        case 1: fn = iir_launch_k1(D, in_kind); break;
-        case 2: fn = iir_launch_k2(D, in_kind); break;
-        case 3: fn = iir_launch_k3(D, in_kind); break;
-        case 4: fn = iir_launch_k4(D, in_kind); break;
+        case 1: fn = iir_launch_k1(D, in_kind, par); break;
+        case 2: fn = iir_launch_k2(D, in_kind, par); break;
+        case 3: fn = iir_launch_k3(D, in_kind, par); break;
+        case 4: fn = iir_launch_k4(D, in_kind, par); break;
     }
     if (!fn) return (int)cudaErrorInvalidValue;
     return fn(tmap, p, t, grid_ctas, st);
 }
 
-int iir_max_ctas_per_sm(int K, int D, int in_kind)
+int iir_max_ctas_per_sm(int K, int D, int in_kind, bool par)
 {
     iir_occ_fn fn = nullptr;
     switch (K) {
-        case 1: fn = iir_occ_k1(D, in_kind); break;
-        case 2: fn = iir_occ_k2(D, in_kind); break;
-        case 3: fn = iir_occ_k3(D, in_kind); break;
-        case 4: fn = iir_occ_k4(D, in_kind); break;
+        case 1: fn = iir_occ_k1(D, in_kind, par); break;
+        case 2: fn = iir_occ_k2(D, in_kind, par); break;
+        case 3: fn = iir_occ_k3(D, in_kind, par); break;
+        case 4: fn = iir_occ_k4(D, in_kind, par); break;
     }
     return fn ? fn() : 0;
 }
@@ -73,12 +73,21 @@ __global__ void iir_tail_kernel(const __grid_constant__ IirTailParams P)
         }
         double ii = xi, iq = xq;
         for (int k = 0; k < K; k++) {
-            const double ti = fma(-P.a2[k], vi[k][1], ii), wi = fma(-P.a1[k], vi[k][0], ti);
-            const double tq = fma(-P.a2[k], vq[k][1], iq), wq = fma(-P.a1[k], vq[k][0], tq);
-            ii = fma(P.c2[k], vi[k][1], fma(P.c1[k], vi[k][0], wi));
-            iq = fma(P.c2[k], vq[k][1], fma(P.c1[k], vq[k][0], wq));
-            vi[k][1] = vi[k][0]; vi[k][0] = wi;
-            vq[k][1] = vq[k][0]; vq[k][0] = wq;
+            if (P.par) {    // all sections see x; the output taps the state before the update
+                ii = fma(P.c2[k], vi[k][1], fma(P.c1[k], vi[k][0], ii));
+                iq = fma(P.c2[k], vq[k][1], fma(P.c1[k], vq[k][0], iq));
+                const double wi = fma(-P.a1[k], vi[k][0], fma(-P.a2[k], vi[k][1], xi));
+                const double wq = fma(-P.a1[k], vq[k][0], fma(-P.a2[k], vq[k][1], xq));
+                vi[k][1] = vi[k][0]; vi[k][0] = wi;
+                vq[k][1] = vq[k][0]; vq[k][0] = wq;
+            } else {
+                const double ti = fma(-P.a2[k], vi[k][1], ii), wi = fma(-P.a1[k], vi[k][0], ti);
+                const double tq = fma(-P.a2[k], vq[k][1], iq), wq = fma(-P.a1[k], vq[k][0], tq);
+                ii = fma(P.c2[k], vi[k][1], fma(P.c1[k], vi[k][0], wi));
+                iq = fma(P.c2[k], vq[k][1], fma(P.c1[k], vq[k][0], wq));
+                vi[k][1] = vi[k][0]; vi[k][0] = wi;
+                vq[k][1] = vq[k][0]; vq[k][0] = wq;
+            }
         }
         if (n % P.D == 0) {
             const double yi = ii * P.gain, yq = iq * P.gain;

@@ -3,10 +3,23 @@
 //
 // Math (per rail; the two rails I and Q share coefficients, never state):
 //   reference stage k (LC/iir/iir/State.h:116-126):  w = in - a1 v1 - a2 v2 ; out = b0 w + b1 v1 + b2 v2
-//   kernel coordinates: every stage's state is divided by g_k = prod_{j<k} b0_j, so that
-//       w' = in' - a1 v1' - a2 v2' ;  in'_{k+1} = w' + c1 v1' + c2 v2'   (c = b/b0)
-//   and y = G * in'_K with G = prod b0.  One multiply less per inner stage, same transfer function.
-//   The 2K-vector s = (v1'_0, v2'_0, v1'_1, ...) obeys s[n+1] = A s[n] + B x[n]; in'_K[n] = Cu s[n] + x-term.
+//   Two realisations of the same transfer function H(z) = G * prod_k (1 + c1 q + c2 q^2) / (1 + a1 q + a2 q^2),
+//   q = z^-1, c = b/b0, G = prod b0 (tables.cpp picks one per filter):
+//   CASCADE coordinates: every stage's state is divided by g_k = prod_{j<k} b0_j, so that
+//       w' = in' - a1 v1' - a2 v2' ;  in'_{k+1} = w' + c1 v1' + c2 v2'
+//     and y = G * in'_K.  The reference's arithmetic order minus one multiply per inner stage.
+//   PARALLEL coordinates (partial fractions, needs distinct poles): all sections see the input itself,
+//       w_k = x - a1_k v1_k - a2_k v2_k ;  y = G * (x + sum_k alpha_k v1_k + beta_k v2_k)
+//     2K FMAs per sample on the recurrence and 2K more only where an output is kept; the K sections are
+//     independent chains.  State converts to/from the reference's (v1,v2) by a constant S x S matrix.
+//   Either way the 2K-vector s obeys s[n+1] = A s[n] + B x[n]; y/G = Cu s[n] + x[n].
+//
+// Input conversion without conversion instructions (integer inputs, PARALLEL form): the 13-bit (16-bit)
+// two's-complement field is XOR-ed into offset binary and dropped into the mantissa of a double with a
+// fixed exponent, which IS the double x + 12288 (x + 98304) - two ALU ops, no I2F on the quarter-rate
+// pipe.  A constant input offset c only shifts the whole state trajectory by the steady state
+// s* = (I - A)^-1 B c when the run starts AT s*, and the output by c * H(1): runs start at s*, s* is
+// subtracted from the run end state and c * H(1) * gain rides in the final multiply-add.
 //
 // Parallelisation: a *run* is LT consecutive samples owned by one thread; a *tile* is the 32
 // consecutive runs of one warp.  Every thread filters its run from ZERO state (exactly the
@@ -36,8 +49,11 @@ enum { OUT_F32 = 0,          // (float)y                              (parity F3
 
 // Filter constants that sit in the kernel-parameter constant bank (operands of DFMA).
 struct IirTables {
-    double a1[kMaxK], a2[kMaxK], c1[kMaxK], c2[kMaxK];
+    double a1[kMaxK], a2[kMaxK];          // recurrence, both forms
+    double c1[kMaxK], c2[kMaxK];          // cascade: b1/b0, b2/b0.  parallel: alpha_k, beta_k
     double gain;                          // G * output scale
+    double out_bias;                      // added after the gain: -c * Hn(1) * gain (0 when the input carries no offset)
+    double sbias[kMaxS];                  // s*: state every run starts from (0 when the input carries no offset)
     double Mp[5][kMaxS * kMaxS];          // M^(2^j), row-major S x S (S = 2K)
     double R[kMaxNK][kMaxS];              // R[m] = Cu A^(m D)
 };
@@ -52,13 +68,13 @@ struct IirParams {
     int      window;            // J: look-back window in tiles (aggregates only)
     int      chained;           // 1: no contraction - wait for the predecessor's inclusive state
     int      write_state;       // last tile of each stream writes the stream end state
-    int      layout;            // IN_WORDS: 0 = S1G (I = hi13), 1 = HiF (I = lo13)
+    int      layout;            // IN_WORDS: 0 = S1G (I = hi13), 1 = HiF (I = lo13).  The kernel filters rail A = hi13
+                                // and rail B = lo13 and swaps at its borders (state in/out, output store)
     int      out_mode;
     const double* mtile_pow;    // [window+1][S*S]  M_tile^j (row-major)
     const double* plane;        // [S*S][33]        plane[e*33 + t] = (M^t)[e]
-    double*   desc_agg;         // [total_tiles][2S]  zero-state tile end states
-    double*   desc_incl;        // [total_tiles][2S]  true tile end states
-    uint32_t* desc_flag;        // [total_tiles]      0 none, 1 aggregate, 2 inclusive (zeroed per launch)
+    double*   desc_agg;         // [total_tiles][2S]  zero-state tile end states; every double validates itself:
+    double*   desc_incl;        // [total_tiles][2S]  true tile end states         the arrays are pre-set to kDescEmpty
     uint32_t* ticket;           // zeroed per launch
     const double* state_in;     // [n_streams][2S] kernel coordinates
     double*   state_out;        // [n_streams][2S]
@@ -72,7 +88,7 @@ struct IirTailParams {
     const void* in; uint64_t in_stride;     // elements
     uint64_t first;  uint64_t n;            // samples [first, n) of every stream
     void* out; uint64_t out_stride;
-    int in_kind, layout, out_mode, K, D;
+    int in_kind, layout, out_mode, K, D, par;
     double a1[kMaxK], a2[kMaxK], c1[kMaxK], c2[kMaxK];
     double gain;
     double* state;                          // [n_streams][2S] kernel coordinates, updated in place
@@ -81,14 +97,26 @@ struct IirTailParams {
 
 // run length for a decimation factor
 __host__ __device__ constexpr int iir_run_len(int D) { return D == 1 ? 32 : (D == 2 ? 64 : 128); }
-constexpr int kIirWarpsPerCta = 4;
-constexpr int kIirRingStages  = 2;
+#ifndef CBL_IIR_WPC
+#define CBL_IIR_WPC 4
+#endif
+#ifndef CBL_IIR_STAGES
+#define CBL_IIR_STAGES 2
+#endif
+constexpr int kIirWarpsPerCta = CBL_IIR_WPC;
+constexpr int kIirRingStages  = CBL_IIR_STAGES;
+// look-back descriptors: a slot holds this bit pattern (a NaN no computation produces) until its owner
+// has written it; a value that happens to equal it is nudged to the neighbouring NaN pattern
+constexpr unsigned long long kDescEmpty = 0xFFFFFFFFFFFFFFFFull;
+// offsets the integer->double mantissa injection adds to the sample value
+constexpr double kBiasWords = 12288.0;    // 2^13 + 2^12
+constexpr double kBiasCs16  = 98304.0;    // 2^16 + 2^15
 
 size_t iir_smem_bytes(int K, int D, int in_kind);
 // returns cudaError_t as int
-int launch_iir(int K, int D, int in_kind, const CUtensorMap& tmap, const IirParams& p, const IirTables& t,
+int launch_iir(int K, int D, int in_kind, bool par, const CUtensorMap& tmap, const IirParams& p, const IirTables& t,
                int grid_ctas, cudaStream_t st);
-int iir_max_ctas_per_sm(int K, int D, int in_kind);
+int iir_max_ctas_per_sm(int K, int D, int in_kind, bool par);
 void launch_iir_tail(const IirTailParams& p, cudaStream_t st);
 // state <- state_next (n doubles) unless *gate != 0
 void launch_commit_state(double* state, const double* state_next, size_t n, const int32_t* gate, cudaStream_t st);

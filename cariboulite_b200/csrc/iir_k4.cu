@@ -1,6 +1,6 @@
 // Kernel (b) instantiations for cascades of 4 biquad(s).
 #include "iir_kernel.cuh"
 namespace cbl {
-iir_launch_fn iir_launch_k4(int D, int in_kind) { return iir_pick_launch<4>(D, in_kind); }
-iir_occ_fn iir_occ_k4(int D, int in_kind) { return iir_pick_occ<4>(D, in_kind); }
+iir_launch_fn iir_launch_k4(int D, int in_kind, bool par) { return iir_pick_launch<4>(D, in_kind, par); }
+iir_occ_fn iir_occ_k4(int D, int in_kind, bool par) { return iir_pick_occ<4>(D, in_kind, par); }
 }

@@ -1,4 +1,18 @@
 // Kernel (b) template.  See iir.cuh for the math.  Included by iir_k{1,2,3,4}.cu.
+//
+// Shape of one warp's life (persistent; 32 lanes = 32 consecutive runs of LT samples = one tile):
+//
+//   claim a tile (ticket) ---------------------------------------------.
+//   phase 1  every lane filters its run from the steady state s*,       |  the NEXT tile is claimed at the top
+//            fed by a per-warp ring of 4 KiB TMA boxes (128B swizzle:   |  of phase 1 and its first boxes are
+//            lane = row, bank-conflict-free 16-byte reads); zero-state  |  requested while phase 1 drains, so
+//            outputs at the kept (decimated) positions go to smem       |  the ring never runs dry between tiles
+//   phase 2  warp scan of the run end states with the constant powers   |
+//            M^(2^j) (shuffles); lane 31 publishes the tile aggregate --'
+//   look-back  state entering the tile from the predecessors' aggregates (window bounded by the filter's
+//            contraction) or, without contraction, from the predecessor's inclusive state.  Descriptor
+//            doubles validate themselves (kDescEmpty until written): no flag, no fence.
+//   phase 3  y[m] = gain * (y_zs[m] + R[m] . s0) + out_bias, converted and stored.
 #pragma once
 #include "iir.cuh"
 
@@ -31,15 +45,24 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* tma
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
         ::"r"(dst), "l"(tmap), "r"(x), "r"(y), "r"(z), "r"(bar) : "memory");
 }
-__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p)
+// look-back descriptor slots: relaxed, L2-coherent 8-byte accesses; the value is its own "ready" flag
+__device__ __forceinline__ unsigned long long ld_desc(const double* p)
 {
-    uint32_t v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v)
+__device__ __forceinline__ void st_desc(double* p, double x)
 {
-    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+    unsigned long long v = (unsigned long long)__double_as_longlong(x);
+    if (v == kDescEmpty) v = kDescEmpty - 1;      // still a NaN, no longer "empty"
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ double wait_desc(const double* p)
+{
+    unsigned long long v = ld_desc(p);
+    while (v == kDescEmpty) { __nanosleep(32); v = ld_desc(p); }
+    return __longlong_as_double((long long)v);
 }
 // explicit shared-space accesses (the carve-up below goes through integers, which would
 // otherwise demote these to generic LD/ST)
@@ -59,18 +82,42 @@ __device__ __forceinline__ void sts64(uint32_t a, double v)
 {
     asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory");
 }
-// int32 -> double.  Default: I2F.F64 (conversion pipe).  -DCBL_CONV_MAGIC: exponent trick + one DADD.
-__device__ __forceinline__ double i2d(int v)
-{
-#ifdef CBL_CONV_MAGIC
-    return __hiloint2double(0x43300000, (int)((uint32_t)v ^ 0x80000000u)) - 4503601774854144.0;   // 2^52 + 2^31
-#else
-    return (double)v;
-#endif
-}
 __device__ __forceinline__ double shfl_up_f64(double v, int d)
 {
     return __shfl_up_sync(0xffffffffu, v, d);
+}
+
+// ------------------------------------------------------------------ sample -> (rail A, rail B) doubles
+// rail A = hi13 / int16 low half / float re, rail B = lo13 / int16 high half / float im.
+// INJECT: integer fields become doubles offset by kBiasWords / kBiasCs16 with two ALU ops each.
+template <int IN, bool INJECT>
+__device__ __forceinline__ void sample_to_f64(uint32_t w0, uint32_t w1, double& xa, double& xb)
+{
+    if (IN == IN_WORDS) {
+        if (INJECT) {
+            // field bits 29:17 (13:1) -> mantissa bits 51:39 of a double with exponent 2^13, sign bit flipped
+            const uint32_t ha = ((w0 >> 10) & 0x000FFF80u) ^ 0x40C80000u;
+            const uint32_t hb = ((w0 << 6) & 0x000FFF80u) ^ 0x40C80000u;
+            xa = __hiloint2double((int)ha, 0);
+            xb = __hiloint2double((int)hb, 0);
+        } else {
+            xa = (double)hi13(w0);
+            xb = (double)lo13(w0);
+        }
+    } else if (IN == IN_CS16) {
+        if (INJECT) {
+            const uint32_t ha = ((w0 << 4) & 0x000FFFF0u) ^ 0x40F80000u;
+            const uint32_t hb = ((w0 >> 12) & 0x000FFFF0u) ^ 0x40F80000u;
+            xa = __hiloint2double((int)ha, 0);
+            xb = __hiloint2double((int)hb, 0);
+        } else {
+            xa = (double)(int)(int16_t)(w0 & 0xFFFFu);
+            xb = (double)((int32_t)w0 >> 16);
+        }
+    } else {
+        xa = (double)__uint_as_float(w0);
+        xb = (double)__uint_as_float(w1);
+    }
 }
 
 template <int K, int D, int IN>
@@ -89,29 +136,47 @@ struct IirCfg {
     static constexpr int SMEM_BYTES = WPC * WARP_BYTES + WPC * STAGES * 8 + 1024;   // + mbarriers + alignment slack
 };
 
-// One cascade step on one rail.  v = (v1,v2) per stage.  Returns in'_K if LAST else undefined.
-template <int K, bool NEED_OUT>
-__device__ __forceinline__ double cascade_step(const IirTables& T, double (&v)[K][2], double x)
+// One filter step on one rail.  v = (v1,v2) per section.  Returns y/G at this sample if NEED_OUT.
+template <int K, bool PAR, bool NEED_OUT>
+__device__ __forceinline__ double filter_step(const IirTables& T, double (&v)[K][2], double x)
 {
-    double in = x;
+    if (PAR) {
+        double out = x;
 #pragma unroll
-    for (int k = 0; k < K; k++) {
-        const double t = fma(-T.a2[k], v[k][1], in);
-        const double w = fma(-T.a1[k], v[k][0], t);
-        if (k < K - 1 || NEED_OUT) in = fma(T.c2[k], v[k][1], fma(T.c1[k], v[k][0], w));
-        v[k][1] = v[k][0];
-        v[k][0] = w;
+        for (int k = 0; k < K; k++) {
+            if (NEED_OUT) out = fma(T.c2[k], v[k][1], fma(T.c1[k], v[k][0], out));
+            const double w = fma(-T.a1[k], v[k][0], fma(-T.a2[k], v[k][1], x));
+            v[k][1] = v[k][0];
+            v[k][0] = w;
+        }
+        return out;
+    } else {
+        double in = x;
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const double t = fma(-T.a2[k], v[k][1], in);
+            const double w = fma(-T.a1[k], v[k][0], t);
+            if (k < K - 1 || NEED_OUT) in = fma(T.c2[k], v[k][1], fma(T.c1[k], v[k][0], w));
+            v[k][1] = v[k][0];
+            v[k][0] = w;
+        }
+        return in;
     }
-    return in;
 }
 
-template <int K, int D, int IN>
+// non-zero columns of row `row` of A^n: the section's own 2x2 block (parallel) / everything up to and
+// including it (cascade: block lower-triangular)
+template <bool PAR> __device__ __forceinline__ constexpr int col_lo(int row) { return PAR ? 2 * (row / 2) : 0; }
+__device__ __forceinline__ constexpr int col_hi(int row) { return 2 * (row / 2 + 1); }
+
+template <int K, int D, int IN, bool PAR>
 __global__ void __launch_bounds__(kIirWarpsPerCta * 32)
 iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ IirParams P,
                 const __grid_constant__ IirTables T)
 {
     using C = IirCfg<K, D, IN>;
     constexpr int S = C::S;
+    constexpr bool INJECT = PAR && IN != IN_CF32;
     extern __shared__ uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // shared-memory carve-up, as 32-bit shared-window addresses (1024-byte aligned for the 128B swizzle)
@@ -131,29 +196,52 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
 
     if (P.gate != nullptr && __ldg(P.gate) != 0) return;
 
-    uint32_t gstep = 0;    // steps consumed by this warp so far (ring position / parity)
+    const int swap = (IN == IN_WORDS) ? P.layout : 0;     // rail A carries Q instead of I
 
-    for (;;) {
-        uint32_t tile = 0;
-        if (lane == 0) tile = atomicAdd(P.ticket, 1u);
-        tile = __shfl_sync(0xffffffffu, tile, 0);
-        if (tile >= P.total_tiles) break;
+    // this lane's M^lane, non-zero pattern only (s0 = M^lane S_in + E_{lane-1})
+    constexpr int NPL = PAR ? 2 : S;
+    double pl[S][NPL];
+#pragma unroll
+    for (int row = 0; row < S; row++)
+#pragma unroll
+        for (int col = col_lo<PAR>(row); col < col_hi(row); col++)
+            pl[row][col - col_lo<PAR>(row)] = __ldg(P.plane + (row * S + col) * 33 + lane);
+
+    // request box `lstep` of `tile` into ring slot `slot` (lane 0 only)
+    auto issue = [&](uint32_t tile, int lstep, uint32_t slot) {
+        const uint32_t stream = tile / P.tiles_per_stream;
+        const uint32_t tis = tile - stream * P.tiles_per_stream;
+        mbar_expect_tx(bar_u32 + 8 * slot, 4096);
+        tma_load_3d(ring_u32 + slot * 4096, &tmap, lstep * 32, (int)tis * 32, (int)stream, bar_u32 + 8 * slot);
+    };
+
+    uint32_t gstep = 0;    // steps consumed by this warp so far (ring position / parity)
+    uint32_t tile = 0;
+    if (lane == 0) {
+        tile = atomicAdd(P.ticket, 1u);
+        if (tile < P.total_tiles) {
+#pragma unroll
+            for (int s = 0; s < C::STAGES; s++) issue(tile, s, (uint32_t)s);
+        }
+    }
+    tile = __shfl_sync(0xffffffffu, tile, 0);
+
+    while (tile < P.total_tiles) {
+        // the next tile is claimed now; the atomic's round trip hides behind phase 1 (lane 0 keeps it)
+        uint32_t next = 0xFFFFFFFFu;
+        if (lane == 0) next = atomicAdd(P.ticket, 1u);
+
         const uint32_t stream = tile / P.tiles_per_stream;
         const uint32_t tis = tile - stream * P.tiles_per_stream;       // tile index within the stream
         const int run0 = (int)tis * 32;
 
-        // ---- phase 1: zero-state pass over the run, TMA-fed through a per-warp ring
-        if (lane == 0) {
+        // ---- phase 1: zero-state pass over the run (started at s*, see iir.cuh)
+        double va[K][2], vb[K][2];
 #pragma unroll
-            for (int s = 0; s < C::STAGES; s++) {
-                const uint32_t st = (gstep + s) % C::STAGES;
-                mbar_expect_tx(bar_u32 + 8 * st, 4096);
-                tma_load_3d(ring_u32 + st * 4096, &tmap, s * 32, run0, (int)stream, bar_u32 + 8 * st);
-            }
+        for (int k = 0; k < K; k++) {
+            va[k][0] = vb[k][0] = T.sbias[2 * k];
+            va[k][1] = vb[k][1] = T.sbias[2 * k + 1];
         }
-        double vi[K][2], vq[K][2];
-#pragma unroll
-        for (int k = 0; k < K; k++) { vi[k][0] = vi[k][1] = vq[k][0] = vq[k][1] = 0.0; }
 
 #pragma unroll 1
         for (int step = 0; step < C::NSTEP; step++) {
@@ -168,49 +256,42 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
 #pragma unroll
                 for (int e = 0; e < PER; e++) {
                     const int i = c * PER + e;                   // sample index within the step
-                    double xi, xq;
-                    if (IN == IN_WORDS) {
-                        const int h = hi13(wv[e]), l = lo13(wv[e]);
-                        xi = i2d(P.layout ? l : h);
-                        xq = i2d(P.layout ? h : l);
-                    } else if (IN == IN_CS16) {
-                        xi = i2d((int)(int16_t)(wv[e] & 0xFFFFu));
-                        xq = i2d((int32_t)wv[e] >> 16);
-                    } else {
-                        xi = (double)__uint_as_float(wv[2 * e]);
-                        xq = (double)__uint_as_float(wv[2 * e + 1]);
-                    }
+                    double xa, xb;
+                    if (IN == IN_CF32) sample_to_f64<IN, INJECT>(wv[2 * e], wv[2 * e + 1], xa, xb);
+                    else               sample_to_f64<IN, INJECT>(wv[e], 0u, xa, xb);
                     // kept iff (step*SPS + i) % D == 0
                     const bool kept_static = (D <= C::SPS) ? (i % D == 0) : (i == 0);
                     if (kept_static) {
                         const bool kept = (D <= C::SPS) ? true : (((step * C::SPS) % D) == 0);
-                        const double yi = cascade_step<K, true>(T, vi, xi);
-                        const double yq = cascade_step<K, true>(T, vq, xq);
+                        const double ya = filter_step<K, PAR, true>(T, va, xa);
+                        const double yb = filter_step<K, PAR, true>(T, vb, xb);
                         if (kept) {
                             const int m = (step * C::SPS + i) / D;
-                            sts64(ystage + ((m * 2 + 0) * 32 + lane) * 8, yi);
-                            sts64(ystage + ((m * 2 + 1) * 32 + lane) * 8, yq);
+                            sts64(ystage + ((m * 2 + 0) * 32 + lane) * 8, ya);
+                            sts64(ystage + ((m * 2 + 1) * 32 + lane) * 8, yb);
                         }
                     } else {
-                        cascade_step<K, false>(T, vi, xi);
-                        cascade_step<K, false>(T, vq, xq);
+                        filter_step<K, PAR, false>(T, va, xa);
+                        filter_step<K, PAR, false>(T, vb, xb);
                     }
                 }
             }
             __syncwarp();
-            if (lane == 0 && step + C::STAGES < C::NSTEP) {
-                mbar_expect_tx(bar_u32 + 8 * st, 4096);
-                tma_load_3d(ring_u32 + st * 4096, &tmap, (step + C::STAGES) * 32, run0, (int)stream, bar_u32 + 8 * st);
+            if (lane == 0) {
+                const int ls = step + C::STAGES;                 // the box that follows the ones in flight
+                if (ls < C::NSTEP) issue(tile, ls, st);
+                else if (next < P.total_tiles) issue(next, ls - C::NSTEP, st);
             }
             gstep++;
         }
+        next = __shfl_sync(0xffffffffu, next, 0);
 
         // ---- phase 2: warp scan of run end states: E_t = sum_{j<=t} M^(t-j) f_j
         double f[2][S];
 #pragma unroll
         for (int k = 0; k < K; k++) {
-            f[0][2 * k] = vi[k][0]; f[0][2 * k + 1] = vi[k][1];
-            f[1][2 * k] = vq[k][0]; f[1][2 * k + 1] = vq[k][1];
+            f[0][2 * k] = va[k][0] - T.sbias[2 * k]; f[0][2 * k + 1] = va[k][1] - T.sbias[2 * k + 1];
+            f[1][2 * k] = vb[k][0] - T.sbias[2 * k]; f[1][2 * k + 1] = vb[k][1] - T.sbias[2 * k + 1];
         }
 #pragma unroll
         for (int j = 0; j < 5; j++) {
@@ -226,50 +307,48 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
 #pragma unroll
                     for (int row = 0; row < S; row++) {
                         double acc = f[r][row];
-                        // A (hence every power of it) is block lower-triangular: stage k only sees stages <= k
 #pragma unroll
-                        for (int col = 0; col < 2 * (row / 2 + 1); col++) acc = fma(T.Mp[j][row * S + col], g[r][col], acc);
+                        for (int col = col_lo<PAR>(row); col < col_hi(row); col++) acc = fma(T.Mp[j][row * S + col], g[r][col], acc);
                         f[r][row] = acc;
                     }
             }
         }
         // f = inclusive scan value E_lane.  Lane 31 holds the tile aggregate.
-        double* agg = P.desc_agg + (size_t)tile * (2 * S);
-        if (lane == 31) {
+        if (lane == 31 && !P.chained) {
+            double* agg = P.desc_agg + (size_t)tile * (2 * S);
 #pragma unroll
             for (int r = 0; r < 2; r++)
 #pragma unroll
-                for (int c = 0; c < S; c++) agg[r * S + c] = f[r][c];
-            if (tis != 0 || !P.chained) { __threadfence(); st_release_u32(P.desc_flag + tile, 1u); }
+                for (int c = 0; c < S; c++) st_desc(agg + r * S + c, f[r][c]);
         }
 
         // ---- decoupled look-back: state entering this tile, component `lane` (< 2S) per lane
         const int comp = lane < 2 * S ? lane : 0;
         const int crail = comp / S, crow = comp % S;
         double sin_c = 0.0;
-        if (tis == 0) {
-            sin_c = P.state_in[(size_t)stream * (2 * S) + comp];
-        } else if (P.chained) {
-            while (ld_acquire_u32(P.desc_flag + tile - 1) != 2u) { }
-            sin_c = __ldcg(P.desc_incl + (size_t)(tile - 1) * (2 * S) + comp);
-        } else {
-            const int depth = (int)tis < P.window ? (int)tis : P.window;
-            for (int j = 1; j <= depth; j++) {
-                while (ld_acquire_u32(P.desc_flag + tile - j) == 0u) { }
-                const double* a = P.desc_agg + (size_t)(tile - j) * (2 * S) + crail * S;
-                const double* mp = P.mtile_pow + (size_t)(j - 1) * (S * S) + crow * S;
+        if (lane < 2 * S) {
+            if (tis == 0) {
+                sin_c = P.state_in[(size_t)stream * (2 * S) + (crail ^ swap) * S + crow];
+            } else if (P.chained) {
+                sin_c = wait_desc(P.desc_incl + (size_t)(tile - 1) * (2 * S) + comp);
+            } else {
+                const int depth = (int)tis < P.window ? (int)tis : P.window;
+                sin_c = wait_desc(P.desc_agg + (size_t)(tile - 1) * (2 * S) + comp);     // M_tile^0 = I
+                for (int j = 2; j <= depth; j++) {
+                    const double* a = P.desc_agg + (size_t)(tile - j) * (2 * S) + crail * S;
+                    const double* mp = P.mtile_pow + (size_t)(j - 1) * (S * S) + crow * S;
 #pragma unroll
-                for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), __ldcg(a + col), sin_c);
-            }
-            if ((int)tis <= P.window) {     // the window reaches the start of the stream
-                const double* a = P.state_in + (size_t)stream * (2 * S) + crail * S;
-                const double* mp = P.mtile_pow + (size_t)tis * (S * S) + crow * S;
+                    for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), wait_desc(a + col), sin_c);
+                }
+                if ((int)tis <= P.window) {     // the window reaches the start of the stream
+                    const double* a = P.state_in + (size_t)stream * (2 * S) + (crail ^ swap) * S;
+                    const double* mp = P.mtile_pow + (size_t)tis * (S * S) + crow * S;
 #pragma unroll
-                for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), __ldg(a + col), sin_c);
+                    for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), __ldg(a + col), sin_c);
+                }
             }
+            sts64(scratch + lane * 8, sin_c);
         }
-        __syncwarp();
-        if (lane < 2 * S) sts64(scratch + lane * 8, sin_c);
         __syncwarp();
         double sin[2][S];
 #pragma unroll
@@ -289,8 +368,8 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
 #pragma unroll
         for (int row = 0; row < S; row++)
 #pragma unroll
-            for (int col = 0; col < 2 * (row / 2 + 1); col++) {
-                const double m = __ldg(P.plane + (row * S + col) * 33 + lane);
+            for (int col = col_lo<PAR>(row); col < col_hi(row); col++) {
+                const double m = pl[row][col - col_lo<PAR>(row)];
                 s0[0][row] = fma(m, sin[0][col], s0[0][row]);
                 s0[1][row] = fma(m, sin[1][col], s0[1][row]);
             }
@@ -304,20 +383,19 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                 double* incl = P.desc_incl + (size_t)tile * (2 * S);
 #pragma unroll
                 for (int row = 0; row < S; row++) {
-                    double ai = f[0][row], aq = f[1][row];
+                    double ea = f[0][row], eb = f[1][row];
 #pragma unroll
-                    for (int col = 0; col < 2 * (row / 2 + 1); col++) {
+                    for (int col = col_lo<PAR>(row); col < col_hi(row); col++) {
                         const double m = __ldg(P.plane + (row * S + col) * 33 + lastl + 1);
-                        ai = fma(m, sin[0][col], ai);
-                        aq = fma(m, sin[1][col], aq);
+                        ea = fma(m, sin[0][col], ea);
+                        eb = fma(m, sin[1][col], eb);
                     }
-                    incl[row] = ai; incl[S + row] = aq;
+                    if (P.chained) { st_desc(incl + row, ea); st_desc(incl + S + row, eb); }
                     if (last_tile && P.write_state) {
-                        P.state_out[(size_t)stream * (2 * S) + row] = ai;
-                        P.state_out[(size_t)stream * (2 * S) + S + row] = aq;
+                        P.state_out[(size_t)stream * (2 * S) + (0 ^ swap) * S + row] = ea;
+                        P.state_out[(size_t)stream * (2 * S) + (1 ^ swap) * S + row] = eb;
                     }
                 }
-                if (P.chained) { __threadfence(); st_release_u32(P.desc_flag + tile, 2u); }
             }
         }
 
@@ -327,14 +405,16 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             const uint64_t o0 = (uint64_t)stream * P.out_stride + (uint64_t)run * C::NK;
 #pragma unroll 4
             for (int m = 0; m < C::NK; m++) {
-                double yi = lds64(ystage + ((m * 2 + 0) * 32 + lane) * 8);
-                double yq = lds64(ystage + ((m * 2 + 1) * 32 + lane) * 8);
+                double ya = lds64(ystage + ((m * 2 + 0) * 32 + lane) * 8);
+                double yb = lds64(ystage + ((m * 2 + 1) * 32 + lane) * 8);
 #pragma unroll
                 for (int c = 0; c < S; c++) {
-                    yi = fma(T.R[m][c], s0[0][c], yi);
-                    yq = fma(T.R[m][c], s0[1][c], yq);
+                    ya = fma(T.R[m][c], s0[0][c], ya);
+                    yb = fma(T.R[m][c], s0[1][c], yb);
                 }
-                yi *= T.gain; yq *= T.gain;
+                ya = fma(ya, T.gain, T.out_bias);
+                yb = fma(yb, T.gain, T.out_bias);
+                const double yi = swap ? yb : ya, yq = swap ? ya : yb;
                 const uint64_t o = o0 + m;
                 if (P.out_mode == OUT_F32) {
                     __stcs(reinterpret_cast<float2*>(P.out) + o, make_float2((float)yi, (float)yq));
@@ -360,59 +440,73 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             }
         }
         __syncwarp();   // ystage / scratch are reused by the next tile
+        tile = next;
     }
 }
 
-template <int K, int D, int IN>
+template <int K, int D, int IN, bool PAR>
 int launch_iir_t(const CUtensorMap& tmap, const IirParams& p, const IirTables& t, int grid, cudaStream_t st)
 {
     using C = IirCfg<K, D, IN>;
-    auto kern = iir_scan_kernel<K, D, IN>;
+    auto kern = iir_scan_kernel<K, D, IN, PAR>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
     if (e != cudaSuccess) return (int)e;
     kern<<<grid, C::WPC * 32, C::SMEM_BYTES, st>>>(tmap, p, t);
     return (int)cudaGetLastError();
 }
 
-template <int K, int D, int IN>
+template <int K, int D, int IN, bool PAR>
 int occupancy_iir_t()
 {
     using C = IirCfg<K, D, IN>;
-    auto kern = iir_scan_kernel<K, D, IN>;
+    auto kern = iir_scan_kernel<K, D, IN, PAR>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
     int n = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, C::WPC * 32, C::SMEM_BYTES) != cudaSuccess) return 0;
     return n;
 }
 
-#define CBL_IIR_DISPATCH_D(KK, IN_, CALL)                    \
+#define CBL_IIR_DISPATCH_D(KK, IN_, PAR_, CALL)              \
     switch (D) {                                            \
-        case 1:  return CALL<KK, 1, IN_>;                    \
-        case 2:  return CALL<KK, 2, IN_>;                    \
-        case 4:  return CALL<KK, 4, IN_>;                    \
-        case 8:  return CALL<KK, 8, IN_>;                    \
-        case 16: return CALL<KK, 16, IN_>;                   \
-        case 32: return CALL<KK, 32, IN_>;                   \
+        case 1:  return CALL<KK, 1, IN_, PAR_>;              \
+        case 2:  return CALL<KK, 2, IN_, PAR_>;              \
+        case 4:  return CALL<KK, 4, IN_, PAR_>;              \
+        case 8:  return CALL<KK, 8, IN_, PAR_>;              \
+        case 16: return CALL<KK, 16, IN_, PAR_>;             \
+        case 32: return CALL<KK, 32, IN_, PAR_>;             \
         default: return nullptr;                            \
     }
 
 typedef int (*iir_launch_fn)(const CUtensorMap&, const IirParams&, const IirTables&, int, cudaStream_t);
 typedef int (*iir_occ_fn)();
 
+// K == 1 has a single section: the parallel form is the cascade, only the cascade kernel is built
 template <int KK>
-iir_launch_fn iir_pick_launch(int D, int in_kind)
+iir_launch_fn iir_pick_launch(int D, int in_kind, bool par)
 {
-    if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, &launch_iir_t) }
-    if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, &launch_iir_t) }
-    if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, &launch_iir_t) }
+    if (par && KK > 1) {
+        if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, (KK > 1), &launch_iir_t) }
+        if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, (KK > 1), &launch_iir_t) }
+        if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, (KK > 1), &launch_iir_t) }
+        return nullptr;
+    }
+    if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, false, &launch_iir_t) }
+    if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, false, &launch_iir_t) }
+    if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, false, &launch_iir_t) }
     return nullptr;
 }
 template <int KK>
-iir_occ_fn iir_pick_occ(int D, int in_kind)
+iir_occ_fn iir_pick_occ(int D, int in_kind, bool par)
 {
-    if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, &occupancy_iir_t) }
-    if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, &occupancy_iir_t) }
-    if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, &occupancy_iir_t) }
+    if (par && KK > 1) {
+        if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, (KK > 1), &occupancy_iir_t) }
+        if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, (KK > 1), &occupancy_iir_t) }
+        if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, (KK > 1), &occupancy_iir_t) }
+        return nullptr;
+    }
+    if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, false, &occupancy_iir_t) }
+    if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, false, &occupancy_iir_t) }
+    if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, false, &occupancy_iir_t) }
     return nullptr;
 }
 

@@ -75,6 +75,7 @@ int butter_lowpass_sos(int order, double fs, double fc_hz, double* sos)
 // ------------------------------------------------------------------ small dense algebra (long double)
 namespace {
 typedef long double ld;
+typedef std::complex<ld> cl;
 struct Mat { ld a[kMaxS][kMaxS]; };
 
 Mat mat_mul(const Mat& x, const Mat& y, int S)
@@ -91,8 +92,8 @@ Mat mat_mul(const Mat& x, const Mat& y, int S)
 Mat mat_eye(int S)
 {
     Mat r;
-    for (int i = 0; i < S; i++)
-        for (int j = 0; j < S; j++) r.a[i][j] = (i == j);
+    for (int i = 0; i < kMaxS; i++)
+        for (int j = 0; j < kMaxS; j++) r.a[i][j] = (i == j && i < S);
     return r;
 }
 Mat mat_pow(Mat b, uint64_t n, int S)
@@ -110,6 +111,26 @@ void mat_store(const Mat& m, int S, double* out)
     for (int i = 0; i < S; i++)
         for (int j = 0; j < S; j++) out[i * S + j] = (double)m.a[i][j];
 }
+// Gauss-Jordan with partial pivoting on an (n x n | m) augmented system, in place.  false if singular.
+bool solve_inplace(ld* a, int n, int m)
+{
+    const int w = n + m;
+    for (int c = 0; c < n; c++) {
+        int piv = c;
+        for (int r = c + 1; r < n; r++) if (fabsl(a[r * w + c]) > fabsl(a[piv * w + c])) piv = r;
+        if (!(fabsl(a[piv * w + c]) > 0)) return false;
+        if (piv != c) for (int j = 0; j < w; j++) std::swap(a[piv * w + j], a[c * w + j]);
+        const ld inv = 1 / a[c * w + c];
+        for (int j = c; j < w; j++) a[c * w + j] *= inv;
+        for (int r = 0; r < n; r++) {
+            if (r == c) continue;
+            const ld f = a[r * w + c];
+            if (f == 0) continue;
+            for (int j = c; j < w; j++) a[r * w + j] -= f * a[c * w + j];
+        }
+    }
+    return true;
+}
 // scaled max-norm: max_ij |m_ij| * scale_j / scale_i  (how much of a typical state survives)
 ld scaled_norm(const Mat& m, int S, const std::vector<ld>& sc)
 {
@@ -121,9 +142,177 @@ ld scaled_norm(const Mat& m, int S, const std::vector<ld>& sc)
         }
     return v;
 }
+
+// ------------------------------------------------------------------ the two realisations
+struct Form {
+    int K; bool par;
+    ld a1[kMaxK], a2[kMaxK], c1[kMaxK], c2[kMaxK];    // values the kernel uses (already rounded to double)
+};
+// one sample: ns = A s + B x, out = Cu s + x (this is y / G)
+void form_step(const Form& F, const ld* s, ld x, ld* ns, ld* out)
+{
+    if (F.par) {
+        ld o = x;
+        for (int k = 0; k < F.K; k++) {
+            o += F.c1[k] * s[2 * k] + F.c2[k] * s[2 * k + 1];
+            ns[2 * k] = x - F.a1[k] * s[2 * k] - F.a2[k] * s[2 * k + 1];
+            ns[2 * k + 1] = s[2 * k];
+        }
+        *out = o;
+    } else {
+        ld in = x;
+        for (int k = 0; k < F.K; k++) {
+            const ld w = in - F.a1[k] * s[2 * k] - F.a2[k] * s[2 * k + 1];
+            in = w + F.c1[k] * s[2 * k] + F.c2[k] * s[2 * k + 1];
+            ns[2 * k] = w; ns[2 * k + 1] = s[2 * k];
+        }
+        *out = in;
+    }
+}
+struct Realisation { Mat A; ld B[kMaxS], Cu[kMaxS]; };
+Realisation realise(const Form& F)
+{
+    Realisation R;
+    const int S = 2 * F.K;
+    R.A = mat_eye(0);
+    for (int j = 0; j <= S; j++) {
+        ld s[kMaxS], ns[kMaxS], out;
+        for (int i = 0; i < S; i++) s[i] = (i == j);
+        form_step(F, s, j == S ? 1 : 0, ns, &out);
+        if (j < S) { for (int i = 0; i < S; i++) R.A.a[i][j] = ns[i]; R.Cu[j] = out; }
+        else       { for (int i = 0; i < S; i++) R.B[i] = ns[i]; }
+    }
+    return R;
+}
+// typical magnitude of each state component: peak over frequency of |(zI - A)^-1 B|
+std::vector<ld> state_scale(const Realisation& R, int S)
+{
+    std::vector<ld> scale(S, 0);
+    const int NF = 2048;
+    for (int f = 0; f <= NF; f++) {
+        const ld w = 3.14159265358979323846264338327950288L * f / NF;
+        const cl z(cosl(w), sinl(w));
+        cl m[kMaxS][kMaxS + 1];
+        for (int i = 0; i < S; i++) {
+            for (int j = 0; j < S; j++) m[i][j] = cl((i == j), 0) * z - cl(R.A.a[i][j], 0);
+            m[i][S] = R.B[i];
+        }
+        bool ok = true;
+        for (int c = 0; c < S && ok; c++) {
+            int piv = c;
+            for (int r = c + 1; r < S; r++) if (std::abs(m[r][c]) > std::abs(m[piv][c])) piv = r;
+            if (std::abs(m[piv][c]) == 0) { ok = false; break; }
+            if (piv != c) for (int j = 0; j <= S; j++) std::swap(m[piv][j], m[c][j]);
+            for (int r = 0; r < S; r++) {
+                if (r == c) continue;
+                const cl fct = m[r][c] / m[c][c];
+                for (int j = c; j <= S; j++) m[r][j] -= fct * m[c][j];
+            }
+        }
+        if (!ok) continue;
+        for (int i = 0; i < S; i++) {
+            const ld v = std::abs(m[i][S] / m[i][i]);
+            if (std::isfinite((double)v) && v > scale[i]) scale[i] = v;
+        }
+    }
+    for (int i = 0; i < S; i++) if (!(scale[i] > 0)) scale[i] = 1;
+    return scale;
+}
+
+// Partial fractions of Hn(q) = prod (1 + c1 q + c2 q^2) / prod (1 + a1 q + a2 q^2), q = z^-1:
+//   Hn(q) = 1 + sum_k (alpha_k q + beta_k q^2) / D_k(q)
+// by evaluating (Hn(q) - 1) / q * D_k(q) = Nn(q) / (q prod_{j != k} D_j(q)) at the roots of D_k.
+bool partial_fractions(int K, const ld* a1, const ld* a2, const ld* c1, const ld* c2, ld* alpha, ld* beta, const char** why)
+{
+    int degN = 0, degD = 0;
+    for (int k = 0; k < K; k++) {
+        degN += c2[k] != 0 ? 2 : (c1[k] != 0 ? 1 : 0);
+        degD += a2[k] != 0 ? 2 : (a1[k] != 0 ? 1 : 0);
+        if (a1[k] == 0 && a2[k] == 0) { *why = "a section without poles"; return false; }
+    }
+    if (degN > degD) { *why = "more zeros than poles"; return false; }
+    for (int k = 0; k < K; k++) {
+        cl q[2];
+        int nr;
+        if (a2[k] == 0) { q[0] = cl(-1 / a1[k], 0); nr = 1; }
+        else {
+            // poles z: z^2 + a1 z + a2 = 0; q = 1 / z
+            const cl disc = std::sqrt(cl(a1[k] * a1[k] - 4 * a2[k], 0));
+            const cl z0 = (-a1[k] + disc) / cl(2, 0), z1 = (-a1[k] - disc) / cl(2, 0);
+            if (std::abs(z0 - z1) < 1e-9L * std::abs(z0)) { *why = "a double pole inside one section"; return false; }
+            q[0] = cl(1, 0) / z0; q[1] = cl(1, 0) / z1; nr = 2;
+        }
+        cl rho[2];
+        for (int r = 0; r < nr; r++) {
+            cl num(1, 0), den = q[r];
+            for (int j = 0; j < K; j++) {
+                num *= cl(1, 0) + c1[j] * q[r] + c2[j] * q[r] * q[r];
+                if (j != k) den *= cl(1, 0) + a1[j] * q[r] + a2[j] * q[r] * q[r];
+            }
+            if (!(std::abs(den) > 0)) { *why = "two sections share a pole"; return false; }
+            rho[r] = num / den;
+        }
+        if (nr == 1) { alpha[k] = rho[0].real(); beta[k] = 0; }
+        else if (fabsl(q[0].imag()) > 0) {            // complex pair: alpha + beta q = rho
+            beta[k] = rho[0].imag() / q[0].imag();
+            alpha[k] = rho[0].real() - beta[k] * q[0].real();
+        } else {                                      // two real poles
+            beta[k] = ((rho[0] - rho[1]) / (q[0] - q[1])).real();
+            alpha[k] = (rho[0] - beta[k] * q[0]).real();
+        }
+        if (!std::isfinite((double)alpha[k]) || !std::isfinite((double)beta[k])) { *why = "partial fractions overflow"; return false; }
+    }
+    return true;
+}
+
+// T with T A_c = A_p T and T B_c = B_p (the state map between two realisations driven by the same
+// input), solved in coordinates normalised by the typical state magnitudes.
+bool state_map(const Realisation& Rc, const std::vector<ld>& sc, const Realisation& Rp, const std::vector<ld>& sp,
+               int S, Mat* T)
+{
+    const int nu = S * S, ne = S * S + S;
+    std::vector<ld> a((size_t)ne * (nu + 1), 0);
+    auto Ac = [&](int i, int j) { return Rc.A.a[i][j] * sc[j] / sc[i]; };
+    auto Ap = [&](int i, int j) { return Rp.A.a[i][j] * sp[j] / sp[i]; };
+    const int w = nu + 1;
+    int row = 0;
+    for (int i = 0; i < S; i++)
+        for (int j = 0; j < S; j++, row++) {
+            for (int k = 0; k < S; k++) {
+                a[(size_t)row * w + i * S + k] += Ac(k, j);       // (T Ac)[i][j]
+                a[(size_t)row * w + k * S + j] -= Ap(i, k);       // (Ap T)[i][j]
+            }
+        }
+    for (int i = 0; i < S; i++, row++) {
+        for (int k = 0; k < S; k++) a[(size_t)row * w + i * S + k] = Rc.B[k] / sc[k];
+        a[(size_t)row * w + nu] = Rp.B[i] / sp[i];
+    }
+    // elimination over all ne rows (the system is consistent and has full column rank)
+    std::vector<int> prow(nu, -1);
+    std::vector<char> used(ne, 0);
+    for (int c = 0; c < nu; c++) {
+        int piv = -1;
+        ld best = 0;
+        for (int r = 0; r < ne; r++) if (!used[r] && fabsl(a[(size_t)r * w + c]) > best) { best = fabsl(a[(size_t)r * w + c]); piv = r; }
+        if (piv < 0 || !(best > 1e-300L)) return false;
+        used[piv] = 1; prow[c] = piv;
+        const ld inv = 1 / a[(size_t)piv * w + c];
+        for (int j = 0; j < w; j++) a[(size_t)piv * w + j] *= inv;
+        for (int r = 0; r < ne; r++) {
+            if (r == piv) continue;
+            const ld f = a[(size_t)r * w + c];
+            if (f == 0) continue;
+            for (int j = 0; j < w; j++) a[(size_t)r * w + j] -= f * a[(size_t)piv * w + j];
+        }
+    }
+    for (int r = 0; r < ne; r++) if (!used[r] && fabsl(a[(size_t)r * w + nu]) > 1e-9L) return false;   // inconsistent
+    for (int i = 0; i < S; i++)
+        for (int j = 0; j < S; j++) T->a[i][j] = a[(size_t)prow[i * S + j] * w + nu] * sp[i] / sc[j];
+    return true;
+}
 }  // namespace
 
-bool make_filter_plan(int K, const double (*sos)[6], int D, FilterPlan* P, const char** msg)
+bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, FilterPlan* P, const char** msg)
 {
     static const char* e_k = "n_sos must be 1..4";
     static const char* e_d = "decimation must be one of 1,2,4,8,16,32";
@@ -135,7 +324,8 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, FilterPlan* P, const
     P->LT = iir_run_len(D);
     P->NK = P->LT / D;
     std::memset(&P->tables, 0, sizeof(P->tables));
-    ld a1[kMaxK], a2[kMaxK], c1[kMaxK], c2[kMaxK];
+    Form Fc;
+    Fc.K = K; Fc.par = false;
     P->g[0] = 1.0;
     for (int k = 0; k < K; k++) {
         // Biquad::setCoefficients (Biquad.cpp:123-139): everything divided by a0, in double
@@ -144,68 +334,110 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, FilterPlan* P, const
         const double A1 = sos[k][4] / a0, A2 = sos[k][5] / a0;
         if (!std::isfinite(b0) || !std::isfinite(b1) || !std::isfinite(b2) || !std::isfinite(A1) ||
             !std::isfinite(A2) || a0 == 0.0 || b0 == 0.0) { *msg = e_c; return false; }
-        a1[k] = A1; a2[k] = A2;
-        c1[k] = (ld)b1 / (ld)b0; c2[k] = (ld)b2 / (ld)b0;
-        P->tables.a1[k] = A1; P->tables.a2[k] = A2;
-        P->tables.c1[k] = (double)c1[k]; P->tables.c2[k] = (double)c2[k];
+        Fc.a1[k] = A1; Fc.a2[k] = A2;
+        // the kernel uses the rounded (double) c's: the model does too, so that model and kernel agree
+        Fc.c1[k] = (double)((ld)b1 / (ld)b0); Fc.c2[k] = (double)((ld)b2 / (ld)b0);
         P->g[k + 1] = (double)((ld)P->g[k] * (ld)b0);
     }
+    const Realisation Rc = realise(Fc);
+    const std::vector<ld> sc = state_scale(Rc, S);
+
+    // ---- try the parallel realisation
+    Form F = Fc;
+    Realisation R = Rc;
+    std::vector<ld> scale = sc;
+    Mat Tp = mat_eye(S);          // kernel <- normalised cascade coordinates
+    P->par = false; P->par_err = 0; P->form_note = "";
+    if (force_cascade) P->form_note = "cascade form requested";
+    else if (K == 1) P->form_note = "single section";
+    else {
+        Form Fp = Fc;
+        Fp.par = true;
+        ld al[kMaxK], be[kMaxK];
+        const char* why = "";
+        bool ok = partial_fractions(K, Fc.a1, Fc.a2, Fc.c1, Fc.c2, al, be, &why);
+        Realisation Rp;
+        std::vector<ld> sp;
+        Mat T;
+        if (ok) {
+            for (int k = 0; k < K; k++) { Fp.c1[k] = (double)al[k]; Fp.c2[k] = (double)be[k]; }
+            Rp = realise(Fp);
+            sp = state_scale(Rp, S);
+            ok = state_map(Rc, sc, Rp, sp, S, &T);
+            if (!ok) why = "no state map between the realisations (pole-zero cancellation?)";
+        }
+        if (ok) {
+            // both realisations side by side on a deterministic full-scale test signal
+            ld s1[kMaxS] = {0}, s2[kMaxS] = {0}, n1[kMaxS], n2[kMaxS], o1, o2, e2 = 0, p2 = 0;
+            uint64_t lcg = 0x9E3779B97F4A7C15ull;
+            const int N = 1 << 15;
+            for (int n = 0; n < N; n++) {
+                lcg = lcg * 6364136223846793005ull + 1442695040888963407ull;
+                const ld x = (ld)((int)((lcg >> 40) & 8191) - 4096) + 3000 * cosl(0.0078539816339744830962L * n);
+                form_step(Fc, s1, x, n1, &o1);
+                form_step(Fp, s2, x, n2, &o2);
+                for (int i = 0; i < S; i++) { s1[i] = n1[i]; s2[i] = n2[i]; }
+                e2 += (o1 - o2) * (o1 - o2); p2 += o1 * o1;
+            }
+            P->par_err = (double)sqrtl(e2 / (p2 > 0 ? p2 : 1));
+            ld worst = 0;
+            for (int i = 0; i < S; i++) {
+                ld acc = 0;
+                for (int j = 0; j < S; j++) acc += T.a[i][j] * s1[j];
+                const ld e = fabsl(acc - s2[i]) / sp[i];
+                if (e > worst) worst = e;
+            }
+            if (!(P->par_err < 1e-11)) { ok = false; why = "parallel form loses too much to cancellation"; }
+            else if (!(worst < 1e-9L * 8192)) { ok = false; why = "state map inaccurate"; }
+        }
+        // constant-input steady state must exist (no pole at z = 1) for the mantissa-injection input path
+        ld sst[kMaxS];
+        if (ok) {
+            std::vector<ld> a((size_t)S * (S + 1));
+            for (int i = 0; i < S; i++) {
+                for (int j = 0; j < S; j++) a[(size_t)i * (S + 1) + j] = (ld)(i == j) - Rp.A.a[i][j];
+                a[(size_t)i * (S + 1) + S] = Rp.B[i];
+            }
+            ok = solve_inplace(a.data(), S, 1);
+            for (int i = 0; i < S && ok; i++) {
+                sst[i] = a[(size_t)i * (S + 1) + S];
+                if (!std::isfinite((double)sst[i]) || fabsl(sst[i]) > 4 * sp[i]) ok = false;
+            }
+            if (!ok) why = "pole at z = 1";
+        }
+        if (ok) {
+            P->par = true;
+            F = Fp; R = Rp; scale = sp; Tp = T;
+            ld h = 1;
+            for (int i = 0; i < S; i++) { P->sstar[i] = (double)sst[i]; h += Rp.Cu[i] * sst[i]; }
+            P->hn1 = (double)h;
+        } else {
+            P->form_note = why;
+        }
+    }
+    if (!P->par) { for (int i = 0; i < kMaxS; i++) P->sstar[i] = 0; P->hn1 = 1; }
+    for (int k = 0; k < K; k++) {
+        P->tables.a1[k] = (double)F.a1[k]; P->tables.a2[k] = (double)F.a2[k];
+        P->tables.c1[k] = (double)F.c1[k]; P->tables.c2[k] = (double)F.c2[k];
+    }
     P->tables.gain = P->g[K];
-    // use the rounded (double) c's in the model too, so model and kernel agree
-    for (int k = 0; k < K; k++) { c1[k] = P->tables.c1[k]; c2[k] = P->tables.c2[k]; }
-
-    // one-sample transition in kernel coordinates: columns = images of unit states with x = 0;
-    // Cu = in'_K as a function of the state; Bv = image of x = 1 from zero state
-    Mat A;
-    ld Cu[kMaxS], Bv[kMaxS];
-    for (int j = 0; j <= S; j++) {
-        ld s[kMaxS];
-        for (int i = 0; i < S; i++) s[i] = (i == j);
-        ld in = (j == S) ? 1 : 0;
-        ld ns[kMaxS];
-        for (int k = 0; k < K; k++) {
-            const ld w = in - a1[k] * s[2 * k] - a2[k] * s[2 * k + 1];
-            in = w + c1[k] * s[2 * k] + c2[k] * s[2 * k + 1];
-            ns[2 * k] = w; ns[2 * k + 1] = s[2 * k];
-        }
-        if (j < S) { for (int i = 0; i < S; i++) A.a[i][j] = ns[i]; Cu[j] = in; }
-        else       { for (int i = 0; i < S; i++) Bv[i] = ns[i]; }
-    }
-    for (int i = 0; i < S; i++) for (int j = 0; j < S; j++) P->A[i][j] = A.a[i][j];
-
-    // typical magnitude of each state component: peak over frequency of |(zI - A)^-1 B|
-    P->scale.assign(S, 0);
+    // state maps: reference DF-II state = g[stage] * normalised cascade state
     {
-        const int NF = 2048;
-        for (int f = 0; f <= NF; f++) {
-            const ld w = 3.14159265358979323846264338327950288L * f / NF;
-            const std::complex<ld> z(cosl(w), sinl(w));
-            // solve (zI - A) x = B by Gaussian elimination with partial pivoting
-            std::complex<ld> m[kMaxS][kMaxS + 1];
-            for (int i = 0; i < S; i++) {
-                for (int j = 0; j < S; j++) m[i][j] = std::complex<ld>((i == j), 0) * z - std::complex<ld>(A.a[i][j], 0);
-                m[i][S] = Bv[i];
+        const int w = 2 * S;
+        std::vector<ld> a((size_t)S * w);
+        for (int i = 0; i < S; i++)
+            for (int j = 0; j < S; j++) { a[(size_t)i * w + j] = Tp.a[i][j]; a[(size_t)i * w + S + j] = (i == j); }
+        if (!solve_inplace(a.data(), S, S)) { *msg = "state map is singular"; return false; }
+        for (int i = 0; i < S; i++)
+            for (int j = 0; j < S; j++) {
+                P->Tkr[i][j] = Tp.a[i][j] / (ld)P->g[j / 2];
+                P->Trk[i][j] = (ld)P->g[i / 2] * a[(size_t)i * w + S + j];
             }
-            bool ok = true;
-            for (int c = 0; c < S && ok; c++) {
-                int piv = c;
-                for (int r = c + 1; r < S; r++) if (std::abs(m[r][c]) > std::abs(m[piv][c])) piv = r;
-                if (std::abs(m[piv][c]) == 0) { ok = false; break; }
-                if (piv != c) for (int j = 0; j <= S; j++) std::swap(m[piv][j], m[c][j]);
-                for (int r = 0; r < S; r++) {
-                    if (r == c) continue;
-                    const std::complex<ld> fct = m[r][c] / m[c][c];
-                    for (int j = c; j <= S; j++) m[r][j] -= fct * m[c][j];
-                }
-            }
-            if (!ok) continue;
-            for (int i = 0; i < S; i++) {
-                const ld v = std::abs(m[i][S] / m[i][i]);
-                if (std::isfinite((double)v) && v > P->scale[i]) P->scale[i] = v;
-            }
-        }
-        for (int i = 0; i < S; i++) if (!(P->scale[i] > 0)) P->scale[i] = 1;
     }
+    const Mat& A = R.A;
+    const ld* Cu = R.Cu;
+    for (int i = 0; i < S; i++) for (int j = 0; j < S; j++) P->A[i][j] = A.a[i][j];
+    P->scale = scale;
 
     // R[m] = Cu A^(mD): walk the row vector through the run
     {
@@ -280,16 +512,39 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, FilterPlan* P, const
     return true;
 }
 
+void plan_power_kernel(const FilterPlan& P, uint64_t n, double* m)
+{
+    const int S = P.S;
+    Mat A = mat_eye(0);
+    for (int i = 0; i < S; i++) for (int j = 0; j < S; j++) A.a[i][j] = P.A[i][j];
+    mat_store(mat_pow(A, n, S), S, m);
+}
+
 void plan_shard_matrix(const FilterPlan& P, uint64_t n, double* m)
 {
     const int S = P.S;
-    Mat A;
-    for (int i = 0; i < S; i++) for (int j = 0; j < S; j++) A.a[i][j] = P.A[i][j];
-    const Mat p = mat_pow(A, n, S);
-    // reference coordinates: s_ref[i] = g[stage(i)] * s_kernel[i]
+    Mat A = mat_eye(0), Tkr = mat_eye(0), Trk = mat_eye(0);
     for (int i = 0; i < S; i++)
-        for (int j = 0; j < S; j++)
-            m[i * S + j] = (double)(p.a[i][j] * (ld)P.g[i / 2] / (ld)P.g[j / 2]);
+        for (int j = 0; j < S; j++) { A.a[i][j] = P.A[i][j]; Tkr.a[i][j] = P.Tkr[i][j]; Trk.a[i][j] = P.Trk[i][j]; }
+    // reference coordinates: s_ref = Trk s_kernel
+    mat_store(mat_mul(mat_mul(Trk, mat_pow(A, n, S), S), Tkr, S), S, m);
+}
+
+void plan_state_to_kernel(const FilterPlan& P, const double* ref, double* ker)
+{
+    for (int i = 0; i < P.S; i++) {
+        ld acc = 0;
+        for (int j = 0; j < P.S; j++) acc += P.Tkr[i][j] * (ld)ref[j];
+        ker[i] = (double)acc;
+    }
+}
+void plan_state_to_ref(const FilterPlan& P, const double* ker, double* ref)
+{
+    for (int i = 0; i < P.S; i++) {
+        ld acc = 0;
+        for (int j = 0; j < P.S; j++) acc += P.Trk[i][j] * (ld)ker[j];
+        ref[i] = (double)acc;
+    }
 }
 
 }  // namespace cbl

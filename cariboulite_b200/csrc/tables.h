@@ -13,8 +13,15 @@ int butter_lowpass_sos(int order, double fs, double fc, double* sos);
 // Everything the kernels need for one (cascade, decimation) pair.
 struct FilterPlan {
     int K = 0, D = 1, LT = 32, NK = 32, S = 0;
+    bool par = false;             // kernels run the parallel (partial-fraction) realisation, else the cascade
+    const char* form_note = "";   // why the cascade was chosen, when it was
+    double par_err = 0;           // parallel vs cascade, rel. rms over a long-double simulation (0 if not tried)
     double g[kMaxK + 1];          // g[k] = prod_{j<k} b0_j ; g[K] = overall gain G
-    IirTables tables;             // constant-bank tables (gain left at G; the caller applies the output scale)
+    IirTables tables;             // constant-bank tables (gain left at G, sbias/out_bias at 0: the launch fills them)
+    double sstar[kMaxS];          // steady state under a unit constant input, kernel coordinates
+    double hn1 = 1;               // H(1) / G
+    long double Tkr[kMaxS][kMaxS];// kernel state <- reference (DF-II v1,v2) state, per rail
+    long double Trk[kMaxS][kMaxS];// reference state <- kernel state
     std::vector<double> plane;    // [S*S][33]  (M^t)[e] at plane[e*33 + t]
     std::vector<double> mtile_pow;// [window+1][S*S]
     int window = 1;               // look-back window J (tiles)
@@ -25,9 +32,14 @@ struct FilterPlan {
 };
 
 // false (with msg) if the cascade cannot be handled (b0 == 0, non-finite coefficients, ...)
-bool make_filter_plan(int K, const double (*sos)[6], int D, FilterPlan* plan, const char** msg);
+bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, FilterPlan* plan, const char** msg);
 
 // A^n in REFERENCE state coordinates (row-major S x S doubles)
 void plan_shard_matrix(const FilterPlan& plan, uint64_t n, double* m);
+// A^n in KERNEL state coordinates
+void plan_power_kernel(const FilterPlan& plan, uint64_t n, double* m);
+// per-rail state vectors (S doubles) between the two coordinate systems
+void plan_state_to_kernel(const FilterPlan& plan, const double* ref, double* ker);
+void plan_state_to_ref(const FilterPlan& plan, const double* ker, double* ref);
 
 }  // namespace cbl

@@ -75,7 +75,25 @@ typedef struct {
     int      parity;                  /* caribou_cuda_parity */
     int      out_format;              /* caribou_cuda_format of the filtered output */
     void*    cuda_stream;             /* cudaStream_t to run on; NULL -> the library creates one */
+    int      kernel_form;             /* caribou_cuda_form: AUTO picks the parallel (partial-fraction) realisation of the
+                                         cascade when the poles allow it; CASCADE keeps the reference's stage-by-stage
+                                         arithmetic order inside every run */
 } caribou_cuda_config;
+
+typedef enum { CARIBOU_CUDA_FORM_AUTO = 0, CARIBOU_CUDA_FORM_CASCADE = 1, CARIBOU_CUDA_FORM_PARALLEL = 2 } caribou_cuda_form;
+
+/* What the scan kernel does with the configured cascade (for tests, DESIGN.md numbers and the curious). */
+typedef struct {
+    int      n_sos, decimation;
+    int      form;                 /* CASCADE or PARALLEL: the realisation the kernels run */
+    int      run_len;              /* samples one thread filters sequentially */
+    int      tile_samples;         /* samples per warp tile (32 runs) */
+    int      lookback_window;      /* tiles of look-back (aggregates only); meaningless when chained */
+    int      chained;              /* 1: no useful contraction, tiles wait for the predecessor's inclusive state */
+    uint64_t decay_samples;        /* samples after which an initial state has decayed below 2^-60 (0 if chained) */
+    double   parallel_form_error;  /* parallel vs cascade realisation, rel. rms in extended precision */
+    char     note[96];             /* why the cascade form was kept, if it was */
+} caribou_cuda_filter_info_t;
 
 /* Output buffers of the unpack stage.  Any pointer may be NULL (= not wanted), as in
  * LC/caribou_smi/caribou_smi.c:348-349.  Slots the reference leaves unwritten (tail of a
@@ -118,6 +136,14 @@ int64_t     caribou_cuda_wait(caribou_cuda_ctx* ctx, caribou_cuda_result* res);
 /* Number of kernels this context has launched so far (bench.py's gpu_launches). */
 uint64_t    caribou_cuda_launch_count(const caribou_cuda_ctx* ctx);
 
+/* Profiling aid for bench.py's roofline leg: when enabled, every submit brackets its dominant kernel
+ * (the IIR scan kernel; the unpack kernel for a context without filter) with CUDA events on the
+ * launching stream.  caribou_cuda_read_profile waits for the context, writes the device time in
+ * milliseconds of each bracketed launch since the previous read (oldest first, at most the last 256)
+ * to ms[0..cap) and returns how many it wrote (-1 on error). */
+int caribou_cuda_set_profiling(caribou_cuda_ctx* ctx, int enable);
+int caribou_cuda_read_profile(caribou_cuda_ctx* ctx, float* ms, int cap);
+
 /* page-locked host buffers for CARIBOU_CUDA_MEM_HOST_PINNED */
 void* caribou_cuda_host_alloc(size_t nbytes);
 void  caribou_cuda_host_free(void* p);
@@ -159,6 +185,7 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* ctx, const void* bytes, size_t nbyt
 int caribou_cuda_get_state(caribou_cuda_ctx* ctx, int stream, double* state);
 int caribou_cuda_set_state(caribou_cuda_ctx* ctx, int stream, const double* state);
 int caribou_cuda_reset(caribou_cuda_ctx* ctx);   /* zero state, decimation phase and sample position */
+int caribou_cuda_filter_info(caribou_cuda_ctx* ctx, caribou_cuda_filter_info_t* info);
 
 /* Multi-GPU time sharding: a shard is filtered from zero state; its end state f
  * (caribou_cuda_get_state) travels to the next rank; the receiving rank then re-runs the first

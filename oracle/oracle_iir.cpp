@@ -175,4 +175,30 @@ void orc_cascade_run_cs16_inplace(orc_cascade* ci, orc_cascade* cq, int16_t* iq,
     }
 }
 
+
+// Whole RX path of one in-memory capture (composition of the functions above, same order as
+// oracle/ref_shim/ref_glue.cpp::ref_rx_path_f32): MTU-sized orc_smi_read requests -> CS16 ->
+// (float)v / 4096.0f -> cascade per rail -> keep every D-th output.  Returns filtered samples or < 0.
+long orc_rx_path_f32(const uint8_t* bytes, size_t nbytes, size_t native_batch_len, int channel,
+                     orc_cascade* ci, orc_cascade* cq, int D, float* out, size_t n_samples)
+{
+    const size_t mtu = native_batch_len / ORC_BYTES_PER_SAMPLE;
+    std::vector<int16_t> cs16((mtu + 1) * 2);
+    std::vector<uint8_t> meta(mtu + 1);
+    size_t cursor = 0, pos = 0, m = 0;
+    while (pos < n_samples) {
+        const size_t want = n_samples - pos < mtu ? n_samples - pos : mtu;
+        const long got = orc_smi_read(bytes, nbytes, &cursor, native_batch_len, channel, cs16.data(), meta.data(), want);
+        if (got < 0) return got;
+        if (got == 0) break;
+        for (long k = 0; k < got; k++) {
+            const float yi = static_cast<float>(ci->step((float)cs16[2 * k + 0] / 4096.0f));
+            const float yq = static_cast<float>(cq->step((float)cs16[2 * k + 1] / 4096.0f));
+            if ((pos + (size_t)k) % (size_t)D == 0) { out[2 * m] = yi; out[2 * m + 1] = yq; m++; }
+        }
+        pos += (size_t)got;
+    }
+    return (long)m;
+}
+
 }  // extern "C"

@@ -74,6 +74,8 @@ def lib():
         L.orc_cascade_run_f32.argtypes = [_p, _p, _p, C.c_size_t]
         L.orc_cascade_run_f64.argtypes = [_p, _p, _p, C.c_size_t]
         L.orc_cascade_run_cs16_inplace.argtypes = [_p, _p, _p, C.c_size_t]
+        L.orc_rx_path_f32.restype = C.c_long
+        L.orc_rx_path_f32.argtypes = [_p, C.c_size_t, C.c_size_t, C.c_int, _p, _p, C.c_int, _p, C.c_size_t]
         for f in ("orc_cs16_to_cf32", "orc_cs16_to_cf64", "orc_cs16_to_cs8"):
             getattr(L, f).argtypes = [_p, _p, C.c_size_t]
             getattr(L, f).restype = None
@@ -311,6 +313,7 @@ def ref():
         R.ref_dev_open.restype = _p
         R.ref_dev_open.argtypes = [_p, C.c_size_t, C.c_size_t, C.c_int]
         R.ref_dev_close.argtypes = [_p]
+        R.ref_dev_rewind.argtypes = [_p]
         for f in ("ref_dev_smi_read", "ref_dev_radio_read"):
             getattr(R, f).restype = C.c_int
             getattr(R, f).argtypes = [_p, _p, _p, C.c_size_t]
@@ -333,6 +336,8 @@ def ref():
         R.ref_filt_run_f32.argtypes = [_p, _p, _p, C.c_size_t]
         R.ref_filt_run_f64.argtypes = [_p, _p, _p, C.c_size_t]
         R.ref_filt_run_cs16_inplace.argtypes = [_p, _p, _p, C.c_size_t]
+        R.ref_rx_path_f32.restype = C.c_long
+        R.ref_rx_path_f32.argtypes = [_p, _p, _p, C.c_int, _p, C.c_size_t]
         _ref = R
     return _ref
 
@@ -421,3 +426,38 @@ class RefFilter:
         y = np.empty_like(x)
         ref().ref_filt_run_f64(self.h, _ptr(x), _ptr(y), x.size)
         return y
+
+
+# ------------------------------------------------------------------ whole RX path (CPU baseline legs)
+def rx_path_f32(raw, sos, D, channel=CH_S1G, native_batch_len=NATIVE_BATCH_LEN):
+    """Oracle port: raw SMI bytes -> CF32 filtered, decimated [m,2] (one capture, zero initial state)."""
+    raw = np.ascontiguousarray(raw).view(np.uint8).reshape(-1)
+    n = raw.size // 4
+    ci, cq = Cascade(sos), Cascade(sos)
+    out = np.zeros((n // D + 1, 2), dtype=np.float32)
+    m = lib().orc_rx_path_f32(_ptr(raw), raw.size, native_batch_len, channel, ci.h, cq.h, D, _ptr(out), n)
+    if m < 0:
+        raise RuntimeError("orc_rx_path_f32 -> %d" % m)
+    return out[:m]
+
+
+class RefRxPath:
+    """The reference build's whole path for one capture: memfd device + two iir1 filter objects."""
+
+    def __init__(self, raw, order, fs, fc, D, channel=CH_S1G, native_batch_len=NATIVE_BATCH_LEN):
+        self.dev = RefDev(raw, channel, native_batch_len)
+        self.fi, self.fq = RefFilter(order, fs, fc), RefFilter(order, fs, fc)
+        self.D = D
+        self.n = np.ascontiguousarray(raw).view(np.uint8).size // 4
+        self.out = np.zeros((self.n // D + 1, 2), dtype=np.float32)
+
+    def rewind(self):
+        ref().ref_dev_rewind(self.dev.h)
+        self.fi.reset()
+        self.fq.reset()
+
+    def run(self):
+        m = ref().ref_rx_path_f32(self.dev.h, self.fi.h, self.fq.h, self.D, _ptr(self.out), self.n)
+        if m < 0:
+            raise RuntimeError("ref_rx_path_f32 -> %d" % m)
+        return self.out[:m]

@@ -101,6 +101,9 @@ void ref_dev_close(void* h)
     delete d;
 }
 
+// Re-arm the memfd so the same capture can be read again (bench repetitions).
+void ref_dev_rewind(void* h) { lseek(((RefDev*)h)->sys->smi.filedesc, 0, SEEK_SET); }
+
 // caribou_smi_read (caribou_smi.c:632-682), unmodified, on the memfd.
 int ref_dev_smi_read(void* h, int16_t* cs16, uint8_t* meta, size_t length_samples)
 {
@@ -146,7 +149,20 @@ struct RefFilt {
     virtual double f64(double x) = 0;
     virtual int    sos(double* out) = 0;   // rows of (b0,b1,b2,a0,a1,a2)
     virtual void   reset() = 0;
+    // one rail of a CS16 block: (float)v / 4096.0f (LC/CaribouLiteRadioCpp.cpp:91) -> filter<float>
+    // (LC/iir/iir/Cascade.h:161-169) at full rate; every D-th output (global phase *pos) is kept.
+    virtual size_t rail_f32(const int16_t* iq, int rail, size_t n, size_t pos, int D, float* out2) = 0;
 };
+template <class F>
+static size_t rail_loop(F& f, const int16_t* iq, int rail, size_t n, size_t pos, int D, float* out2)
+{
+    size_t m = 0;
+    for (size_t k = 0; k < n; k++) {
+        const float y = f.template filter<float>((float)iq[2 * k + rail] / 4096.0f);
+        if ((pos + k) % (size_t)D == 0) { out2[2 * m + rail] = y; m++; }
+    }
+    return m;
+}
 template <class F>
 static int dump_sos(F& f, double* out)
 {
@@ -166,6 +182,8 @@ struct RefButter : RefFilt {
     double f64(double x) override { return f.template filter<double>(x); }
     int    sos(double* out) override { return dump_sos(f, out); }
     void   reset() override { f.reset(); }
+    size_t rail_f32(const int16_t* iq, int rail, size_t n, size_t pos, int D, float* out2) override
+    { return rail_loop(f, iq, rail, n, pos, D, out2); }
 };
 template <int K>
 struct RefSos : RefFilt {
@@ -179,6 +197,8 @@ struct RefSos : RefFilt {
     double f64(double x) override { return f.template filter<double>(x); }
     int    sos(double* out) override { return dump_sos(f, out); }
     void   reset() override { f.reset(); }
+    size_t rail_f32(const int16_t* iq, int rail, size_t n, size_t pos, int D, float* out2) override
+    { return rail_loop(f, iq, rail, n, pos, D, out2); }
 };
 
 extern "C" {
@@ -236,3 +256,30 @@ void ref_filt_run_cs16_inplace(void* fi, void* fq, int16_t* iq, size_t n)
 }
 
 }  // extern "C"
+
+// The whole RX path for one capture, composed of the reference's own functions in the order the
+// north star names: caribou_smi_read (unmodified, MTU-sized requests as Stream::ReadSamples issues
+// them, CaribouliteStream.cpp:304-323) -> CS16 -> CF32 (/4096.0f) -> iir1 cascade per rail ->
+// keep every D-th sample.  Returns filtered samples written to out (interleaved CF32), or < 0.
+extern "C" long ref_rx_path_f32(void* h, void* fi, void* fq, int D, float* out, size_t n_samples)
+{
+    RefDev* d = (RefDev*)h;
+    RefFilt* pi = (RefFilt*)fi; RefFilt* pq = (RefFilt*)fq;
+    const size_t mtu = caribou_smi_get_native_batch_samples(&d->sys->smi);
+    int16_t* cs16 = (int16_t*)malloc((mtu + 1) * 4);
+    uint8_t* meta = (uint8_t*)malloc(mtu + 1);
+    size_t pos = 0, m = 0;
+    long rc = 0;
+    while (pos < n_samples) {
+        const size_t want = n_samples - pos < mtu ? n_samples - pos : mtu;
+        const int got = ref_dev_radio_read(h, cs16, meta, want);
+        if (got < 0) { rc = got; break; }
+        if (got == 0) break;
+        const size_t mi = pi->rail_f32(cs16, 0, (size_t)got, pos, D, out + 2 * m);
+        pq->rail_f32(cs16, 1, (size_t)got, pos, D, out + 2 * m);
+        m += mi;
+        pos += (size_t)got;
+    }
+    free(cs16); free(meta);
+    return rc < 0 ? rc : (long)m;
+}
