@@ -191,6 +191,9 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
         p.out = d_out;
         p.out_stride = out_stride;
         p.gate = gate;
+        // (0x413 << 21) | sign bit of the 13-bit field at bits 13:1;  (0x414 << 21) | sign bit of the int16
+        p.inj_mul = 1u << 31;
+        p.inj_xor = in_kind == IN_WORDS ? 0x82602000u : 0x82808000u;
         static int occ_cache[kMaxK + 1][33][3][2];
         int& occ = occ_cache[P.K][P.D][in_kind][P.par ? 1 : 0];
         if (occ == 0) occ = std::max(1, iir_max_ctas_per_sm(P.K, P.D, in_kind, P.par));

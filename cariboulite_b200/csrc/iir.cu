@@ -12,7 +12,7 @@ size_t iir_smem_bytes(int K, int D, int in_kind)
 {
     const int LT = iir_run_len(D), NK = LT / D, SPS = in_kind == IN_CF32 ? 16 : 32;
     const int nstep = LT / SPS, stages = nstep < kIirRingStages ? nstep : kIirRingStages;
-    const int warp_bytes = stages * 4096 + NK * 2 * 32 * 8 + 2 * (2 * K) * 8 * 2;
+    const int warp_bytes = stages * 4096 + 2 * (NK * 2 * 32 * 8) + 2 * (2 * K) * 8 * 2;
     return (size_t)kIirWarpsPerCta * warp_bytes + kIirWarpsPerCta * stages * 8 + 1024;
 }
 

@@ -16,8 +16,8 @@
 //
 // Input conversion without conversion instructions (integer inputs, PARALLEL form): the 13-bit (16-bit)
 // two's-complement field is XOR-ed into offset binary and dropped into the mantissa of a double with a
-// fixed exponent, which IS the double x + 12288 (x + 98304) - two ALU ops, no I2F on the quarter-rate
-// pipe.  A constant input offset c only shifts the whole state trajectory by the steady state
+// fixed exponent, which IS the double x + 2^20 + 2^12 (x + 2^21 + 2^15) - one LOP3 and one IMAD.WIDE
+// (plus a shift for the field in the upper half-word), no I2F on the quarter-rate pipe.  A constant input offset c only shifts the whole state trajectory by the steady state
 // s* = (I - A)^-1 B c when the run starts AT s*, and the output by c * H(1): runs start at s*, s* is
 // subtracted from the run end state and c * H(1) * gain rides in the final multiply-add.
 //
@@ -81,6 +81,8 @@ struct IirParams {
     void*     out;              // kept outputs, NK per run, streams out_stride elements apart
     uint64_t  out_stride;
     const int32_t* gate;        // optional: the launch is a no-op when *gate != 0 (misaligned capture)
+    // mantissa injection (iir_kernel.cuh inject_f64): sign-flip | exponent << 1 word, and the multiplier 2^31
+    uint32_t  inj_xor, inj_mul;
 };
 
 struct IirTailParams {
@@ -98,7 +100,7 @@ struct IirTailParams {
 // run length for a decimation factor
 __host__ __device__ constexpr int iir_run_len(int D) { return D == 1 ? 32 : (D == 2 ? 64 : 128); }
 #ifndef CBL_IIR_WPC
-#define CBL_IIR_WPC 4
+#define CBL_IIR_WPC 3
 #endif
 #ifndef CBL_IIR_STAGES
 #define CBL_IIR_STAGES 2
@@ -109,8 +111,8 @@ constexpr int kIirRingStages  = CBL_IIR_STAGES;
 // has written it; a value that happens to equal it is nudged to the neighbouring NaN pattern
 constexpr unsigned long long kDescEmpty = 0xFFFFFFFFFFFFFFFFull;
 // offsets the integer->double mantissa injection adds to the sample value
-constexpr double kBiasWords = 12288.0;    // 2^13 + 2^12
-constexpr double kBiasCs16  = 98304.0;    // 2^16 + 2^15
+constexpr double kBiasWords = 1052672.0;   // 2^20 + 2^12
+constexpr double kBiasCs16  = 2129920.0;   // 2^21 + 2^15
 
 size_t iir_smem_bytes(int K, int D, int in_kind);
 // returns cudaError_t as int

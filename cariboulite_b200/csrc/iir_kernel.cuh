@@ -13,6 +13,10 @@
 //            contraction) or, without contraction, from the predecessor's inclusive state.  Descriptor
 //            doubles validate themselves (kDescEmpty until written): no flag, no fence.
 //   phase 3  y[m] = gain * (y_zs[m] + R[m] . s0) + out_bias, converted and stored.
+//
+// Look-back and phase 3 of a tile run one tile LATE (after phases 1-2 of the warp's next tile, from the
+// other half of a double-buffered output stage): a warp never idles on a predecessor that is a little
+// behind, which otherwise synchronises all warps of the GPU into one convoy.
 #pragma once
 #include "iir.cuh"
 
@@ -89,31 +93,47 @@ __device__ __forceinline__ double shfl_up_f64(double v, int d)
 
 // ------------------------------------------------------------------ sample -> (rail A, rail B) doubles
 // rail A = hi13 / int16 low half / float re, rail B = lo13 / int16 high half / float im.
-// INJECT: integer fields become doubles offset by kBiasWords / kBiasCs16 with two ALU ops each.
+// Injection: integer fields become doubles offset by kBiasWords / kBiasCs16 with two integer ops each.
+// One LOP3 isolates the field, flips its sign bit (offset binary u = v + 2^(bits-1)) and ORs in the
+// exponent bits shifted left by one; one IMAD.WIDE by 2^31 then spreads that word over a register pair
+// whose high half is (exponent | u) and whose low half is (the last field bit, zeros): the double
+// 2^20 + u (SMI words) or 2^21 + u (CS16).  The second field of the word is shifted into place first.
+template <uint32_t MASK>
+__device__ __forceinline__ uint32_t and_xor(uint32_t a, uint32_t c)     // (a & MASK) ^ c, c in a register
+{
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0x6A;" : "=r"(d) : "r"(a), "n"(MASK), "r"(c));
+    return d;
+}
+// the multiplier comes in a register (kernel parameter): an immediate power of two is strength-reduced
+// by ptxas into shifts plus moves
+__device__ __forceinline__ double mul_wide_f64(uint32_t a, uint32_t mul)
+{
+    unsigned long long r;
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(r) : "r"(a), "r"(mul));
+    return __longlong_as_double((long long)r);
+}
+template <int IN>
+__device__ __forceinline__ void inject_f64(uint32_t w, uint32_t xc, uint32_t m31, double& xa, double& xb)
+{
+    if (IN == IN_WORDS) {      // rail A: bits 29:17, rail B: bits 13:1
+        xa = mul_wide_f64(and_xor<0x00003FFEu>(w >> 16, xc), m31);
+        xb = mul_wide_f64(and_xor<0x00003FFEu>(w, xc), m31);
+    } else {                   // rail A: bits 15:0, rail B: bits 31:16
+        xa = mul_wide_f64(and_xor<0x0000FFFFu>(w, xc), m31);
+        xb = mul_wide_f64(and_xor<0x0000FFFFu>(w >> 16, xc), m31);
+    }
+}
+
 template <int IN, bool INJECT>
 __device__ __forceinline__ void sample_to_f64(uint32_t w0, uint32_t w1, double& xa, double& xb)
 {
     if (IN == IN_WORDS) {
-        if (INJECT) {
-            // field bits 29:17 (13:1) -> mantissa bits 51:39 of a double with exponent 2^13, sign bit flipped
-            const uint32_t ha = ((w0 >> 10) & 0x000FFF80u) ^ 0x40C80000u;
-            const uint32_t hb = ((w0 << 6) & 0x000FFF80u) ^ 0x40C80000u;
-            xa = __hiloint2double((int)ha, 0);
-            xb = __hiloint2double((int)hb, 0);
-        } else {
-            xa = (double)hi13(w0);
-            xb = (double)lo13(w0);
-        }
+        xa = (double)hi13(w0);
+        xb = (double)lo13(w0);
     } else if (IN == IN_CS16) {
-        if (INJECT) {
-            const uint32_t ha = ((w0 << 4) & 0x000FFFF0u) ^ 0x40F80000u;
-            const uint32_t hb = ((w0 >> 12) & 0x000FFFF0u) ^ 0x40F80000u;
-            xa = __hiloint2double((int)ha, 0);
-            xb = __hiloint2double((int)hb, 0);
-        } else {
-            xa = (double)(int)(int16_t)(w0 & 0xFFFFu);
-            xb = (double)((int32_t)w0 >> 16);
-        }
+        xa = (double)(int)(int16_t)(w0 & 0xFFFFu);
+        xb = (double)((int32_t)w0 >> 16);
     } else {
         xa = (double)__uint_as_float(w0);
         xb = (double)__uint_as_float(w1);
@@ -130,9 +150,9 @@ struct IirCfg {
     static constexpr int STAGES = (NSTEP < kIirRingStages) ? NSTEP : kIirRingStages;
     static constexpr int WPC   = kIirWarpsPerCta;
     static constexpr int RING_BYTES    = STAGES * 4096;
-    static constexpr int YSTAGE_BYTES  = NK * 2 * 32 * 8;
+    static constexpr int YSTAGE_BYTES  = NK * 2 * 32 * 8;      // one tile's zero-state outputs; two of them per warp
     static constexpr int SCRATCH_BYTES = 2 * S * 8 * 2;        // S_in broadcast + spare
-    static constexpr int WARP_BYTES = RING_BYTES + YSTAGE_BYTES + SCRATCH_BYTES;
+    static constexpr int WARP_BYTES = RING_BYTES + 2 * YSTAGE_BYTES + SCRATCH_BYTES;
     static constexpr int SMEM_BYTES = WPC * WARP_BYTES + WPC * STAGES * 8 + 1024;   // + mbarriers + alignment slack
 };
 
@@ -182,8 +202,8 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     // shared-memory carve-up, as 32-bit shared-window addresses (1024-byte aligned for the 128B swizzle)
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t ring_u32 = base + warp * C::RING_BYTES;
-    const uint32_t ystage = base + C::WPC * C::RING_BYTES + warp * C::YSTAGE_BYTES;
-    const uint32_t scratch = base + C::WPC * (C::RING_BYTES + C::YSTAGE_BYTES) + warp * C::SCRATCH_BYTES;
+    const uint32_t ystage0 = base + C::WPC * C::RING_BYTES + warp * (2 * C::YSTAGE_BYTES);
+    const uint32_t scratch = base + C::WPC * (C::RING_BYTES + 2 * C::YSTAGE_BYTES) + warp * C::SCRATCH_BYTES;
     const uint32_t bar_u32 = base + C::WPC * C::WARP_BYTES + warp * C::STAGES * 8;
 
     if (lane == 0) {
@@ -207,6 +227,10 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
         for (int col = col_lo<PAR>(row); col < col_hi(row); col++)
             pl[row][col - col_lo<PAR>(row)] = __ldg(P.plane + (row * S + col) * 33 + lane);
 
+    // mantissa-injection constants.  They come from the kernel parameters because ptxas folds anything it can
+    // see through, and then splits the LOP3 and the IMAD.WIDE into longer immediate-friendly sequences.
+    const uint32_t inj_xor = P.inj_xor, inj_mul = P.inj_mul;
+
     // request box `lstep` of `tile` into ring slot `slot` (lane 0 only)
     auto issue = [&](uint32_t tile, int lstep, uint32_t slot) {
         const uint32_t stream = tile / P.tiles_per_stream;
@@ -226,220 +250,248 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     }
     tile = __shfl_sync(0xffffffffu, tile, 0);
 
-    while (tile < P.total_tiles) {
-        // the next tile is claimed now; the atomic's round trip hides behind phase 1 (lane 0 keeps it)
+    // the tile whose look-back + phase 3 are still owed (one behind the tile in phases 1-2)
+    bool owe = false;
+    uint32_t ptile = 0;
+    double pf[2][S];       // its inclusive scan values E_lane
+    uint32_t buf = 0;      // half of the output stage the CURRENT tile writes
+#pragma unroll
+    for (int r = 0; r < 2; r++)
+#pragma unroll
+        for (int c = 0; c < S; c++) pf[r][c] = 0.0;
+
+    for (;;) {
+        const bool have = tile < P.total_tiles;
         uint32_t next = 0xFFFFFFFFu;
-        if (lane == 0) next = atomicAdd(P.ticket, 1u);
+        double f[2][S];
+        if (have) {
+            // the next tile is claimed now; the atomic's round trip hides behind phase 1 (lane 0 keeps it)
+            if (lane == 0) next = atomicAdd(P.ticket, 1u);
+            const uint32_t ystage = ystage0 + buf * C::YSTAGE_BYTES;
 
-        const uint32_t stream = tile / P.tiles_per_stream;
-        const uint32_t tis = tile - stream * P.tiles_per_stream;       // tile index within the stream
-        const int run0 = (int)tis * 32;
-
-        // ---- phase 1: zero-state pass over the run (started at s*, see iir.cuh)
-        double va[K][2], vb[K][2];
+            // ---- phase 1: zero-state pass over the run (started at s*, see iir.cuh)
+            double va[K][2], vb[K][2];
 #pragma unroll
-        for (int k = 0; k < K; k++) {
-            va[k][0] = vb[k][0] = T.sbias[2 * k];
-            va[k][1] = vb[k][1] = T.sbias[2 * k + 1];
-        }
-
+            for (int k = 0; k < K; k++) {
+                va[k][0] = vb[k][0] = T.sbias[2 * k];
+                va[k][1] = vb[k][1] = T.sbias[2 * k + 1];
+            }
 #pragma unroll 1
-        for (int step = 0; step < C::NSTEP; step++) {
-            const uint32_t st = gstep % C::STAGES;
-            mbar_wait(bar_u32 + 8 * st, (gstep / C::STAGES) & 1u);
-            const uint32_t row = ring_u32 + st * 4096 + lane * 128;
+            for (int step = 0; step < C::NSTEP; step++) {
+                const uint32_t st = gstep % C::STAGES;
+                mbar_wait(bar_u32 + 8 * st, (gstep / C::STAGES) & 1u);
+                const uint32_t row = ring_u32 + st * 4096 + lane * 128;
 #pragma unroll
-            for (int c = 0; c < 8; c++) {
-                const uint4 q = lds128(row + ((c ^ (lane & 7)) << 4));
-                const uint32_t wv[4] = {q.x, q.y, q.z, q.w};
-                constexpr int PER = (IN == IN_CF32) ? 2 : 4;     // samples per 16 bytes
+                for (int c = 0; c < 8; c++) {
+                    const uint4 q = lds128(row + ((c ^ (lane & 7)) << 4));
+                    const uint32_t wv[4] = {q.x, q.y, q.z, q.w};
+                    constexpr int PER = (IN == IN_CF32) ? 2 : 4;     // samples per 16 bytes
 #pragma unroll
-                for (int e = 0; e < PER; e++) {
-                    const int i = c * PER + e;                   // sample index within the step
-                    double xa, xb;
-                    if (IN == IN_CF32) sample_to_f64<IN, INJECT>(wv[2 * e], wv[2 * e + 1], xa, xb);
-                    else               sample_to_f64<IN, INJECT>(wv[e], 0u, xa, xb);
-                    // kept iff (step*SPS + i) % D == 0
-                    const bool kept_static = (D <= C::SPS) ? (i % D == 0) : (i == 0);
-                    if (kept_static) {
-                        const bool kept = (D <= C::SPS) ? true : (((step * C::SPS) % D) == 0);
-                        const double ya = filter_step<K, PAR, true>(T, va, xa);
-                        const double yb = filter_step<K, PAR, true>(T, vb, xb);
-                        if (kept) {
-                            const int m = (step * C::SPS + i) / D;
-                            sts64(ystage + ((m * 2 + 0) * 32 + lane) * 8, ya);
-                            sts64(ystage + ((m * 2 + 1) * 32 + lane) * 8, yb);
+                    for (int e = 0; e < PER; e++) {
+                        const int i = c * PER + e;                   // sample index within the step
+                        double xa, xb;
+                        if (INJECT) {
+                            inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
+                        } else if (IN == IN_CF32) {
+                            sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
+                        } else {
+                            sample_to_f64<IN, false>(wv[e], 0u, xa, xb);
                         }
-                    } else {
-                        filter_step<K, PAR, false>(T, va, xa);
-                        filter_step<K, PAR, false>(T, vb, xb);
+                        // kept iff (step*SPS + i) % D == 0
+                        const bool kept_static = (D <= C::SPS) ? (i % D == 0) : (i == 0);
+                        if (kept_static) {
+                            const bool kept = (D <= C::SPS) ? true : (((step * C::SPS) % D) == 0);
+                            const double ya = filter_step<K, PAR, true>(T, va, xa);
+                            const double yb = filter_step<K, PAR, true>(T, vb, xb);
+                            if (kept) {
+                                const int m = (step * C::SPS + i) / D;
+                                sts64(ystage + ((m * 2 + 0) * 32 + lane) * 8, ya);
+                                sts64(ystage + ((m * 2 + 1) * 32 + lane) * 8, yb);
+                            }
+                        } else {
+                            filter_step<K, PAR, false>(T, va, xa);
+                            filter_step<K, PAR, false>(T, vb, xb);
+                        }
                     }
                 }
+                __syncwarp();
+                if (lane == 0) {
+                    const int ls = step + C::STAGES;                 // the box that follows the ones in flight
+                    if (ls < C::NSTEP) issue(tile, ls, st);
+                    else if (next < P.total_tiles) issue(next, ls - C::NSTEP, st);
+                }
+                gstep++;
             }
-            __syncwarp();
-            if (lane == 0) {
-                const int ls = step + C::STAGES;                 // the box that follows the ones in flight
-                if (ls < C::NSTEP) issue(tile, ls, st);
-                else if (next < P.total_tiles) issue(next, ls - C::NSTEP, st);
-            }
-            gstep++;
-        }
-        next = __shfl_sync(0xffffffffu, next, 0);
+            next = __shfl_sync(0xffffffffu, next, 0);
 
-        // ---- phase 2: warp scan of run end states: E_t = sum_{j<=t} M^(t-j) f_j
-        double f[2][S];
+            // ---- phase 2: warp scan of run end states: E_t = sum_{j<=t} M^(t-j) f_j
 #pragma unroll
-        for (int k = 0; k < K; k++) {
-            f[0][2 * k] = va[k][0] - T.sbias[2 * k]; f[0][2 * k + 1] = va[k][1] - T.sbias[2 * k + 1];
-            f[1][2 * k] = vb[k][0] - T.sbias[2 * k]; f[1][2 * k + 1] = vb[k][1] - T.sbias[2 * k + 1];
-        }
+            for (int k = 0; k < K; k++) {
+                f[0][2 * k] = va[k][0] - T.sbias[2 * k]; f[0][2 * k + 1] = va[k][1] - T.sbias[2 * k + 1];
+                f[1][2 * k] = vb[k][0] - T.sbias[2 * k]; f[1][2 * k + 1] = vb[k][1] - T.sbias[2 * k + 1];
+            }
 #pragma unroll
-        for (int j = 0; j < 5; j++) {
-            const int d = 1 << j;
-            double g[2][S];
-#pragma unroll
-            for (int r = 0; r < 2; r++)
-#pragma unroll
-                for (int c = 0; c < S; c++) g[r][c] = shfl_up_f64(f[r][c], d);
-            if (lane >= d) {
+            for (int j = 0; j < 5; j++) {
+                const int d = 1 << j;
+                double g[2][S];
 #pragma unroll
                 for (int r = 0; r < 2; r++)
 #pragma unroll
-                    for (int row = 0; row < S; row++) {
-                        double acc = f[r][row];
+                    for (int c = 0; c < S; c++) g[r][c] = shfl_up_f64(f[r][c], d);
+                if (lane >= d) {
 #pragma unroll
-                        for (int col = col_lo<PAR>(row); col < col_hi(row); col++) acc = fma(T.Mp[j][row * S + col], g[r][col], acc);
-                        f[r][row] = acc;
-                    }
+                    for (int r = 0; r < 2; r++)
+#pragma unroll
+                        for (int row = 0; row < S; row++) {
+                            double acc = f[r][row];
+#pragma unroll
+                            for (int col = col_lo<PAR>(row); col < col_hi(row); col++) acc = fma(T.Mp[j][row * S + col], g[r][col], acc);
+                            f[r][row] = acc;
+                        }
+                }
+            }
+            // f = inclusive scan value E_lane.  Lane 31 holds the tile aggregate.
+            if (lane == 31 && !P.chained) {
+                double* agg = P.desc_agg + (size_t)tile * (2 * S);
+#pragma unroll
+                for (int r = 0; r < 2; r++)
+#pragma unroll
+                    for (int c = 0; c < S; c++) st_desc(agg + r * S + c, f[r][c]);
             }
         }
-        // f = inclusive scan value E_lane.  Lane 31 holds the tile aggregate.
-        if (lane == 31 && !P.chained) {
-            double* agg = P.desc_agg + (size_t)tile * (2 * S);
+
+        // ---- the owed tile: decoupled look-back, then phase 3 out of the other half of the output stage
+        if (owe) {
+            const uint32_t ystage = ystage0 + (buf ^ 1u) * C::YSTAGE_BYTES;
+            const uint32_t stream = ptile / P.tiles_per_stream;
+            const uint32_t tis = ptile - stream * P.tiles_per_stream;       // tile index within the stream
+            // state entering the tile, component `lane` (< 2S) per lane
+            const int comp = lane < 2 * S ? lane : 0;
+            const int crail = comp / S, crow = comp % S;
+            if (lane < 2 * S) {
+                double sin_c = 0.0;
+                if (tis == 0) {
+                    sin_c = P.state_in[(size_t)stream * (2 * S) + (crail ^ swap) * S + crow];
+                } else if (P.chained) {
+                    sin_c = wait_desc(P.desc_incl + (size_t)(ptile - 1) * (2 * S) + comp);
+                } else {
+                    const int depth = (int)tis < P.window ? (int)tis : P.window;
+                    sin_c = wait_desc(P.desc_agg + (size_t)(ptile - 1) * (2 * S) + comp);     // M_tile^0 = I
+                    for (int j = 2; j <= depth; j++) {
+                        const double* a = P.desc_agg + (size_t)(ptile - j) * (2 * S) + crail * S;
+                        const double* mp = P.mtile_pow + (size_t)(j - 1) * (S * S) + crow * S;
+#pragma unroll
+                        for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), wait_desc(a + col), sin_c);
+                    }
+                    if ((int)tis <= P.window) {     // the window reaches the start of the stream
+                        const double* a = P.state_in + (size_t)stream * (2 * S) + (crail ^ swap) * S;
+                        const double* mp = P.mtile_pow + (size_t)tis * (S * S) + crow * S;
+#pragma unroll
+                        for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), __ldg(a + col), sin_c);
+                    }
+                }
+                sts64(scratch + lane * 8, sin_c);
+            }
+            __syncwarp();
+            double sin[2][S];
 #pragma unroll
             for (int r = 0; r < 2; r++)
 #pragma unroll
-                for (int c = 0; c < S; c++) st_desc(agg + r * S + c, f[r][c]);
-        }
+                for (int c = 0; c < S; c++) sin[r][c] = lds64(scratch + (r * S + c) * 8);
 
-        // ---- decoupled look-back: state entering this tile, component `lane` (< 2S) per lane
-        const int comp = lane < 2 * S ? lane : 0;
-        const int crail = comp / S, crow = comp % S;
-        double sin_c = 0.0;
-        if (lane < 2 * S) {
-            if (tis == 0) {
-                sin_c = P.state_in[(size_t)stream * (2 * S) + (crail ^ swap) * S + crow];
-            } else if (P.chained) {
-                sin_c = wait_desc(P.desc_incl + (size_t)(tile - 1) * (2 * S) + comp);
-            } else {
-                const int depth = (int)tis < P.window ? (int)tis : P.window;
-                sin_c = wait_desc(P.desc_agg + (size_t)(tile - 1) * (2 * S) + comp);     // M_tile^0 = I
-                for (int j = 2; j <= depth; j++) {
-                    const double* a = P.desc_agg + (size_t)(tile - j) * (2 * S) + crail * S;
-                    const double* mp = P.mtile_pow + (size_t)(j - 1) * (S * S) + crow * S;
+            // true state entering this lane's run: s0 = M^lane S_in + E_{lane-1}
+            double s0[2][S];
 #pragma unroll
-                    for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), wait_desc(a + col), sin_c);
-                }
-                if ((int)tis <= P.window) {     // the window reaches the start of the stream
-                    const double* a = P.state_in + (size_t)stream * (2 * S) + (crail ^ swap) * S;
-                    const double* mp = P.mtile_pow + (size_t)tis * (S * S) + crow * S;
-#pragma unroll
-                    for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), __ldg(a + col), sin_c);
-                }
-            }
-            sts64(scratch + lane * 8, sin_c);
-        }
-        __syncwarp();
-        double sin[2][S];
-#pragma unroll
-        for (int r = 0; r < 2; r++)
-#pragma unroll
-            for (int c = 0; c < S; c++) sin[r][c] = lds64(scratch + (r * S + c) * 8);
-
-        // true state entering this lane's run: s0 = M^lane S_in + E_{lane-1}
-        double s0[2][S];
-#pragma unroll
-        for (int r = 0; r < 2; r++)
-#pragma unroll
-            for (int c = 0; c < S; c++) {
-                const double e = shfl_up_f64(f[r][c], 1);
-                s0[r][c] = lane == 0 ? 0.0 : e;
-            }
-#pragma unroll
-        for (int row = 0; row < S; row++)
-#pragma unroll
-            for (int col = col_lo<PAR>(row); col < col_hi(row); col++) {
-                const double m = pl[row][col - col_lo<PAR>(row)];
-                s0[0][row] = fma(m, sin[0][col], s0[0][row]);
-                s0[1][row] = fma(m, sin[1][col], s0[1][row]);
-            }
-
-        // true end state of the tile (chained mode) / of the stream (last tile)
-        const bool last_tile = (tis == P.tiles_per_stream - 1);
-        if (P.chained || (last_tile && P.write_state)) {
-            const int lastl = last_tile && P.write_state ? (int)P.last_tile_runs - 1 : 31;
-            // state after run `lastl`: M^(lastl+1) S_in + E_lastl, evaluated by lane lastl
-            if (lane == lastl) {
-                double* incl = P.desc_incl + (size_t)tile * (2 * S);
-#pragma unroll
-                for (int row = 0; row < S; row++) {
-                    double ea = f[0][row], eb = f[1][row];
-#pragma unroll
-                    for (int col = col_lo<PAR>(row); col < col_hi(row); col++) {
-                        const double m = __ldg(P.plane + (row * S + col) * 33 + lastl + 1);
-                        ea = fma(m, sin[0][col], ea);
-                        eb = fma(m, sin[1][col], eb);
-                    }
-                    if (P.chained) { st_desc(incl + row, ea); st_desc(incl + S + row, eb); }
-                    if (last_tile && P.write_state) {
-                        P.state_out[(size_t)stream * (2 * S) + (0 ^ swap) * S + row] = ea;
-                        P.state_out[(size_t)stream * (2 * S) + (1 ^ swap) * S + row] = eb;
-                    }
-                }
-            }
-        }
-
-        // ---- phase 3: correct the staged outputs and store (decimation already applied)
-        const uint32_t run = (uint32_t)run0 + lane;
-        if (run < P.n_runs) {
-            const uint64_t o0 = (uint64_t)stream * P.out_stride + (uint64_t)run * C::NK;
-#pragma unroll 4
-            for (int m = 0; m < C::NK; m++) {
-                double ya = lds64(ystage + ((m * 2 + 0) * 32 + lane) * 8);
-                double yb = lds64(ystage + ((m * 2 + 1) * 32 + lane) * 8);
+            for (int r = 0; r < 2; r++)
 #pragma unroll
                 for (int c = 0; c < S; c++) {
-                    ya = fma(T.R[m][c], s0[0][c], ya);
-                    yb = fma(T.R[m][c], s0[1][c], yb);
+                    const double e = shfl_up_f64(pf[r][c], 1);
+                    s0[r][c] = lane == 0 ? 0.0 : e;
                 }
-                ya = fma(ya, T.gain, T.out_bias);
-                yb = fma(yb, T.gain, T.out_bias);
-                const double yi = swap ? yb : ya, yq = swap ? ya : yb;
-                const uint64_t o = o0 + m;
-                if (P.out_mode == OUT_F32) {
-                    __stcs(reinterpret_cast<float2*>(P.out) + o, make_float2((float)yi, (float)yq));
-                } else if (P.out_mode == OUT_F64) {
-                    __stcs(reinterpret_cast<double2*>(P.out) + o, make_double2(yi, yq));
-                } else {
-                    // (int16_t)(float)y, CaribouliteStream.cpp:295-296: round to float, truncate toward zero
-                    const int qi = (int)(int16_t)__float2int_rz((float)yi);
-                    const int qq = (int)(int16_t)__float2int_rz((float)yq);
-                    if (P.out_mode == OUT_Q16_CS16) {
-                        reinterpret_cast<uint32_t*>(P.out)[o] = ((uint32_t)qi & 0xFFFFu) | ((uint32_t)qq << 16);
-                    } else if (P.out_mode == OUT_Q16_CF32) {
-                        __stcs(reinterpret_cast<float2*>(P.out) + o,
-                               make_float2((float)qi * (1.0f / 4096.0f), (float)qq * (1.0f / 4096.0f)));
-                    } else if (P.out_mode == OUT_Q16_CF64) {
-                        __stcs(reinterpret_cast<double2*>(P.out) + o,
-                               make_double2((double)qi * (1.0 / 4096.0), (double)qq * (1.0 / 4096.0)));
-                    } else {   // OUT_Q16_CS8, CaribouliteStream.cpp:362-363
-                        reinterpret_cast<uint16_t*>(P.out)[o] =
-                            (uint16_t)(((uint32_t)(qi >> 5) & 0xFFu) | (((uint32_t)(qq >> 5) & 0xFFu) << 8));
+#pragma unroll
+            for (int row = 0; row < S; row++)
+#pragma unroll
+                for (int col = col_lo<PAR>(row); col < col_hi(row); col++) {
+                    const double m = pl[row][col - col_lo<PAR>(row)];
+                    s0[0][row] = fma(m, sin[0][col], s0[0][row]);
+                    s0[1][row] = fma(m, sin[1][col], s0[1][row]);
+                }
+
+            // true end state of the tile (chained mode) / of the stream (last tile)
+            const bool last_tile = (tis == P.tiles_per_stream - 1);
+            if (P.chained || (last_tile && P.write_state)) {
+                const int lastl = last_tile && P.write_state ? (int)P.last_tile_runs - 1 : 31;
+                // state after run `lastl`: M^(lastl+1) S_in + E_lastl, evaluated by lane lastl
+                if (lane == lastl) {
+                    double* incl = P.desc_incl + (size_t)ptile * (2 * S);
+#pragma unroll
+                    for (int row = 0; row < S; row++) {
+                        double ea = pf[0][row], eb = pf[1][row];
+#pragma unroll
+                        for (int col = col_lo<PAR>(row); col < col_hi(row); col++) {
+                            const double m = __ldg(P.plane + (row * S + col) * 33 + lastl + 1);
+                            ea = fma(m, sin[0][col], ea);
+                            eb = fma(m, sin[1][col], eb);
+                        }
+                        if (P.chained) { st_desc(incl + row, ea); st_desc(incl + S + row, eb); }
+                        if (last_tile && P.write_state) {
+                            P.state_out[(size_t)stream * (2 * S) + (0 ^ swap) * S + row] = ea;
+                            P.state_out[(size_t)stream * (2 * S) + (1 ^ swap) * S + row] = eb;
+                        }
                     }
                 }
             }
+
+            // ---- phase 3: correct the staged outputs and store (decimation already applied)
+            const uint32_t run = tis * 32u + lane;
+            if (run < P.n_runs) {
+                const uint64_t o0 = (uint64_t)stream * P.out_stride + (uint64_t)run * C::NK;
+#pragma unroll 4
+                for (int m = 0; m < C::NK; m++) {
+                    double ya = lds64(ystage + ((m * 2 + 0) * 32 + lane) * 8);
+                    double yb = lds64(ystage + ((m * 2 + 1) * 32 + lane) * 8);
+#pragma unroll
+                    for (int c = 0; c < S; c++) {
+                        ya = fma(T.R[m][c], s0[0][c], ya);
+                        yb = fma(T.R[m][c], s0[1][c], yb);
+                    }
+                    ya = fma(ya, T.gain, T.out_bias);
+                    yb = fma(yb, T.gain, T.out_bias);
+                    const double yi = swap ? yb : ya, yq = swap ? ya : yb;
+                    const uint64_t o = o0 + m;
+                    if (P.out_mode == OUT_F32) {
+                        __stcs(reinterpret_cast<float2*>(P.out) + o, make_float2((float)yi, (float)yq));
+                    } else if (P.out_mode == OUT_F64) {
+                        __stcs(reinterpret_cast<double2*>(P.out) + o, make_double2(yi, yq));
+                    } else {
+                        // (int16_t)(float)y, CaribouliteStream.cpp:295-296: round to float, truncate toward zero
+                        const int qi = (int)(int16_t)__float2int_rz((float)yi);
+                        const int qq = (int)(int16_t)__float2int_rz((float)yq);
+                        if (P.out_mode == OUT_Q16_CS16) {
+                            reinterpret_cast<uint32_t*>(P.out)[o] = ((uint32_t)qi & 0xFFFFu) | ((uint32_t)qq << 16);
+                        } else if (P.out_mode == OUT_Q16_CF32) {
+                            __stcs(reinterpret_cast<float2*>(P.out) + o,
+                                   make_float2((float)qi * (1.0f / 4096.0f), (float)qq * (1.0f / 4096.0f)));
+                        } else if (P.out_mode == OUT_Q16_CF64) {
+                            __stcs(reinterpret_cast<double2*>(P.out) + o,
+                                   make_double2((double)qi * (1.0 / 4096.0), (double)qq * (1.0 / 4096.0)));
+                        } else {   // OUT_Q16_CS8, CaribouliteStream.cpp:362-363
+                            reinterpret_cast<uint16_t*>(P.out)[o] =
+                                (uint16_t)(((uint32_t)(qi >> 5) & 0xFFu) | (((uint32_t)(qq >> 5) & 0xFFu) << 8));
+                        }
+                    }
+                }
+            }
+            __syncwarp();   // this half of the output stage and the scratch are free again
         }
-        __syncwarp();   // ystage / scratch are reused by the next tile
+        if (!have) break;
+        owe = true;
+        ptile = tile;
+#pragma unroll
+        for (int r = 0; r < 2; r++)
+#pragma unroll
+            for (int c = 0; c < S; c++) pf[r][c] = f[r][c];
+        buf ^= 1u;
         tile = next;
     }
 }
