@@ -98,7 +98,10 @@ struct IirTailParams {
 };
 
 // run length for a decimation factor
-__host__ __device__ constexpr int iir_run_len(int D) { return D == 1 ? 32 : (D == 2 ? 64 : 128); }
+#ifndef CBL_IIR_LTMAX
+#define CBL_IIR_LTMAX 128
+#endif
+__host__ __device__ constexpr int iir_run_len(int D) { return D == 1 ? 32 : (D == 2 ? 64 : CBL_IIR_LTMAX); }
 #ifndef CBL_IIR_WPC
 #define CBL_IIR_WPC 3
 #endif
