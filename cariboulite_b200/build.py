@@ -12,7 +12,8 @@ OBJ = os.path.join(HERE, "_obj" + ("_" + VARIANT if VARIANT else ""))
 LIB = os.path.join(HERE, "libcaribou_cuda%s.so" % ("_" + VARIANT if VARIANT else ""))
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-CU = ["unpack.cu", "iir.cu", "iir_k1.cu", "iir_k2.cu", "iir_k3.cu", "iir_k4.cu", "api.cu", "compat.cu"]
+CU = ["unpack.cu", "iir.cu", "iir_k1.cu", "iir_k2.cu", "iir_k3.cu", "iir_k4.cu", "iir_k1y.cu", "iir_k2y.cu", "iir_k3y.cu",
+      "iir_k4y.cu", "api.cu", "compat.cu"]
 CPP = ["tables.cpp"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall"]
 
@@ -46,7 +47,7 @@ def build(force=False, verbose=False):
     if force:
         for f in os.listdir(OBJ):
             os.remove(os.path.join(OBJ, f))
-    with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
+    with ThreadPoolExecutor(max_workers=min(12, len(srcs))) as ex:
         objs = list(ex.map(_compile, srcs))
     if force or not os.path.exists(LIB) or any(os.path.getmtime(o) > os.path.getmtime(LIB) for o in objs):
         cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-lcudart_static", "-lpthread", "-ldl", "-lrt"]

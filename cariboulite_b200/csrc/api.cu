@@ -194,13 +194,16 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
         // (0x413 << 21) | sign bit of the 13-bit field at bits 13:1;  (0x414 << 21) | sign bit of the int16
         p.inj_mul = 1u << 31;
         p.inj_xor = in_kind == IN_WORDS ? 0x82602000u : 0x82808000u;
-        static int occ_cache[kMaxK + 1][33][3][2];
-        int& occ = occ_cache[P.K][P.D][in_kind][P.par ? 1 : 0];
-        if (occ == 0) occ = std::max(1, iir_max_ctas_per_sm(P.K, P.D, in_kind, P.par));
-        const uint64_t want = (total + kIirWarpsPerCta - 1) / kIirWarpsPerCta;
-        const int grid = (int)std::min<uint64_t>(want, (uint64_t)occ * c->num_sms);
+        p.scan_rounds = P.scan_rounds;
+        // CF32 output without int16 truncation: the float-staged kernel (half the shared memory per warp, more
+        // warps per SM).  It stages gain * y_zs, so its R table carries the gain as well.
+        const bool y32 = c->out_mode == OUT_F32 && iir_has_y32(P.K, P.par);
+        IirTables Tl = T;
+        if (y32)
+            for (int m = 0; m < kMaxNK; m++)
+                for (int i = 0; i < kMaxS; i++) Tl.R[m][i] *= T.gain;
         prof_mark(c, 0);
-        const int e = launch_iir(P.K, P.D, in_kind, P.par, tm, p, T, grid, c->stream);
+        const int e = launch_iir(P.K, P.D, in_kind, P.par, y32, tm, p, Tl, c->num_sms, c->stream);
         prof_mark(c, 1);
         if (e != 0) { cuda_ok((cudaError_t)e, "iir_scan_kernel launch"); return CARIBOU_CUDA_ERR; }
         c->launches++;

@@ -3,43 +3,23 @@
 
 namespace cbl {
 
-iir_launch_fn iir_launch_k1(int, int, bool); iir_launch_fn iir_launch_k2(int, int, bool);
-iir_launch_fn iir_launch_k3(int, int, bool); iir_launch_fn iir_launch_k4(int, int, bool);
-iir_occ_fn iir_occ_k1(int, int, bool); iir_occ_fn iir_occ_k2(int, int, bool);
-iir_occ_fn iir_occ_k3(int, int, bool); iir_occ_fn iir_occ_k4(int, int, bool);
+iir_launch_fn iir_launch_k1(int, int, bool, bool); iir_launch_fn iir_launch_k2(int, int, bool, bool);
+iir_launch_fn iir_launch_k3(int, int, bool, bool); iir_launch_fn iir_launch_k4(int, int, bool, bool);
 
-size_t iir_smem_bytes(int K, int D, int in_kind)
-{
-    const int LT = iir_run_len(D), NK = LT / D, SPS = in_kind == IN_CF32 ? 16 : 32;
-    const int nstep = LT / SPS, stages = nstep < kIirRingStages ? nstep : kIirRingStages;
-    const int warp_bytes = stages * 4096 + 2 * (NK * 2 * 32 * 8) + 2 * (2 * K) * 8 * 2;
-    return (size_t)kIirWarpsPerCta * warp_bytes + kIirWarpsPerCta * stages * 8 + 1024;
-}
+bool iir_has_y32(int K, bool par) { return K == 1 || par; }
 
-int launch_iir(int K, int D, int in_kind, bool par, const CUtensorMap& tmap, const IirParams& p, const IirTables& t,
-               int grid_ctas, cudaStream_t st)
+int launch_iir(int K, int D, int in_kind, bool par, bool y32, const CUtensorMap& tmap, const IirParams& p,
+               const IirTables& t, int num_sms, cudaStream_t st)
 {
     iir_launch_fn fn = nullptr;
     switch (K) {
-        case 1: fn = iir_launch_k1(D, in_kind, par); break;
-        case 2: fn = iir_launch_k2(D, in_kind, par); break;
-        case 3: fn = iir_launch_k3(D, in_kind, par); break;
-        case 4: fn = iir_launch_k4(D, in_kind, par); break;
+        case 1: fn = iir_launch_k1(D, in_kind, par, y32); break;
+        case 2: fn = iir_launch_k2(D, in_kind, par, y32); break;
+        case 3: fn = iir_launch_k3(D, in_kind, par, y32); break;
+        case 4: fn = iir_launch_k4(D, in_kind, par, y32); break;
     }
     if (!fn) return (int)cudaErrorInvalidValue;
-    return fn(tmap, p, t, grid_ctas, st);
-}
-
-int iir_max_ctas_per_sm(int K, int D, int in_kind, bool par)
-{
-    iir_occ_fn fn = nullptr;
-    switch (K) {
-        case 1: fn = iir_occ_k1(D, in_kind, par); break;
-        case 2: fn = iir_occ_k2(D, in_kind, par); break;
-        case 3: fn = iir_occ_k3(D, in_kind, par); break;
-        case 4: fn = iir_occ_k4(D, in_kind, par); break;
-    }
-    return fn ? fn() : 0;
+    return fn(tmap, p, t, num_sms, st);
 }
 
 // ------------------------------------------------------------------ sequential tail

@@ -83,6 +83,7 @@ struct IirParams {
     const int32_t* gate;        // optional: the launch is a no-op when *gate != 0 (misaligned capture)
     // mantissa injection (iir_kernel.cuh inject_f64): sign-flip | exponent << 1 word, and the multiplier 2^31
     uint32_t  inj_xor, inj_mul;
+    int       scan_rounds;      // Kogge-Stone rounds of the warp scan that can still contribute (<= 5)
 };
 
 struct IirTailParams {
@@ -108,8 +109,16 @@ __host__ __device__ constexpr int iir_run_len(int D) { return D == 1 ? 32 : (D =
 #ifndef CBL_IIR_STAGES
 #define CBL_IIR_STAGES 2
 #endif
-constexpr int kIirWarpsPerCta = CBL_IIR_WPC;
+#ifndef CBL_IIR_WPC32
+#define CBL_IIR_WPC32 4
+#endif
+#ifndef CBL_IIR_STAGES32
+#define CBL_IIR_STAGES32 1
+#endif
+constexpr int kIirWarpsPerCta = CBL_IIR_WPC;        // double-staged kernels: 3 warps x ~25 KiB, 3 CTAs per SM
 constexpr int kIirRingStages  = CBL_IIR_STAGES;
+constexpr int kIirWarpsPerCta32 = CBL_IIR_WPC32;    // float-staged kernels: 4 warps x ~12 KiB, 4 CTAs per SM
+constexpr int kIirRingStages32  = CBL_IIR_STAGES32;
 // look-back descriptors: a slot holds this bit pattern (a NaN no computation produces) until its owner
 // has written it; a value that happens to equal it is nudged to the neighbouring NaN pattern
 constexpr unsigned long long kDescEmpty = 0xFFFFFFFFFFFFFFFFull;
@@ -117,11 +126,10 @@ constexpr unsigned long long kDescEmpty = 0xFFFFFFFFFFFFFFFFull;
 constexpr double kBiasWords = 1052672.0;   // 2^20 + 2^12
 constexpr double kBiasCs16  = 2129920.0;   // 2^21 + 2^15
 
-size_t iir_smem_bytes(int K, int D, int in_kind);
-// returns cudaError_t as int
-int launch_iir(int K, int D, int in_kind, bool par, const CUtensorMap& tmap, const IirParams& p, const IirTables& t,
-               int grid_ctas, cudaStream_t st);
-int iir_max_ctas_per_sm(int K, int D, int in_kind, bool par);
+// returns cudaError_t as int; y32 selects the float-staged kernel (iir_has_y32 says whether one exists)
+bool iir_has_y32(int K, bool par);
+int launch_iir(int K, int D, int in_kind, bool par, bool y32, const CUtensorMap& tmap, const IirParams& p,
+               const IirTables& t, int num_sms, cudaStream_t st);
 void launch_iir_tail(const IirTailParams& p, cudaStream_t st);
 // state <- state_next (n doubles) unless *gate != 0
 void launch_commit_state(double* state, const double* state_next, size_t n, const int32_t* gate, cudaStream_t st);

@@ -1,0 +1,5 @@
+// Kernel (b) instantiations for cascades of 3 biquad(s), float-staged (CF32 output without int16 truncation).
+#include "iir_kernel.cuh"
+namespace cbl {
+iir_launch_fn iir_launch_k3y(int D, int in_kind, bool par) { return iir_pick_launch<3, true>(D, in_kind, par); }
+}

@@ -19,6 +19,18 @@
 // behind, which otherwise synchronises all warps of the GPU into one convoy.
 #pragma once
 #include "iir.cuh"
+#ifndef CBL_P3_UNROLL
+#define CBL_P3_UNROLL 2
+#endif
+#ifndef CBL_P1_UNROLL
+#define CBL_P1_UNROLL 8
+#endif
+#ifdef CBL_NO_FASTPATH
+namespace cbl { constexpr int kP3GenUnroll = 4; }
+#else
+namespace cbl { constexpr int kP3GenUnroll = 1; }
+#endif
+namespace cbl { constexpr int kP3Unroll = CBL_P3_UNROLL; constexpr int kP1Unroll = CBL_P1_UNROLL; }
 
 namespace cbl {
 
@@ -62,6 +74,14 @@ __device__ __forceinline__ void st_desc(double* p, double x)
     if (v == kDescEmpty) v = kDescEmpty - 1;      // still a NaN, no longer "empty"
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+// ticket: plain PTX atomic (atomicAdd() is compiled into a warp-aggregated sequence whose shuffle waits for the
+// atomic's round trip on the spot; here the value is not looked at until one tile later)
+__device__ __forceinline__ uint32_t take_ticket(uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("atom.relaxed.gpu.global.add.u32 %0, [%1], 1;" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ double wait_desc(const double* p)
 {
     unsigned long long v = ld_desc(p);
@@ -85,6 +105,16 @@ __device__ __forceinline__ double lds64(uint32_t a)
 __device__ __forceinline__ void sts64(uint32_t a, double v)
 {
     asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory");
+}
+__device__ __forceinline__ void sts_f32x2(uint32_t a, float x, float y)
+{
+    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(x), "f"(y) : "memory");
+}
+__device__ __forceinline__ float2 lds_f32x2(uint32_t a)
+{
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a) : "memory");
+    return v;
 }
 __device__ __forceinline__ double shfl_up_f64(double v, int d)
 {
@@ -140,20 +170,27 @@ __device__ __forceinline__ void sample_to_f64(uint32_t w0, uint32_t w1, double& 
     }
 }
 
-template <int K, int D, int IN>
+// Y32: the zero-state outputs are staged as (already scaled) floats instead of doubles - half the shared memory
+// per warp, which buys occupancy; used when the output itself is CF32 without the int16 truncation.
+template <int K, int D, int IN, bool Y32>
 struct IirCfg {
     static constexpr int S     = 2 * K;                       // state dimension per rail
     static constexpr int LT    = iir_run_len(D);              // samples per run
     static constexpr int NK    = LT / D;                      // kept outputs per run
     static constexpr int SPS   = (IN == IN_CF32) ? 16 : 32;   // samples per 128-byte row step
     static constexpr int NSTEP = LT / SPS;
-    static constexpr int STAGES = (NSTEP < kIirRingStages) ? NSTEP : kIirRingStages;
-    static constexpr int WPC   = kIirWarpsPerCta;
+    static constexpr int RSTG  = Y32 ? kIirRingStages32 : kIirRingStages;
+    static constexpr int STAGES = (NSTEP < RSTG) ? NSTEP : RSTG;
+    static constexpr int WPC   = Y32 ? kIirWarpsPerCta32 : kIirWarpsPerCta;
     static constexpr int RING_BYTES    = STAGES * 4096;
-    static constexpr int YSTAGE_BYTES  = NK * 2 * 32 * 8;      // one tile's zero-state outputs; two of them per warp
+    static constexpr int YSLOT_BYTES   = Y32 ? 256 : 512;      // one kept output of all 32 lanes: float2 / 2 doubles each
+    static constexpr int YSTAGE_BYTES  = NK * YSLOT_BYTES;     // one tile's zero-state outputs; two of them per warp
     static constexpr int SCRATCH_BYTES = 2 * S * 8 * 2;        // S_in broadcast + spare
     static constexpr int WARP_BYTES = RING_BYTES + 2 * YSTAGE_BYTES + SCRATCH_BYTES;
-    static constexpr int SMEM_BYTES = WPC * WARP_BYTES + WPC * STAGES * 8 + 1024;   // + mbarriers + alignment slack
+#ifndef CBL_EXP_SMEM_PAD
+#define CBL_EXP_SMEM_PAD 0
+#endif
+    static constexpr int SMEM_BYTES = WPC * WARP_BYTES + WPC * STAGES * 8 + 1024 + ((D == 32) ? CBL_EXP_SMEM_PAD : 0);   // + mbarriers + alignment slack
 };
 
 // One filter step on one rail.  v = (v1,v2) per section.  Returns y/G at this sample if NEED_OUT.
@@ -189,12 +226,12 @@ __device__ __forceinline__ double filter_step(const IirTables& T, double (&v)[K]
 template <bool PAR> __device__ __forceinline__ constexpr int col_lo(int row) { return PAR ? 2 * (row / 2) : 0; }
 __device__ __forceinline__ constexpr int col_hi(int row) { return 2 * (row / 2 + 1); }
 
-template <int K, int D, int IN, bool PAR>
-__global__ void __launch_bounds__(kIirWarpsPerCta * 32)
+template <int K, int D, int IN, bool PAR, bool Y32>
+__global__ void __launch_bounds__((IirCfg<K, D, IN, Y32>::WPC) * 32)
 iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ IirParams P,
                 const __grid_constant__ IirTables T)
 {
-    using C = IirCfg<K, D, IN>;
+    using C = IirCfg<K, D, IN, Y32>;
     constexpr int S = C::S;
     constexpr bool INJECT = PAR && IN != IN_CF32;
     extern __shared__ uint8_t smem_raw[];
@@ -217,6 +254,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     if (P.gate != nullptr && __ldg(P.gate) != 0) return;
 
     const int swap = (IN == IN_WORDS) ? P.layout : 0;     // rail A carries Q instead of I
+    const uint32_t tps = P.tiles_per_stream;
 
     // this lane's M^lane, non-zero pattern only (s0 = M^lane S_in + E_{lane-1})
     constexpr int NPL = PAR ? 2 : S;
@@ -231,28 +269,31 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     // see through, and then splits the LOP3 and the IMAD.WIDE into longer immediate-friendly sequences.
     const uint32_t inj_xor = P.inj_xor, inj_mul = P.inj_mul;
 
-    // request box `lstep` of `tile` into ring slot `slot` (lane 0 only)
-    auto issue = [&](uint32_t tile, int lstep, uint32_t slot) {
-        const uint32_t stream = tile / P.tiles_per_stream;
-        const uint32_t tis = tile - stream * P.tiles_per_stream;
+    // request box `lstep` of tile (stream, tis) into ring slot `slot` (lane 0 only)
+    auto issue = [&](uint32_t stream, uint32_t tis, int lstep, uint32_t slot) {
         mbar_expect_tx(bar_u32 + 8 * slot, 4096);
         tma_load_3d(ring_u32 + slot * 4096, &tmap, lstep * 32, (int)tis * 32, (int)stream, bar_u32 + 8 * slot);
     };
 
+    // Tickets run two tiles ahead: `tile` is being filtered, `next` is already known (its first boxes are
+    // requested while `tile` drains), and the atomic for the tile after that is in flight meanwhile, so
+    // its round trip never sits on the critical path.  next / next2 are meaningful in lane 0 only.
     uint32_t gstep = 0;    // steps consumed by this warp so far (ring position / parity)
-    uint32_t tile = 0;
+    uint32_t tile = 0xFFFFFFFFu, next = 0xFFFFFFFFu;
     if (lane == 0) {
-        tile = atomicAdd(P.ticket, 1u);
-        if (tile < P.total_tiles) {
-#pragma unroll
-            for (int s = 0; s < C::STAGES; s++) issue(tile, s, (uint32_t)s);
-        }
+        tile = take_ticket(P.ticket);
+        next = take_ticket(P.ticket);
     }
     tile = __shfl_sync(0xffffffffu, tile, 0);
+    uint32_t stream = tile / tps, tis = tile - stream * tps;
+    if (lane == 0 && tile < P.total_tiles) {
+#pragma unroll
+        for (int s = 0; s < C::STAGES; s++) issue(stream, tis, s, (uint32_t)s);
+    }
 
     // the tile whose look-back + phase 3 are still owed (one behind the tile in phases 1-2)
     bool owe = false;
-    uint32_t ptile = 0;
+    uint32_t ptile = 0, pstream = 0, ptis = 0;
     double pf[2][S];       // its inclusive scan values E_lane
     uint32_t buf = 0;      // half of the output stage the CURRENT tile writes
 #pragma unroll
@@ -262,15 +303,16 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
 
     for (;;) {
         const bool have = tile < P.total_tiles;
-        uint32_t next = 0xFFFFFFFFu;
+        uint32_t next2 = 0xFFFFFFFFu, nstream = 0, ntis = 0;
         double f[2][S];
+        double va[K][2], vb[K][2];
         if (have) {
-            // the next tile is claimed now; the atomic's round trip hides behind phase 1 (lane 0 keeps it)
-            if (lane == 0) next = atomicAdd(P.ticket, 1u);
+            if (lane == 0) next2 = take_ticket(P.ticket);      // the tile after `next`; consumed one iteration later
+            nstream = next / tps;
+            ntis = next - nstream * tps;
             const uint32_t ystage = ystage0 + buf * C::YSTAGE_BYTES;
 
             // ---- phase 1: zero-state pass over the run (started at s*, see iir.cuh)
-            double va[K][2], vb[K][2];
 #pragma unroll
             for (int k = 0; k < K; k++) {
                 va[k][0] = vb[k][0] = T.sbias[2 * k];
@@ -281,49 +323,79 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                 const uint32_t st = gstep % C::STAGES;
                 mbar_wait(bar_u32 + 8 * st, (gstep / C::STAGES) & 1u);
                 const uint32_t row = ring_u32 + st * 4096 + lane * 128;
+                // the 128-byte row in groups of U 16-byte pieces: the group body is unrolled, the group loop is
+                // not (the whole row unrolled is ~9 KiB of code per kernel, which the instruction cache feels)
+                constexpr int U = kP1Unroll;                     // 16-byte pieces per group
+                constexpr int PER = (IN == IN_CF32) ? 2 : 4;     // samples per 16 bytes
+                constexpr int GS = U * PER;                      // samples per group
+                const uint32_t ylane = ystage + lane * 8;
+#pragma unroll 1
+                for (int co = 0; co < 8 / U; co++) {
+                    const int gbase = step * C::SPS + co * GS;   // first sample of the group within the run
+                    uint4 q[U];
 #pragma unroll
-                for (int c = 0; c < 8; c++) {
-                    const uint4 q = lds128(row + ((c ^ (lane & 7)) << 4));
-                    const uint32_t wv[4] = {q.x, q.y, q.z, q.w};
-                    constexpr int PER = (IN == IN_CF32) ? 2 : 4;     // samples per 16 bytes
+                    for (int ci = 0; ci < U; ci++) q[ci] = lds128(row + (((co * U + ci) ^ (lane & 7)) << 4));
 #pragma unroll
-                    for (int e = 0; e < PER; e++) {
-                        const int i = c * PER + e;                   // sample index within the step
-                        double xa, xb;
-                        if (INJECT) {
-                            inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
-                        } else if (IN == IN_CF32) {
-                            sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
-                        } else {
-                            sample_to_f64<IN, false>(wv[e], 0u, xa, xb);
-                        }
-                        // kept iff (step*SPS + i) % D == 0
-                        const bool kept_static = (D <= C::SPS) ? (i % D == 0) : (i == 0);
-                        if (kept_static) {
-                            const bool kept = (D <= C::SPS) ? true : (((step * C::SPS) % D) == 0);
-                            const double ya = filter_step<K, PAR, true>(T, va, xa);
-                            const double yb = filter_step<K, PAR, true>(T, vb, xb);
-                            if (kept) {
-                                const int m = (step * C::SPS + i) / D;
-                                sts64(ystage + ((m * 2 + 0) * 32 + lane) * 8, ya);
-                                sts64(ystage + ((m * 2 + 1) * 32 + lane) * 8, yb);
+                    for (int ci = 0; ci < U; ci++) {
+                        const uint32_t wv[4] = {q[ci].x, q[ci].y, q[ci].z, q[ci].w};
+#pragma unroll
+                        for (int e = 0; e < PER; e++) {
+                            const int j = ci * PER + e;              // sample index within the group
+                            double xa, xb;
+                            if (INJECT) {
+#ifdef CBL_EXP_NOCONV
+                                xa = __longlong_as_double(((long long)inj_xor << 32) | wv[e]); xb = xa;   // timing experiment only
+#else
+                                inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
+#endif
+                            } else if (IN == IN_CF32) {
+                                sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
+                            } else {
+                                sample_to_f64<IN, false>(wv[e], 0u, xa, xb);
                             }
-                        } else {
-                            filter_step<K, PAR, false>(T, va, xa);
-                            filter_step<K, PAR, false>(T, vb, xb);
+                            // kept iff (gbase + j) % D == 0; gbase is a multiple of GS
+                            const bool kept_static = (D <= GS) ? (j % D == 0) : (j == 0);
+                            if (kept_static) {
+                                const bool kept = (D <= GS) ? true : ((gbase % D) == 0);
+                                const double ya = filter_step<K, PAR, true>(T, va, xa);
+                                const double yb = filter_step<K, PAR, true>(T, vb, xb);
+                                if (kept) {
+                                    // slot m = (gbase + j) / D: 2 rails x 32 lanes x 8 bytes, or 32 lanes x float2
+                                    const uint32_t ya_addr = ylane + (uint32_t)(gbase / D) * C::YSLOT_BYTES + (uint32_t)((D <= GS) ? (j / D) : 0) * C::YSLOT_BYTES;
+                                    if (Y32) {
+                                        sts_f32x2(ya_addr, (float)fma(ya, T.gain, T.out_bias), (float)fma(yb, T.gain, T.out_bias));
+                                    } else {
+                                        sts64(ya_addr, ya);
+                                        sts64(ya_addr + 256, yb);
+                                    }
+                                }
+                            } else {
+                                filter_step<K, PAR, false>(T, va, xa);
+                                filter_step<K, PAR, false>(T, vb, xb);
+                            }
                         }
                     }
                 }
                 __syncwarp();
                 if (lane == 0) {
                     const int ls = step + C::STAGES;                 // the box that follows the ones in flight
-                    if (ls < C::NSTEP) issue(tile, ls, st);
-                    else if (next < P.total_tiles) issue(next, ls - C::NSTEP, st);
+                    if (ls < C::NSTEP) issue(stream, tis, ls, st);
+                    else if (next < P.total_tiles) issue(nstream, ntis, ls - C::NSTEP, st);
                 }
                 gstep++;
             }
-            next = __shfl_sync(0xffffffffu, next, 0);
+        }
 
+        // The owed tile's first look-back descriptor is requested now and looked at after phase 2: its
+        // L2 round trip hides behind the scan.
+        const int comp = lane < 2 * S ? lane : 0;
+        unsigned long long pre = kDescEmpty;
+#ifndef CBL_NO_PREFETCH
+        if (owe && ptis != 0 && lane < 2 * S)
+            pre = ld_desc((P.chained ? P.desc_incl : P.desc_agg) + (size_t)(ptile - 1) * (2 * S) + comp);
+#endif
+
+        if (have) {
             // ---- phase 2: warp scan of run end states: E_t = sum_{j<=t} M^(t-j) f_j
 #pragma unroll
             for (int k = 0; k < K; k++) {
@@ -332,22 +404,28 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             }
 #pragma unroll
             for (int j = 0; j < 5; j++) {
-                const int d = 1 << j;
-                double g[2][S];
-#pragma unroll
-                for (int r = 0; r < 2; r++)
-#pragma unroll
-                    for (int c = 0; c < S; c++) g[r][c] = shfl_up_f64(f[r][c], d);
-                if (lane >= d) {
+#ifdef CBL_NO_ROUNDS
+                {
+#else
+                if (j < P.scan_rounds) {      // later rounds multiply by a matrix that is numerically zero
+#endif
+                    const int d = 1 << j;
+                    double g[2][S];
 #pragma unroll
                     for (int r = 0; r < 2; r++)
 #pragma unroll
-                        for (int row = 0; row < S; row++) {
-                            double acc = f[r][row];
+                        for (int c = 0; c < S; c++) g[r][c] = shfl_up_f64(f[r][c], d);
+                    if (lane >= d) {
 #pragma unroll
-                            for (int col = col_lo<PAR>(row); col < col_hi(row); col++) acc = fma(T.Mp[j][row * S + col], g[r][col], acc);
-                            f[r][row] = acc;
-                        }
+                        for (int r = 0; r < 2; r++)
+#pragma unroll
+                            for (int row = 0; row < S; row++) {
+                                double acc = f[r][row];
+#pragma unroll
+                                for (int col = col_lo<PAR>(row); col < col_hi(row); col++) acc = fma(T.Mp[j][row * S + col], g[r][col], acc);
+                                f[r][row] = acc;
+                            }
+                    }
                 }
             }
             // f = inclusive scan value E_lane.  Lane 31 holds the tile aggregate.
@@ -363,31 +441,37 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
         // ---- the owed tile: decoupled look-back, then phase 3 out of the other half of the output stage
         if (owe) {
             const uint32_t ystage = ystage0 + (buf ^ 1u) * C::YSTAGE_BYTES;
-            const uint32_t stream = ptile / P.tiles_per_stream;
-            const uint32_t tis = ptile - stream * P.tiles_per_stream;       // tile index within the stream
             // state entering the tile, component `lane` (< 2S) per lane
-            const int comp = lane < 2 * S ? lane : 0;
             const int crail = comp / S, crow = comp % S;
             if (lane < 2 * S) {
                 double sin_c = 0.0;
-                if (tis == 0) {
-                    sin_c = P.state_in[(size_t)stream * (2 * S) + (crail ^ swap) * S + crow];
-                } else if (P.chained) {
-                    sin_c = wait_desc(P.desc_incl + (size_t)(ptile - 1) * (2 * S) + comp);
+                if (ptis == 0) {
+                    sin_c = P.state_in[(size_t)pstream * (2 * S) + (crail ^ swap) * S + crow];
                 } else {
-                    const int depth = (int)tis < P.window ? (int)tis : P.window;
-                    sin_c = wait_desc(P.desc_agg + (size_t)(ptile - 1) * (2 * S) + comp);     // M_tile^0 = I
-                    for (int j = 2; j <= depth; j++) {
-                        const double* a = P.desc_agg + (size_t)(ptile - j) * (2 * S) + crail * S;
-                        const double* mp = P.mtile_pow + (size_t)(j - 1) * (S * S) + crow * S;
+                    const double* first = (P.chained ? P.desc_incl : P.desc_agg) + (size_t)(ptile - 1) * (2 * S) + comp;
+                    while (pre == kDescEmpty) { __nanosleep(32); pre = ld_desc(first); }
+                    sin_c = __longlong_as_double((long long)pre);                               // M_tile^0 = I
+                    if (!P.chained) {
+                        const int depth = (int)ptis < P.window ? (int)ptis : P.window;
+                        for (int j = 2; j <= depth; j++) {
+                            const double* a = P.desc_agg + (size_t)(ptile - j) * (2 * S) + crail * S;
+                            const double* mp = P.mtile_pow + (size_t)(j - 1) * (S * S) + crow * S;
+                            // all S loads go out together; tiles this far back are practically always published
+                            unsigned long long dv[S];
 #pragma unroll
-                        for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), wait_desc(a + col), sin_c);
-                    }
-                    if ((int)tis <= P.window) {     // the window reaches the start of the stream
-                        const double* a = P.state_in + (size_t)stream * (2 * S) + (crail ^ swap) * S;
-                        const double* mp = P.mtile_pow + (size_t)tis * (S * S) + crow * S;
+                            for (int col = 0; col < S; col++) dv[col] = ld_desc(a + col);
 #pragma unroll
-                        for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), __ldg(a + col), sin_c);
+                            for (int col = 0; col < S; col++) {
+                                while (dv[col] == kDescEmpty) { __nanosleep(32); dv[col] = ld_desc(a + col); }
+                                sin_c = fma(__ldg(mp + col), __longlong_as_double((long long)dv[col]), sin_c);
+                            }
+                        }
+                        if ((int)ptis <= P.window) {     // the window reaches the start of the stream
+                            const double* a = P.state_in + (size_t)pstream * (2 * S) + (crail ^ swap) * S;
+                            const double* mp = P.mtile_pow + (size_t)ptis * (S * S) + crow * S;
+#pragma unroll
+                            for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), __ldg(a + col), sin_c);
+                        }
                     }
                 }
                 sts64(scratch + lane * 8, sin_c);
@@ -418,7 +502,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                 }
 
             // true end state of the tile (chained mode) / of the stream (last tile)
-            const bool last_tile = (tis == P.tiles_per_stream - 1);
+            const bool last_tile = (ptis == tps - 1);
             if (P.chained || (last_tile && P.write_state)) {
                 const int lastl = last_tile && P.write_state ? (int)P.last_tile_runs - 1 : 31;
                 // state after run `lastl`: M^(lastl+1) S_in + E_lastl, evaluated by lane lastl
@@ -435,49 +519,80 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                         }
                         if (P.chained) { st_desc(incl + row, ea); st_desc(incl + S + row, eb); }
                         if (last_tile && P.write_state) {
-                            P.state_out[(size_t)stream * (2 * S) + (0 ^ swap) * S + row] = ea;
-                            P.state_out[(size_t)stream * (2 * S) + (1 ^ swap) * S + row] = eb;
+                            P.state_out[(size_t)pstream * (2 * S) + (0 ^ swap) * S + row] = ea;
+                            P.state_out[(size_t)pstream * (2 * S) + (1 ^ swap) * S + row] = eb;
                         }
                     }
                 }
             }
 
-            // ---- phase 3: correct the staged outputs and store (decimation already applied)
-            const uint32_t run = tis * 32u + lane;
+            // ---- phase 3: correct the staged outputs and store (decimation already applied).
+            // The I/Q <-> rail A/B assignment is resolved once per tile, not once per output.
+            const uint32_t run = ptis * 32u + lane;
             if (run < P.n_runs) {
-                const uint64_t o0 = (uint64_t)stream * P.out_stride + (uint64_t)run * C::NK;
-#pragma unroll 4
-                for (int m = 0; m < C::NK; m++) {
-                    double ya = lds64(ystage + ((m * 2 + 0) * 32 + lane) * 8);
-                    double yb = lds64(ystage + ((m * 2 + 1) * 32 + lane) * 8);
+                double si[S], sq[S];
 #pragma unroll
-                    for (int c = 0; c < S; c++) {
-                        ya = fma(T.R[m][c], s0[0][c], ya);
-                        yb = fma(T.R[m][c], s0[1][c], yb);
+                for (int c = 0; c < S; c++) { si[c] = swap ? s0[1][c] : s0[0][c]; sq[c] = swap ? s0[0][c] : s0[1][c]; }
+                const uint32_t yi0 = ystage + ((swap ? 32 : 0) + lane) * 8, yq0 = ystage + ((swap ? 0 : 32) + lane) * 8;
+                const uint64_t o0 = (uint64_t)pstream * P.out_stride + (uint64_t)run * C::NK;
+                if (Y32) {
+                    // staged values are gain * y_zs already, T.R is gain * R (run_iir scales it for these launches)
+                    float2* o = reinterpret_cast<float2*>(P.out) + o0;
+#pragma unroll (kP3Unroll)
+                    for (int m = 0; m < C::NK; m++) {
+                        const float2 z = lds_f32x2(ystage + m * 256 + lane * 8);
+                        double yi = swap ? (double)z.y : (double)z.x, yq = swap ? (double)z.x : (double)z.y;
+#pragma unroll
+                        for (int c = 0; c < S; c++) {
+                            yi = fma(T.R[m][c], si[c], yi);
+                            yq = fma(T.R[m][c], sq[c], yq);
+                        }
+                        __stcs(o + m, make_float2((float)yi, (float)yq));
                     }
-                    ya = fma(ya, T.gain, T.out_bias);
-                    yb = fma(yb, T.gain, T.out_bias);
-                    const double yi = swap ? yb : ya, yq = swap ? ya : yb;
-                    const uint64_t o = o0 + m;
-                    if (P.out_mode == OUT_F32) {
-                        __stcs(reinterpret_cast<float2*>(P.out) + o, make_float2((float)yi, (float)yq));
-                    } else if (P.out_mode == OUT_F64) {
-                        __stcs(reinterpret_cast<double2*>(P.out) + o, make_double2(yi, yq));
-                    } else {
-                        // (int16_t)(float)y, CaribouliteStream.cpp:295-296: round to float, truncate toward zero
-                        const int qi = (int)(int16_t)__float2int_rz((float)yi);
-                        const int qq = (int)(int16_t)__float2int_rz((float)yq);
-                        if (P.out_mode == OUT_Q16_CS16) {
-                            reinterpret_cast<uint32_t*>(P.out)[o] = ((uint32_t)qi & 0xFFFFu) | ((uint32_t)qq << 16);
-                        } else if (P.out_mode == OUT_Q16_CF32) {
-                            __stcs(reinterpret_cast<float2*>(P.out) + o,
-                                   make_float2((float)qi * (1.0f / 4096.0f), (float)qq * (1.0f / 4096.0f)));
-                        } else if (P.out_mode == OUT_Q16_CF64) {
-                            __stcs(reinterpret_cast<double2*>(P.out) + o,
-                                   make_double2((double)qi * (1.0 / 4096.0), (double)qq * (1.0 / 4096.0)));
-                        } else {   // OUT_Q16_CS8, CaribouliteStream.cpp:362-363
-                            reinterpret_cast<uint16_t*>(P.out)[o] =
-                                (uint16_t)(((uint32_t)(qi >> 5) & 0xFFu) | (((uint32_t)(qq >> 5) & 0xFFu) << 8));
+                } else if (P.out_mode == OUT_F32) {
+                    float2* o = reinterpret_cast<float2*>(P.out) + o0;
+#pragma unroll (kP3Unroll)
+                    for (int m = 0; m < C::NK; m++) {
+                        double yi = lds64(yi0 + m * 512), yq = lds64(yq0 + m * 512);
+#pragma unroll
+                        for (int c = 0; c < S; c++) {
+                            yi = fma(T.R[m][c], si[c], yi);
+                            yq = fma(T.R[m][c], sq[c], yq);
+                        }
+                        yi = fma(yi, T.gain, T.out_bias);
+                        yq = fma(yq, T.gain, T.out_bias);
+                        __stcs(o + m, make_float2((float)yi, (float)yq));
+                    }
+                } else if (!Y32) {
+#pragma unroll (kP3GenUnroll)
+                    for (int m = 0; m < C::NK; m++) {
+                        double yi = lds64(yi0 + m * 512), yq = lds64(yq0 + m * 512);
+#pragma unroll
+                        for (int c = 0; c < S; c++) {
+                            yi = fma(T.R[m][c], si[c], yi);
+                            yq = fma(T.R[m][c], sq[c], yq);
+                        }
+                        yi = fma(yi, T.gain, T.out_bias);
+                        yq = fma(yq, T.gain, T.out_bias);
+                        const uint64_t o = o0 + m;
+                        if (P.out_mode == OUT_F64) {
+                            __stcs(reinterpret_cast<double2*>(P.out) + o, make_double2(yi, yq));
+                        } else {
+                            // (int16_t)(float)y, CaribouliteStream.cpp:295-296: round to float, truncate toward zero
+                            const int qi = (int)(int16_t)__float2int_rz((float)yi);
+                            const int qq = (int)(int16_t)__float2int_rz((float)yq);
+                            if (P.out_mode == OUT_Q16_CS16) {
+                                reinterpret_cast<uint32_t*>(P.out)[o] = ((uint32_t)qi & 0xFFFFu) | ((uint32_t)qq << 16);
+                            } else if (P.out_mode == OUT_Q16_CF32) {
+                                __stcs(reinterpret_cast<float2*>(P.out) + o,
+                                       make_float2((float)qi * (1.0f / 4096.0f), (float)qq * (1.0f / 4096.0f)));
+                            } else if (P.out_mode == OUT_Q16_CF64) {
+                                __stcs(reinterpret_cast<double2*>(P.out) + o,
+                                       make_double2((double)qi * (1.0 / 4096.0), (double)qq * (1.0 / 4096.0)));
+                            } else {   // OUT_Q16_CS8, CaribouliteStream.cpp:362-363
+                                reinterpret_cast<uint16_t*>(P.out)[o] =
+                                    (uint16_t)(((uint32_t)(qi >> 5) & 0xFFu) | (((uint32_t)(qq >> 5) & 0xFFu) << 8));
+                            }
                         }
                     }
                 }
@@ -486,79 +601,72 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
         }
         if (!have) break;
         owe = true;
-        ptile = tile;
+        ptile = tile; pstream = stream; ptis = tis;
 #pragma unroll
         for (int r = 0; r < 2; r++)
 #pragma unroll
             for (int c = 0; c < S; c++) pf[r][c] = f[r][c];
         buf ^= 1u;
-        tile = next;
+        // lane 0's view of the ticket pipeline becomes everybody's current tile
+        tile = __shfl_sync(0xffffffffu, next, 0);
+        stream = __shfl_sync(0xffffffffu, nstream, 0);
+        tis = __shfl_sync(0xffffffffu, ntis, 0);
+        next = next2;
     }
 }
 
-template <int K, int D, int IN, bool PAR>
-int launch_iir_t(const CUtensorMap& tmap, const IirParams& p, const IirTables& t, int grid, cudaStream_t st)
+// Launches one instantiation on a persistent grid: as many CTAs as fit on the device (occupancy is queried
+// once per instantiation), never more than the tiles need.
+template <int K, int D, int IN, bool PAR, bool Y32>
+int launch_iir_t(const CUtensorMap& tmap, const IirParams& p, const IirTables& t, int num_sms, cudaStream_t st)
 {
-    using C = IirCfg<K, D, IN>;
-    auto kern = iir_scan_kernel<K, D, IN, PAR>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
-    if (e != cudaSuccess) return (int)e;
+    using C = IirCfg<K, D, IN, Y32>;
+    auto kern = iir_scan_kernel<K, D, IN, PAR, Y32>;
+    static int occ = 0;
+    if (occ == 0) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+        if (e != cudaSuccess) return (int)e;
+        int n = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, C::WPC * 32, C::SMEM_BYTES);
+        if (e != cudaSuccess) return (int)e;
+        occ = n > 0 ? n : 1;
+    }
+    const uint64_t want = ((uint64_t)p.total_tiles + C::WPC - 1) / C::WPC;
+    const uint64_t cap = (uint64_t)occ * (uint64_t)num_sms;
+    const int grid = (int)(want < cap ? want : cap);
     kern<<<grid, C::WPC * 32, C::SMEM_BYTES, st>>>(tmap, p, t);
     return (int)cudaGetLastError();
 }
 
-template <int K, int D, int IN, bool PAR>
-int occupancy_iir_t()
-{
-    using C = IirCfg<K, D, IN>;
-    auto kern = iir_scan_kernel<K, D, IN, PAR>;
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
-    int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, C::WPC * 32, C::SMEM_BYTES) != cudaSuccess) return 0;
-    return n;
-}
-
-#define CBL_IIR_DISPATCH_D(KK, IN_, PAR_, CALL)              \
-    switch (D) {                                            \
-        case 1:  return CALL<KK, 1, IN_, PAR_>;              \
-        case 2:  return CALL<KK, 2, IN_, PAR_>;              \
-        case 4:  return CALL<KK, 4, IN_, PAR_>;              \
-        case 8:  return CALL<KK, 8, IN_, PAR_>;              \
-        case 16: return CALL<KK, 16, IN_, PAR_>;             \
-        case 32: return CALL<KK, 32, IN_, PAR_>;             \
-        default: return nullptr;                            \
+#define CBL_IIR_DISPATCH_D(KK, IN_, PAR_, Y32_)                       \
+    switch (D) {                                                     \
+        case 1:  return &launch_iir_t<KK, 1, IN_, PAR_, Y32_>;        \
+        case 2:  return &launch_iir_t<KK, 2, IN_, PAR_, Y32_>;        \
+        case 4:  return &launch_iir_t<KK, 4, IN_, PAR_, Y32_>;        \
+        case 8:  return &launch_iir_t<KK, 8, IN_, PAR_, Y32_>;        \
+        case 16: return &launch_iir_t<KK, 16, IN_, PAR_, Y32_>;       \
+        case 32: return &launch_iir_t<KK, 32, IN_, PAR_, Y32_>;       \
+        default: return nullptr;                                     \
     }
 
 typedef int (*iir_launch_fn)(const CUtensorMap&, const IirParams&, const IirTables&, int, cudaStream_t);
-typedef int (*iir_occ_fn)();
 
-// K == 1 has a single section: the parallel form is the cascade, only the cascade kernel is built
-template <int KK>
+// K == 1 has a single section: the parallel form is the cascade, only the cascade kernel is built.
+// The float-staged (Y32) kernels exist for the preferred realisation only (parallel for K > 1).
+template <int KK, bool Y32>
 iir_launch_fn iir_pick_launch(int D, int in_kind, bool par)
 {
-    if (par && KK > 1) {
-        if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, (KK > 1), &launch_iir_t) }
-        if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, (KK > 1), &launch_iir_t) }
-        if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, (KK > 1), &launch_iir_t) }
+    constexpr bool PREF = KK > 1;        // the realisation AUTO picks when the poles allow it
+    if (par == PREF || (par && KK == 1)) {
+        if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, PREF, Y32) }
+        if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, PREF, Y32) }
+        if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, PREF, Y32) }
         return nullptr;
     }
-    if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, false, &launch_iir_t) }
-    if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, false, &launch_iir_t) }
-    if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, false, &launch_iir_t) }
-    return nullptr;
-}
-template <int KK>
-iir_occ_fn iir_pick_occ(int D, int in_kind, bool par)
-{
-    if (par && KK > 1) {
-        if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, (KK > 1), &occupancy_iir_t) }
-        if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, (KK > 1), &occupancy_iir_t) }
-        if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, (KK > 1), &occupancy_iir_t) }
-        return nullptr;
-    }
-    if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, false, &occupancy_iir_t) }
-    if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, false, &occupancy_iir_t) }
-    if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, false, &occupancy_iir_t) }
+    if (Y32) return nullptr;
+    if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, false, false) }
+    if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, false, false) }
+    if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, false, false) }
     return nullptr;
 }
 

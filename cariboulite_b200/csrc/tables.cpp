@@ -456,11 +456,15 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, 
     }
     // M = A^LT and its powers
     const Mat M = mat_pow(A, (uint64_t)P->LT, S);
+    P->scan_rounds = 5;
     {
         Mat p = M;
         for (int j = 0; j < 5; j++) {
             // Mp is stored with the kernel's fixed leading dimension S (row*S + col)
             for (int i = 0; i < S; i++) for (int c = 0; c < S; c++) P->tables.Mp[j][i * S + c] = (double)p.a[i][c];
+            // Kogge-Stone round j adds M^(2^j) x (the value 2^j lanes below): once that matrix is below 2^-64 of
+            // a typical state, this round and all later ones add nothing representable
+            if (P->scan_rounds == 5 && scaled_norm(p, S, scale) < ldexpl(1.0L, -64)) P->scan_rounds = j;
             p = mat_mul(p, p, S);
         }
     }

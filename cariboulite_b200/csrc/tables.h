@@ -24,6 +24,7 @@ struct FilterPlan {
     long double Trk[kMaxS][kMaxS];// reference state <- kernel state
     std::vector<double> plane;    // [S*S][33]  (M^t)[e] at plane[e*33 + t]
     std::vector<double> mtile_pow;// [window+1][S*S]
+    int scan_rounds = 5;          // Kogge-Stone rounds of the warp scan that can contribute (M^(2^j) not yet negligible)
     int window = 1;               // look-back window J (tiles)
     bool chained = false;         // no useful contraction: serial inclusive chain
     long double A[kMaxS][kMaxS];  // one-sample transition, kernel coordinates
