@@ -1,6 +1,7 @@
 // libcaribou_cuda C ABI (include/caribou_cuda.h): context, submit paths, state, utilities.
 #include <limits.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 #include <algorithm>
 #include <new>
@@ -296,11 +297,15 @@ static int run_unpack(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, s
     const uint32_t ns = (uint32_t)c->cfg.n_streams;
     const int nsub = n_subs_of(c);
     const uint64_t n_raw_words = (nbytes + 3) / 4;
-    const uint64_t n_groups = (n_raw_words + 7) / 8;
-    const uint32_t n_tiles = (uint32_t)((n_groups + kUnpackTileGroups - 1) / kUnpackTileGroups);
+    const uint32_t n_tiles = (uint32_t)((n_raw_words + kUnpackTileWords - 1) / kUnpackTileWords);
     if (n_tiles == 0) return CARIBOU_CUDA_OK;
-    const bool want_flags = o.invalid_idx || o.sync_idx || true;   // counts are always reported
-    if (!c->desc_inv.reserve((size_t)n_tiles * 8) || !c->desc_syn.reserve((size_t)n_tiles * 8)) return CARIBOU_CUDA_ERR;
+    const bool want_flags = getenv("CBL_EXP_NOFLAGS") == nullptr;   // counts are always reported (the switch is a timing experiment)
+    if (n_raw_words > (1ull << 31)) { set_error("unpack: at most 2^31 words per stream and submit"); return CARIBOU_CUDA_ERR; }
+    // per-tile counts, their scan, work list (+ its length); running totals per stream launch
+    if (!c->desc_inv.reserve((size_t)n_tiles * 20 + 16) || !c->desc_syn.reserve(((size_t)ns + 1) * 16)) return CARIBOU_CUDA_ERR;
+    // running (n_invalid, n_sync) after each stream's launch: slot s is read by launch s, slot s + 1 written by it
+    uint64_t* run_totals = c->desc_syn.as<uint64_t>();
+    CBL_CHECK(cudaMemsetAsync(run_totals, 0, 16, c->stream));
     const bool prof = c->profiling && !c->has_filter;
     if (prof) prof_mark(c, 0);
     for (uint32_t st = 0; st < ns; st++) {
@@ -309,7 +314,6 @@ static int run_unpack(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, s
         const uint8_t* sb = reinterpret_cast<const uint8_t*>(d_bytes) + (size_t)st * stride_bytes;
         p.words = reinterpret_cast<const uint32_t*>(sb);
         p.nbytes = nbytes;
-        p.n_groups = n_groups;
         p.B = c->cfg.interleave_block_words;
         p.chunk_bytes = (uint32_t)c->cfg.chunk_bytes;
         p.spc = p.chunk_bytes / 4;
@@ -335,18 +339,18 @@ static int run_unpack(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, s
         p.inv_idx = o.invalid_idx; p.inv_cap = o.invalid_cap;
         p.syn_idx = o.sync_idx; p.syn_cap = o.sync_cap;
         p.index_base = (uint64_t)st * (nbytes / 4);
-        p.desc_inv = c->desc_inv.as<uint64_t>();
-        p.desc_syn = c->desc_syn.as<uint64_t>();
-        p.ticket = c->d_ticket + 1;
-        p.totals = c->d_counters->totals;
+        p.tile_counts = c->desc_inv.as<uint64_t>();
+        p.tile_offsets = p.tile_counts + n_tiles;
+        p.work = reinterpret_cast<uint32_t*>(p.tile_offsets + n_tiles);
+        p.n_work = p.work + n_tiles;
+        p.totals_in = run_totals + 2 * (size_t)st;
+        p.totals_out = run_totals + 2 * (size_t)st + 2;
         p.n_tiles = n_tiles;
         CBL_CHECK(cudaMemsetAsync(c->desc_inv.p, 0, (size_t)n_tiles * 8, c->stream));
-        CBL_CHECK(cudaMemsetAsync(c->desc_syn.p, 0, (size_t)n_tiles * 8, c->stream));
-        CBL_CHECK(cudaMemsetAsync(c->d_ticket + 1, 0, 4, c->stream));
-        launch_unpack(p, c->stream);
-        c->launches++;
+        c->launches += (uint64_t)launch_unpack(p, c->num_sms, c->stream);
     }
     if (prof) prof_mark(c, 1);
+    CBL_CHECK(cudaMemcpyAsync(c->d_counters->totals, run_totals + 2 * (size_t)ns, 16, cudaMemcpyDeviceToDevice, c->stream));
     CBL_CHECK(cudaGetLastError());
     return CARIBOU_CUDA_OK;
 }

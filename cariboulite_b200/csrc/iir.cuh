@@ -110,14 +110,18 @@ __host__ __device__ constexpr int iir_run_len(int D) { return D == 1 ? 32 : (D =
 #define CBL_IIR_STAGES 2
 #endif
 #ifndef CBL_IIR_WPC32
-#define CBL_IIR_WPC32 4
+#define CBL_IIR_WPC32 2
 #endif
 #ifndef CBL_IIR_STAGES32
-#define CBL_IIR_STAGES32 1
+#define CBL_IIR_STAGES32 2
 #endif
+#ifndef CBL_IIR_MINCTAS32
+#define CBL_IIR_MINCTAS32 1
+#endif
+constexpr int kIirMinCtas32 = CBL_IIR_MINCTAS32;    // __launch_bounds__ min CTAs per SM of the float-staged kernels (register cap)
 constexpr int kIirWarpsPerCta = CBL_IIR_WPC;        // double-staged kernels: 3 warps x ~25 KiB, 3 CTAs per SM
 constexpr int kIirRingStages  = CBL_IIR_STAGES;
-constexpr int kIirWarpsPerCta32 = CBL_IIR_WPC32;    // float-staged kernels: 4 warps x ~12 KiB, 4 CTAs per SM
+constexpr int kIirWarpsPerCta32 = CBL_IIR_WPC32;    // float-staged kernels: 2 warps x ~16 KiB, 6 CTAs per SM (sweep: profiles/r1_sweeps.txt)
 constexpr int kIirRingStages32  = CBL_IIR_STAGES32;
 // look-back descriptors: a slot holds this bit pattern (a NaN no computation produces) until its owner
 // has written it; a value that happens to equal it is nudged to the neighbouring NaN pattern

@@ -227,7 +227,7 @@ template <bool PAR> __device__ __forceinline__ constexpr int col_lo(int row) { r
 __device__ __forceinline__ constexpr int col_hi(int row) { return 2 * (row / 2 + 1); }
 
 template <int K, int D, int IN, bool PAR, bool Y32>
-__global__ void __launch_bounds__((IirCfg<K, D, IN, Y32>::WPC) * 32)
+__global__ void __launch_bounds__((IirCfg<K, D, IN, Y32>::WPC) * 32, (Y32 ? kIirMinCtas32 : 1))
 iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ IirParams P,
                 const __grid_constant__ IirTables T)
 {

@@ -160,90 +160,138 @@ __device__ __forceinline__ void emit_group(const UnpackParams& p, int s, uint64_
     }
 }
 
-// ------------------------------------------------------------------ chained scan of flag counts
-__device__ __forceinline__ uint64_t ld_acquire_u64(const uint64_t* p)
-{
-    uint64_t v;
-    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_u64(uint64_t* p, uint64_t v)
-{
-    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-constexpr uint64_t kDescAgg  = 1ull << 62;
-constexpr uint64_t kDescIncl = 2ull << 62;
-constexpr uint64_t kDescVal  = (1ull << 62) - 1;
+// ------------------------------------------------------------------ flag compaction (A10)
+// Flagged words are rare (one sync word per second of signal, invalid headers only on a damaged link), so the
+// decode kernel only COUNTS them per tile - warps that saw a flag add their packed count to the tile's slot,
+// nobody waits for anybody.  A one-CTA scan turns the per-tile counts into list offsets and a work list of the
+// tiles that have anything to emit; those tiles alone are read a second time to write their indices in order.
+__device__ __forceinline__ uint64_t pack_counts(uint32_t inv, uint32_t syn) { return ((uint64_t)inv << 32) | syn; }
 
-// exclusive prefix of `mine` over tiles [0, tile) (+ base for tile 0); publishes this tile's inclusive value
-__device__ uint64_t lookback_count(uint64_t* desc, uint32_t tile, uint64_t mine, uint64_t base)
+// Is every output slot of tile `tile` a plain aligned decode?  True when the tile holds whole raw words only,
+// all chunks it touches (in every sub-stream) have offs == 0, lie before the first un-alignable chunk and the
+// tile does not reach into a sub-stream's partial last word.  Uniform over the CTA.
+__device__ bool tile_is_plain(const UnpackParams& p, uint64_t w0, uint64_t w1)
 {
-    if (tile == 0) {
-        st_release_u64(desc, kDescIncl | (base + mine));
-        return base;
+    if (!p.vec_ok || w1 > (p.nbytes >> 2)) return false;
+    for (int s = 0; s < p.n_subs; s++) {
+        uint64_t j_lo, j_hi;           // (superset of the) output slots of sub-stream s this tile writes
+        if (p.B == 0)      { j_lo = w0; j_hi = w1; }
+        else if (p.B == 1) { j_lo = w0 >> 1; j_hi = (w1 + 1) >> 1; }
+        else               { j_lo = (w0 / (2ull * p.B)) * p.B; j_hi = ((w1 - 1) / (2ull * p.B)) * p.B + p.B; }
+        if (j_hi > (p.sv[s].nbytes >> 2)) return false;
+        const uint64_t c_lo = j_lo / p.spc, c_hi = (j_hi - 1) / p.spc;
+        if (c_hi - c_lo > 3) return false;
+        if ((int64_t)c_hi >= (int64_t)*p.first_bad[s]) return false;
+        for (uint64_t c = c_lo; c <= c_hi; c++)
+            if (p.offs[s][c] != 0) return false;
     }
-    st_release_u64(desc + tile, kDescAgg | mine);
-    uint64_t excl = 0;
-    for (int64_t j = (int64_t)tile - 1; j >= 0; j--) {
-        uint64_t d;
-        do { d = ld_acquire_u64(desc + j); } while ((d >> 62) == 0);
-        excl += d & kDescVal;
-        if ((d >> 62) == 2) break;
-    }
-    st_release_u64(desc + tile, kDescIncl | (excl + mine));
-    return excl;
+    return true;
 }
 
+// plain decode of 4 consecutive samples of sub-stream s from their 4 source words: 128-bit CS16 store, 32-bit
+// meta store, two 128-bit CF32 stores
+__device__ __forceinline__ void emit_plain4(const UnpackParams& p, int s, uint64_t j0, const uint32_t (&w)[4])
+{
+    const int layout = p.layout[s];
+    int i[4], q[4];
+#pragma unroll
+    for (int e = 0; e < 4; e++) decode_iq(w[e], layout, i[e], q[e]);
+    if (p.cs16[s])
+        __stcs(reinterpret_cast<uint4*>(p.cs16[s] + j0),
+               make_uint4(pack_cs16(i[0], q[0]), pack_cs16(i[1], q[1]), pack_cs16(i[2], q[2]), pack_cs16(i[3], q[3])));
+    if (p.meta[s])
+        __stcs(reinterpret_cast<uint32_t*>(p.meta[s] + j0),
+               (w[0] & 1u) | ((w[1] & 1u) << 8) | ((w[2] & 1u) << 16) | ((w[3] & 1u) << 24));
+    if (p.cf32[s]) {
+        const float2 a = to_cf32(i[0], q[0]), b = to_cf32(i[1], q[1]), cc = to_cf32(i[2], q[2]), d = to_cf32(i[3], q[3]);
+        float4* o = reinterpret_cast<float4*>(p.cf32[s] + j0);
+        __stcs(o, make_float4(a.x, a.y, b.x, b.y));
+        __stcs(o + 1, make_float4(cc.x, cc.y, d.x, d.y));
+    }
+}
+
+// A tile is kUnpackTileWords consecutive raw words.  Single-channel and block-interleaved captures are walked
+// in groups of 4 words per thread (one fully coalesced 128-bit load per warp instruction); a word-interleaved
+// capture (B == 1) in groups of 8, which give 4 samples to each channel.
 __global__ void __launch_bounds__(kUnpackThreads) unpack_kernel(const __grid_constant__ UnpackParams p)
 {
-    __shared__ uint32_t s_tile;
-    __shared__ uint32_t s_cnt[kUnpackIters][kUnpackThreads / 32][2];
-    __shared__ uint64_t s_excl[2];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-
-    // tiles are handed out in launch order so that a tile's predecessors are always resident
-    if (threadIdx.x == 0) s_tile = p.want_flags ? atomicAdd(p.ticket, 1u) : blockIdx.x;
+    __shared__ int s_plain;
+    const int lane = threadIdx.x & 31;
+    const uint32_t tile = blockIdx.x;
+    if (threadIdx.x == 0)
+        s_plain = tile_is_plain(p, (uint64_t)tile * kUnpackTileWords, (uint64_t)(tile + 1) * kUnpackTileWords) ? 1 : 0;
     __syncthreads();
-    const uint32_t tile = s_tile;
-
+    const bool plain = s_plain != 0;
+    const uint64_t tile_w0 = (uint64_t)tile * kUnpackTileWords;
     const uint64_t n_raw = p.nbytes >> 2;            // whole raw words
-    uint32_t inv8[kUnpackIters], syn8[kUnpackIters], pre[kUnpackIters];
+    const int W = (p.B == 1) ? 8 : 4;                // words per group
+    const int iters = kUnpackTileWords / (kUnpackThreads * W);
 
+    uint32_t invb[kUnpackMaxIters], synb[kUnpackMaxIters];
 #pragma unroll
-    for (int it = 0; it < kUnpackIters; it++) {
-        const uint64_t g = ((uint64_t)tile * kUnpackIters + it) * kUnpackThreads + threadIdx.x;
-        const uint64_t k0 = g * 8;
-        uint32_t w[8];
-        inv8[it] = syn8[it] = 0; pre[it] = 0;
-        if (g < p.n_groups) {
-            if (k0 + 8 <= n_raw) {
-                const uint4 a = __ldcs(reinterpret_cast<const uint4*>(p.words + k0));
-                const uint4 b = __ldcs(reinterpret_cast<const uint4*>(p.words + k0 + 4));
-                w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
-                w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
-            } else {
+    for (int it = 0; it < kUnpackMaxIters; it++) invb[it] = synb[it] = 0;
+
+    if (plain && W == 4) {
+        // ---- aligned single-channel / block-interleaved tile: nothing to decide per sample
+        uint4 v[kUnpackMaxIters];
 #pragma unroll
-                for (int e = 0; e < 8; e++) w[e] = (k0 + e < n_raw) ? p.words[k0 + e] : 0u;
+        for (int it = 0; it < kUnpackMaxIters; it++)
+            v[it] = __ldcs(reinterpret_cast<const uint4*>(p.words + tile_w0 + ((uint64_t)it * kUnpackThreads + threadIdx.x) * 4));
+#pragma unroll
+        for (int it = 0; it < kUnpackMaxIters; it++) {
+            const uint64_t k0 = tile_w0 + ((uint64_t)it * kUnpackThreads + threadIdx.x) * 4;
+            const uint32_t w[4] = {v[it].x, v[it].y, v[it].z, v[it].w};
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                invb[it] |= (hdr_ok(w[e]) ? 0u : 1u) << e;
+                synb[it] |= (w[e] & 1u) << e;
             }
-            if (p.want_flags) {
+            if (p.B == 0) {
+                emit_plain4(p, 0, k0, w);
+            } else {
+                const uint32_t kk = (uint32_t)k0, blk = kk / p.B;         // at most 2^31 words per launch
+                emit_plain4(p, (int)(blk & 1u), (uint64_t)(blk >> 1) * p.B + (kk - blk * p.B), w);
+            }
+        }
+    } else if (plain) {
+        // ---- aligned word-interleaved tile: even words to S1G, odd words to HiF
 #pragma unroll
-                for (int e = 0; e < 8; e++) {
-                    if (k0 + e < n_raw) {
-                        inv8[it] |= (hdr_ok(w[e]) ? 0u : 1u) << e;
-                        syn8[it] |= (w[e] & 1u) << e;
-                    }
+        for (int it = 0; it < kUnpackMaxIters / 2; it++) {
+            const uint64_t k0 = tile_w0 + ((uint64_t)it * kUnpackThreads + threadIdx.x) * 8;
+            const uint4 a = __ldcs(reinterpret_cast<const uint4*>(p.words + k0));
+            const uint4 b = __ldcs(reinterpret_cast<const uint4*>(p.words + k0 + 4));
+            const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int e = 0; e < 8; e++) {
+                invb[it] |= (hdr_ok(w[e]) ? 0u : 1u) << e;
+                synb[it] |= (w[e] & 1u) << e;
+            }
+            const uint32_t ev[4] = {w[0], w[2], w[4], w[6]}, od[4] = {w[1], w[3], w[5], w[7]};
+            emit_plain4(p, 0, k0 >> 1, ev);
+            emit_plain4(p, 1, k0 >> 1, od);
+        }
+    } else {
+        // ---- general tile: misaligned chunks, lost sync, stream tail, unaligned output pointers
+        for (int it = 0; it < iters; it++) {
+            const uint64_t k0 = tile_w0 + ((uint64_t)it * kUnpackThreads + threadIdx.x) * W;
+            if (k0 * 4 >= p.nbytes) continue;
+            uint32_t w[8];
+            uint32_t ib = 0, sb = 0;
+            for (int e = 0; e < W; e++) {
+                w[e] = (k0 + e < n_raw) ? p.words[k0 + e] : 0u;
+                if (k0 + e < n_raw) {
+                    ib |= (hdr_ok(w[e]) ? 0u : 1u) << e;
+                    sb |= (w[e] & 1u) << e;
                 }
             }
-            // decode + store
+#pragma unroll
+            for (int q = 0; q < kUnpackMaxIters; q++) if (q == it) { invb[q] = ib; synb[q] = sb; }
             if (p.B == 0) {
                 // the (possibly partial) tail word still has to reach sv_word's byte-wise path
-                if (k0 + 8 > n_raw) {
-#pragma unroll
-                    for (int e = 0; e < 8; e++) w[e] = sv_word(p.sv[0], k0 + e);
-                }
-                const uint32_t lo[4] = {w[0], w[1], w[2], w[3]}, hi[4] = {w[4], w[5], w[6], w[7]};
+                if (k0 + 4 > n_raw)
+                    for (int e = 0; e < 4; e++) w[e] = sv_word(p.sv[0], k0 + e);
+                const uint32_t lo[4] = {w[0], w[1], w[2], w[3]};
                 emit_group(p, 0, k0, lo);
-                emit_group(p, 0, k0 + 4, hi);
             } else if (p.B == 1) {
                 const uint32_t ev[4] = {w[0], w[2], w[4], w[6]}, od[4] = {w[1], w[3], w[5], w[7]};
                 emit_group(p, 0, k0 >> 1, ev);
@@ -251,18 +299,99 @@ __global__ void __launch_bounds__(kUnpackThreads) unpack_kernel(const __grid_con
             } else {   // B % 8 == 0: the whole group belongs to one sub-stream
                 const int s = (int)((k0 / p.B) & 1u);
                 const uint64_t j0 = (k0 / (2ull * p.B)) * p.B + k0 % p.B;
-                const uint32_t lo[4] = {w[0], w[1], w[2], w[3]}, hi[4] = {w[4], w[5], w[6], w[7]};
+                const uint32_t lo[4] = {w[0], w[1], w[2], w[3]};
                 emit_group(p, s, j0, lo);
-                emit_group(p, s, j0 + 4, hi);
             }
         }
-        if (p.want_flags) {
-            // warp-ballot: is anything flagged in this warp-iteration at all?
-            const uint32_t any = __ballot_sync(0xffffffffu, (inv8[it] | syn8[it]) != 0);
-            uint32_t ci = 0, cs = 0;
-            if (any) {
-                // packed inclusive warp scan of (invalid, sync) counts: 16 bits each (max 256)
-                uint32_t v = __popc(inv8[it]) | (__popc(syn8[it]) << 16);
+    }
+    if (!p.want_flags) return;
+    // ---- per-tile counts of flagged words
+    uint32_t ci = 0, cs = 0;
+#pragma unroll
+    for (int it = 0; it < kUnpackMaxIters; it++) { ci += __popc(invb[it]); cs += __popc(synb[it]); }
+    if (__ballot_sync(0xffffffffu, (ci | cs) != 0)) {
+        uint32_t v = ci | (cs << 16);                     // at most 8 * 4 * 32 = 1024 per warp and kind
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) atomicAdd(reinterpret_cast<unsigned long long*>(p.tile_counts + tile), pack_counts(v & 0xFFFFu, v >> 16));
+    }
+}
+
+// One CTA: exclusive scan of the per-tile counts, running totals, work list of the tiles that have flags.
+__global__ void __launch_bounds__(1024) flag_scan_kernel(const __grid_constant__ UnpackParams p)
+{
+    __shared__ uint64_t s_warp[32];
+    __shared__ uint64_t s_carry;
+    __shared__ uint32_t s_nwork;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { s_carry = 0; s_nwork = 0; }
+    __syncthreads();
+    for (uint32_t base = 0; base < p.n_tiles; base += 1024) {
+        const uint32_t t = base + threadIdx.x;
+        const uint64_t mine = t < p.n_tiles ? p.tile_counts[t] : 0;
+        uint64_t v = mine;                                 // both 32-bit halves scan independently (no carry: < 2^31 words)
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint64_t u = __shfl_up_sync(0xffffffffu, v, d);
+            if (lane >= d) v += u;
+        }
+        if (lane == 31) s_warp[warp] = v;
+        __syncthreads();
+        if (warp == 0) {
+            uint64_t w = s_warp[lane];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint64_t u = __shfl_up_sync(0xffffffffu, w, d);
+                if (lane >= d) w += u;
+            }
+            s_warp[lane] = w;
+        }
+        __syncthreads();
+        const uint64_t excl = s_carry + (warp ? s_warp[warp - 1] : 0) + v - mine;
+        if (t < p.n_tiles) {
+            p.tile_offsets[t] = excl;
+            if (mine != 0 && (p.inv_idx || p.syn_idx)) p.work[atomicAdd(&s_nwork, 1u)] = t;
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = excl + mine;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        p.totals_out[0] = p.totals_in[0] + (s_carry >> 32);
+        p.totals_out[1] = p.totals_in[1] + (s_carry & 0xFFFFFFFFull);
+        *p.n_work = s_nwork;
+    }
+}
+
+// Flagged tiles only: read the tile again and write the indices of its flagged words, ascending, at the offsets
+// the scan assigned.  Word order within a tile = (iteration, warp, lane, bit) order.
+__global__ void __launch_bounds__(kUnpackThreads) flag_emit_kernel(const __grid_constant__ UnpackParams p)
+{
+    __shared__ uint32_t s_cnt[kUnpackMaxIters][kUnpackThreads / 32][2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t n_raw = p.nbytes >> 2;
+    const int W = (p.B == 1) ? 8 : 4;
+    const int iters = kUnpackTileWords / (kUnpackThreads * W);
+    const uint32_t n_work = *p.n_work;
+    for (uint32_t wi = blockIdx.x; wi < n_work; wi += gridDim.x) {
+        const uint32_t tile = p.work[wi];
+        const uint64_t tile_w0 = (uint64_t)tile * kUnpackTileWords;
+        uint32_t invb[kUnpackMaxIters], synb[kUnpackMaxIters], pre[kUnpackMaxIters];
+#pragma unroll
+        for (int it = 0; it < kUnpackMaxIters; it++) {
+            invb[it] = synb[it] = 0; pre[it] = 0;
+            uint32_t c2 = 0;
+            if (it < iters) {
+                const uint64_t k0 = tile_w0 + ((uint64_t)it * kUnpackThreads + threadIdx.x) * W;
+                for (int e = 0; e < W; e++) {
+                    if (k0 + e < n_raw) {
+                        const uint32_t w = __ldg(p.words + k0 + e);
+                        invb[it] |= (hdr_ok(w) ? 0u : 1u) << e;
+                        synb[it] |= (w & 1u) << e;
+                    }
+                }
+                // packed inclusive warp scan of (invalid, sync) counts: 16 bits each (at most 256 per warp)
+                uint32_t v = __popc(invb[it]) | (__popc(synb[it]) << 16);
                 const uint32_t own = v;
 #pragma unroll
                 for (int d = 1; d < 32; d <<= 1) {
@@ -270,47 +399,47 @@ __global__ void __launch_bounds__(kUnpackThreads) unpack_kernel(const __grid_con
                     if (lane >= d) v += u;
                 }
                 pre[it] = v - own;                               // exclusive, this thread
-                const uint32_t tot = __shfl_sync(0xffffffffu, v, 31);
-                ci = tot & 0xFFFFu; cs = tot >> 16;
+                c2 = __shfl_sync(0xffffffffu, v, 31);
             }
-            if (lane == 0) { s_cnt[it][warp][0] = ci; s_cnt[it][warp][1] = cs; }
+            if (lane == 0) { s_cnt[it][warp][0] = c2 & 0xFFFFu; s_cnt[it][warp][1] = c2 >> 16; }
         }
-    }
-    if (!p.want_flags) return;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t ti = 0, ts = 0;
-        for (int it = 0; it < kUnpackIters; it++)
-            for (int wv = 0; wv < kUnpackThreads / 32; wv++) {
-                const uint32_t a = s_cnt[it][wv][0], b = s_cnt[it][wv][1];
-                s_cnt[it][wv][0] = ti; s_cnt[it][wv][1] = ts;       // exclusive base within the tile
-                ti += a; ts += b;
-            }
-        const uint64_t bi = tile == 0 ? p.totals[0] : 0, bs = tile == 0 ? p.totals[1] : 0;
-        const uint64_t ei = lookback_count(p.desc_inv, tile, ti, bi);
-        const uint64_t es = lookback_count(p.desc_syn, tile, ts, bs);
-        s_excl[0] = ei; s_excl[1] = es;
-        if (tile == p.n_tiles - 1) { p.totals[0] = ei + ti; p.totals[1] = es + ts; }
-    }
-    __syncthreads();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t ti = 0, ts = 0;
+            for (int it = 0; it < kUnpackMaxIters; it++)
+                for (int wv = 0; wv < kUnpackThreads / 32; wv++) {
+                    const uint32_t a = s_cnt[it][wv][0], b = s_cnt[it][wv][1];
+                    s_cnt[it][wv][0] = ti; s_cnt[it][wv][1] = ts;       // exclusive base within the tile
+                    ti += a; ts += b;
+                }
+        }
+        __syncthreads();
+        const uint64_t off = p.tile_offsets[tile];
+        const uint64_t bi = p.totals_in[0] + (off >> 32), bs = p.totals_in[1] + (off & 0xFFFFFFFFull);
 #pragma unroll
-    for (int it = 0; it < kUnpackIters; it++) {
-        if ((inv8[it] | syn8[it]) == 0) continue;
-        const uint64_t g = ((uint64_t)tile * kUnpackIters + it) * kUnpackThreads + threadIdx.x;
-        const uint64_t k0 = p.index_base + g * 8;
-        uint64_t pi = s_excl[0] + s_cnt[it][warp][0] + (pre[it] & 0xFFFFu);
-        uint64_t ps = s_excl[1] + s_cnt[it][warp][1] + (pre[it] >> 16);
-        for (int e = 0; e < 8; e++) {
-            if ((inv8[it] >> e) & 1u) { if (p.inv_idx && pi < p.inv_cap) p.inv_idx[pi] = (uint32_t)(k0 + e); pi++; }
-            if ((syn8[it] >> e) & 1u) { if (p.syn_idx && ps < p.syn_cap) p.syn_idx[ps] = (uint32_t)(k0 + e); ps++; }
+        for (int it = 0; it < kUnpackMaxIters; it++) {
+            if ((invb[it] | synb[it]) == 0) continue;
+            const uint64_t k0 = p.index_base + tile_w0 + ((uint64_t)it * kUnpackThreads + threadIdx.x) * W;
+            uint64_t pi = bi + s_cnt[it][warp][0] + (pre[it] & 0xFFFFu);
+            uint64_t ps = bs + s_cnt[it][warp][1] + (pre[it] >> 16);
+            for (int e = 0; e < 8; e++) {
+                if ((invb[it] >> e) & 1u) { if (p.inv_idx && pi < p.inv_cap) p.inv_idx[pi] = (uint32_t)(k0 + e); pi++; }
+                if ((synb[it] >> e) & 1u) { if (p.syn_idx && ps < p.syn_cap) p.syn_idx[ps] = (uint32_t)(k0 + e); ps++; }
+            }
         }
+        __syncthreads();
     }
 }
 
-void launch_unpack(const UnpackParams& p, cudaStream_t st)
+int launch_unpack(const UnpackParams& p, int num_sms, cudaStream_t st)
 {
-    if (p.n_tiles == 0) return;
+    if (p.n_tiles == 0) return 0;
     unpack_kernel<<<p.n_tiles, kUnpackThreads, 0, st>>>(p);
+    if (!p.want_flags) return 1;
+    flag_scan_kernel<<<1, 1024, 0, st>>>(p);
+    if (!p.inv_idx && !p.syn_idx) return 2;
+    flag_emit_kernel<<<num_sms, kUnpackThreads, 0, st>>>(p);
+    return 3;
 }
 
 // ------------------------------------------------------------------ synthetic words

@@ -21,7 +21,6 @@ struct OffsetsParams {
 struct UnpackParams {
     const uint32_t* words;        // raw capture (device)
     uint64_t nbytes;              // raw bytes
-    uint64_t n_groups;            // ceil(raw words / 8)
     uint32_t B;                   // interleave block (0, 1 or a multiple of 8)
     uint32_t chunk_bytes;
     uint32_t spc;                 // samples per chunk
@@ -39,19 +38,22 @@ struct UnpackParams {
     uint32_t* inv_idx;  uint64_t inv_cap;
     uint32_t* syn_idx;  uint64_t syn_cap;
     uint64_t  index_base;         // added to the word index (stream offset in a batch)
-    uint64_t* desc_inv;           // [n_tiles] look-back descriptors (status<<62 | value), zeroed
-    uint64_t* desc_syn;
-    uint32_t* ticket;             // zeroed
-    uint64_t* totals;             // [2] running (n_invalid, n_sync) across launches of one submit
+    uint64_t* tile_counts;        // [n_tiles] flagged words per tile (invalid<<32 | sync), zeroed
+    uint64_t* tile_offsets;       // [n_tiles] exclusive scan of tile_counts
+    uint32_t* work;               // [n_tiles] tiles with flags
+    uint32_t* n_work;             // entries in work
+    const uint64_t* totals_in;    // [2] (n_invalid, n_sync) of the earlier launches of this submit: read by every tile
+    uint64_t* totals_out;         // [2] totals_in + this launch, written by the last tile (a different slot)
     uint32_t  n_tiles;
 };
 
 constexpr int kUnpackThreads = 256;
-constexpr int kUnpackIters   = 2;
-constexpr int kUnpackTileGroups = kUnpackThreads * kUnpackIters;   // groups of 8 words per tile
+constexpr int kUnpackMaxIters  = 4;                                        // 4-word groups per thread and tile
+constexpr int kUnpackTileWords = kUnpackThreads * kUnpackMaxIters * 4;    // raw words per tile (4096)
 
 void launch_find_offsets(const OffsetsParams& p, cudaStream_t st);
-void launch_unpack(const UnpackParams& p, cudaStream_t st);
+// returns the number of kernels launched (decode, flag scan, flag index emission)
+int launch_unpack(const UnpackParams& p, int num_sms, cudaStream_t st);
 void launch_synth(uint32_t* out, uint64_t n0, uint64_t n, int hif_layout, uint64_t seed,
                   const int16_t* tone_i, const int16_t* tone_q, cudaStream_t st);
 
