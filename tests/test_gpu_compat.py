@@ -1,0 +1,135 @@
+"""Drop-in shims (include/caribou_cuda.h "drop-in shims"): the caribou_smi_read-shaped entry point and the RX half
+of SoapySDR::Stream, fed from a memfd like the reference build of the oracle is, compared with the oracle call by
+call (return codes included).  Also the device-side synthetic generator against the host one."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _memfd(raw):
+    fd = os.memfd_create("smi")
+    b = np.ascontiguousarray(raw).view(np.uint8).tobytes()
+    os.write(fd, b)
+    os.lseek(fd, 0, os.SEEK_SET)
+    return fd
+
+
+class Smi:
+    def __init__(self, cb, raw, nbl=524288):
+        self.cb, self.L = cb, cb.lib()
+        self.fd = _memfd(raw)
+        self.h = self.L.caribou_cuda_smi_open(self.fd, nbl, 0)
+        assert self.h, cb.last_error()
+
+    def read(self, n, channel=0, sentinel=0x1234, want_cs16=True, want_meta=True):
+        cs16 = np.full((n + 1, 2), sentinel, dtype=np.int16)
+        meta = np.full(n + 1, 0x5A, dtype=np.uint8)
+        r = self.L.caribou_cuda_smi_read(self.h, channel, cs16.ctypes.data if want_cs16 else None,
+                                         meta.ctypes.data if want_meta else None, n)
+        return r, cs16, meta
+
+    def close(self):
+        self.L.caribou_cuda_smi_close(self.h)
+        os.close(self.fd)
+
+
+@pytest.mark.parametrize("channel", [0, 1])
+@pytest.mark.parametrize("drop", [0, 3, 5])
+def test_smi_read_shim_matches_oracle(cb, po, torch_cuda, channel, drop):
+    """int caribou_smi_read(...) (caribou_smi.h:96-97): sequence of reads over one capture, misaligned included;
+    untouched slots keep the caller's bytes; 0 at end of data."""
+    n = 1 << 19
+    raw = np.ascontiguousarray(po.gen_words(n, channel=channel).view(np.uint8)[drop:])
+    s = Smi(cb, raw)
+    cursor = 0
+    try:
+        for req in [1000, 131072, 200000, 131072 * 2, 7, 400000]:
+            got_r, got_cs16, got_meta = s.read(req, channel)
+            ref_cs16 = np.full((req + 1, 2), 0x1234, dtype=np.int16)
+            ref_meta = np.full(req + 1, 0x5A, dtype=np.uint8)
+            ref_r, _, _, cursor = po.smi_read(raw, req, channel, 524288, cursor, cs16=ref_cs16, meta=ref_meta)
+            assert got_r == ref_r, (req, got_r, ref_r)
+            np.testing.assert_array_equal(got_cs16, ref_cs16)
+            np.testing.assert_array_equal(got_meta, ref_meta)
+        assert s.L.caribou_cuda_smi_get_native_batch_samples(s.h) == 131072
+    finally:
+        s.close()
+
+
+def test_smi_read_shim_sync_lost_and_null_buffers(cb, po, torch_cuda):
+    n = 1 << 18
+    w = po.gen_words(n).copy()
+    w[131072:131072 * 2] = 0                    # a whole chunk without any alignable header: -3 (caribou_smi.c:665-668)
+    raw = w.view(np.uint8)
+    s = Smi(cb, raw)
+    try:
+        r, cs16, meta = s.read(131072, want_meta=False)
+        ref_r, ref_cs16, _, cur = po.smi_read(raw, 131072, 0)
+        assert r == ref_r == 131072
+        np.testing.assert_array_equal(cs16[:131072], ref_cs16[:131072])
+        assert np.all(meta == 0x5A)             # metadata == NULL: never written
+        r, _, _ = s.read(131072)
+        ref_r, _, _, _ = po.smi_read(raw, 131072, 0, cursor=cur)
+        assert r == ref_r == -3
+    finally:
+        s.close()
+
+
+FMT = {"CS16": (np.int16, 4), "CS8": (np.int8, 2), "CF32": (np.float32, 8), "CF64": (np.float64, 16)}
+
+
+@pytest.mark.parametrize("fmt", ["CS16", "CF32", "CF64", "CS8"])
+@pytest.mark.parametrize("filt", [0, 2])
+def test_rxstream_shim_matches_stream_oracle(cb, po, torch_cuda, fmt, filt):
+    """Stream::ReadSamplesGen (CaribouliteStream.cpp:370-382): format switch, MTU clamp for non-CS16, persistent
+    filter state across calls.  Unfiltered: bit-exact.  Filtered (int16 truncation after the filter): at most one
+    LSB on a vanishing fraction of samples, 1e-5 of RMS overall."""
+    L = cb.lib()
+    raw = np.ascontiguousarray(po.gen_words(1 << 19).view(np.uint8)[3:])
+    so = po.StreamOracle(raw)
+    so.set_format(fmt)
+    so.set_filter(filt)
+    s = Smi(cb, raw)
+    st = L.caribou_cuda_rxstream_create(s.h, 0)
+    assert st, cb.last_error()
+    try:
+        assert L.caribou_cuda_rxstream_set_format(st, b"XX") == -1
+        assert L.caribou_cuda_rxstream_set_format(st, fmt.encode()) == 0
+        L.caribou_cuda_rxstream_set_filter(st, filt)
+        assert L.caribou_cuda_rxstream_mtu(st) == 131072
+        dt, _ = FMT[fmt]
+        for req in [1000, 131072, 200000, 50000, 131072]:
+            buf = np.zeros((req + 1, 2), dtype=dt)
+            r = L.caribou_cuda_rxstream_read(st, buf.ctypes.data, req, 100000)
+            ref_r, ref = so.read(req)
+            assert r == ref_r, (req, r, ref_r)
+            got = buf[:r]
+            if filt == 0:
+                np.testing.assert_array_equal(got, ref)
+            else:
+                lsb = {"CS16": 1, "CS8": 1, "CF32": 1 / 4096, "CF64": 1 / 4096}[fmt]
+                d = np.abs(got.astype(np.float64) - ref.astype(np.float64))
+                assert d.max() <= lsb * 1.0001
+                assert np.mean(d > 0) < 1e-3
+    finally:
+        L.caribou_cuda_rxstream_destroy(st)
+        s.close()
+
+
+@pytest.mark.parametrize("hif", [0, 1])
+def test_device_generator_matches_host_generator(cb, po, torch_cuda, hif):
+    """the device-side synthetic word generator is cross-checked against the oracle's on a 2^22
+    prefix and on a window far into the stream (64-bit sample index)."""
+    torch = torch_cuda
+    ti, tq = po.tone_tables()
+    with cb.Context() as ctx:
+        for n0, n, seed in [(0, 1 << 22, 0xC0FFEE + hif), ((1 << 33) - 4096, 1 << 16, 12345)]:
+            d = torch.zeros(n, dtype=torch.int32, device="cuda:0")
+            ctx.synth_words(d, n, n0=n0, hif_layout=hif, seed=seed, tone_i=ti, tone_q=tq)
+            ctx.wait()
+            ref = po.gen_words(n, n0=n0, channel=hif, seed=seed)
+            np.testing.assert_array_equal(d.cpu().numpy().view(np.uint32), ref)

@@ -1,0 +1,26 @@
+"""C5 on real GPUs: launches tests/multi_gpu_c5.py under torchrun with NCCL when the box has >= 2 GPUs."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("mode", ["allgather", "chain"])
+def test_time_chunked_stream_over_gpus(torch_cuda, mode):
+    n = torch_cuda.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs (the single-GPU emulation is tests/test_gpu_iir.py::test_shard_handoff_*)")
+    world = min(n, 4)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
+           "--master-addr", "127.0.0.1", "--master-port", "29541", os.path.join(ROOT, "tests", "multi_gpu_c5.py"),
+           "--log2-words", "22", "--mode", mode, "--calls", "2"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1]
+    j = json.loads(line)
+    assert j["ok"] and j["world"] == world, j
