@@ -316,7 +316,7 @@ def run_b200(a):
     k_avg = float(np.mean(kern_ms)) if len(kern_ms) else float("nan")
     alg_bytes = ns * n * BYTES_PER_SAMPLE
     achieved = alg_bytes / (k_avg / 1e3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "iir_scan_kernel<K=2,D=8,IN_WORDS> (fused unpack+IIR+decimate)",
+    roofline = {"bound": "hbm", "kernel": "iir_scan_kernel<K=2,D=8,IN_WORDS,PAR,Y32> (fused unpack+IIR+decimate, float-staged)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": ncu_traffic_per_launch(a), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "bytes_per_sample": BYTES_PER_SAMPLE,

@@ -204,7 +204,8 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
             for (int m = 0; m < kMaxNK; m++)
                 for (int i = 0; i < kMaxS; i++) Tl.R[m][i] *= T.gain;
         prof_mark(c, 0);
-        const int e = launch_iir(P.K, P.D, in_kind, P.par, y32, tm, p, Tl, c->num_sms, c->stream);
+        const int kin = (in_kind == IN_WORDS && layout) ? IN_WORDS_HIF : in_kind;
+        const int e = launch_iir(P.K, P.D, kin, P.par, y32, tm, p, Tl, c->num_sms, c->stream);
         prof_mark(c, 1);
         if (e != 0) { cuda_ok((cudaError_t)e, "iir_scan_kernel launch"); return CARIBOU_CUDA_ERR; }
         c->launches++;

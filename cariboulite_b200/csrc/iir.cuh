@@ -38,7 +38,8 @@ constexpr int kMaxK  = 4;
 constexpr int kMaxS  = 2 * kMaxK;      // state dimension per rail
 constexpr int kMaxNK = 32;             // kept outputs per run
 
-enum { IN_WORDS = 0, IN_CS16 = 1, IN_CF32 = 2 };
+enum { IN_WORDS = 0, IN_CS16 = 1, IN_CF32 = 2,
+       IN_WORDS_HIF = 3 };   // internal: SMI words with the HiF field order (I = lo13), its own kernel instantiation
 // epilogue modes
 enum { OUT_F32 = 0,          // (float)y                              (parity F32)
        OUT_Q16_CS16 = 1,     // (int16)(float)y                       (parity Q16, CS16)

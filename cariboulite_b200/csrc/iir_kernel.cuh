@@ -146,9 +146,12 @@ __device__ __forceinline__ double mul_wide_f64(uint32_t a, uint32_t mul)
 template <int IN>
 __device__ __forceinline__ void inject_f64(uint32_t w, uint32_t xc, uint32_t m31, double& xa, double& xb)
 {
-    if (IN == IN_WORDS) {      // rail A: bits 29:17, rail B: bits 13:1
+    if (IN == IN_WORDS) {      // S1G: I = bits 29:17, Q = bits 13:1
         xa = mul_wide_f64(and_xor<0x00003FFEu>(w >> 16, xc), m31);
         xb = mul_wide_f64(and_xor<0x00003FFEu>(w, xc), m31);
+    } else if (IN == IN_WORDS_HIF) {   // HiF: I = bits 13:1, Q = bits 29:17 (caribou_smi.c:371-373)
+        xa = mul_wide_f64(and_xor<0x00003FFEu>(w, xc), m31);
+        xb = mul_wide_f64(and_xor<0x00003FFEu>(w >> 16, xc), m31);
     } else {                   // rail A: bits 15:0, rail B: bits 31:16
         xa = mul_wide_f64(and_xor<0x0000FFFFu>(w, xc), m31);
         xb = mul_wide_f64(and_xor<0x0000FFFFu>(w >> 16, xc), m31);
@@ -161,6 +164,9 @@ __device__ __forceinline__ void sample_to_f64(uint32_t w0, uint32_t w1, double& 
     if (IN == IN_WORDS) {
         xa = (double)hi13(w0);
         xb = (double)lo13(w0);
+    } else if (IN == IN_WORDS_HIF) {
+        xa = (double)lo13(w0);
+        xb = (double)hi13(w0);
     } else if (IN == IN_CS16) {
         xa = (double)(int)(int16_t)(w0 & 0xFFFFu);
         xb = (double)((int32_t)w0 >> 16);
@@ -253,7 +259,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
 
     if (P.gate != nullptr && __ldg(P.gate) != 0) return;
 
-    const int swap = (IN == IN_WORDS) ? P.layout : 0;     // rail A carries Q instead of I
+    constexpr int swap = 0;     // rail A is I, rail B is Q for every input kind (the HiF layout is its own instantiation)
     const uint32_t tps = P.tiles_per_stream;
 
     // this lane's M^lane, non-zero pattern only (s0 = M^lane S_in + E_{lane-1})
@@ -659,12 +665,14 @@ iir_launch_fn iir_pick_launch(int D, int in_kind, bool par)
     constexpr bool PREF = KK > 1;        // the realisation AUTO picks when the poles allow it
     if (par == PREF || (par && KK == 1)) {
         if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, PREF, Y32) }
+        if (in_kind == IN_WORDS_HIF) { CBL_IIR_DISPATCH_D(KK, IN_WORDS_HIF, PREF, Y32) }
         if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, PREF, Y32) }
         if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, PREF, Y32) }
         return nullptr;
     }
     if (Y32) return nullptr;
     if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, false, false) }
+    if (in_kind == IN_WORDS_HIF) { CBL_IIR_DISPATCH_D(KK, IN_WORDS_HIF, false, false) }
     if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, false, false) }
     if (in_kind == IN_CF32)  { CBL_IIR_DISPATCH_D(KK, IN_CF32, false, false) }
     return nullptr;
