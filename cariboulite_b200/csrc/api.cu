@@ -143,7 +143,8 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
                    void* d_out, size_t out_stride, const int32_t* gate, bool commit, uint32_t max_tiles)
 {
     const FilterPlan& P = c->plan;
-    const uint32_t ns = (uint32_t)c->cfg.n_streams;
+    const uint32_t ns = c->win_cnt;                               // streams of this launch (a window of the batch)
+    const size_t st_off = (size_t)c->win0 * 2 * P.S;             // their filter states
     const int LT = P.LT;
     const uint64_t n_runs = n / LT;
     const uint64_t n_main = n_runs * LT;
@@ -187,8 +188,8 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
         p.desc_agg = c->desc_agg.as<double>();
         p.desc_incl = c->desc_incl.as<double>();
         p.ticket = c->d_ticket;
-        p.state_in = c->d_state;
-        p.state_out = c->d_state_next;
+        p.state_in = c->d_state + st_off;
+        p.state_out = c->d_state_next + st_off;
         p.out = d_out;
         p.out_stride = out_stride;
         p.gate = gate;
@@ -210,7 +211,7 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
         if (e != 0) { cuda_ok((cudaError_t)e, "iir_scan_kernel launch"); return CARIBOU_CUDA_ERR; }
         c->launches++;
         if (p.write_state) {
-            launch_commit_state(c->d_state, c->d_state_next, (size_t)ns * 2 * P.S, gate, c->stream);
+            launch_commit_state(c->d_state + st_off, c->d_state_next + st_off, (size_t)ns * 2 * P.S, gate, c->stream);
             c->launches++;
         }
     }
@@ -224,7 +225,7 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
         t.in_kind = in_kind; t.layout = layout; t.out_mode = c->out_mode; t.K = P.K; t.D = P.D; t.par = P.par ? 1 : 0;
         for (int k = 0; k < P.K; k++) { t.a1[k] = T.a1[k]; t.a2[k] = T.a2[k]; t.c1[k] = T.c1[k]; t.c2[k] = T.c2[k]; }
         t.gain = T.gain;
-        t.state = c->d_state;
+        t.state = c->d_state + st_off;
         t.gate = gate;
         launch_iir_tail(t, c->stream);
         c->launches++;
@@ -262,14 +263,15 @@ static SubGeom sub_geom(const caribou_cuda_ctx* c, const void* d_bytes, size_t n
 
 static int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes)
 {
-    const uint32_t ns = (uint32_t)c->cfg.n_streams;
+    // d_bytes points at the first stream of the current window (c->win0, c->win_cnt)
+    const uint32_t ns_all = (uint32_t)c->cfg.n_streams, ns = c->win_cnt, w0 = c->win0;
     const int nsub = n_subs_of(c);
     uint32_t max_chunks = 0;
     for (int s = 0; s < nsub; s++) max_chunks = std::max(max_chunks, sub_geom(c, d_bytes, nbytes, s).n_chunks);
-    if (!c->offs.reserve((size_t)ns * 2 * std::max<uint32_t>(max_chunks, 1) * 4)) return CARIBOU_CUDA_ERR;
-    // first_bad <- INT_MAX (0x7f7f7f7f is large enough), counters <- 0
-    CBL_CHECK(cudaMemsetAsync(c->d_first_bad, 0x7f, (size_t)ns * 2 * 4, c->stream));
-    CBL_CHECK(cudaMemsetAsync(c->d_counters, 0, sizeof(Counters), c->stream));
+    if (!c->offs.reserve((size_t)ns_all * 2 * std::max<uint32_t>(max_chunks, 1) * 4)) return CARIBOU_CUDA_ERR;
+    // first_bad <- INT_MAX (0x7f7f7f7f is large enough) for the window; counters <- 0 at the first window
+    CBL_CHECK(cudaMemsetAsync(c->d_first_bad + (size_t)w0 * 2, 0x7f, (size_t)ns * 2 * 4, c->stream));
+    if (w0 == 0) CBL_CHECK(cudaMemsetAsync(c->d_counters, 0, sizeof(Counters), c->stream));
     for (int s = 0; s < nsub; s++) {
         const SubGeom g = sub_geom(c, d_bytes, nbytes, s);
         OffsetsParams p;
@@ -278,9 +280,9 @@ static int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nby
         p.n_streams = ns;
         p.chunk_bytes = (uint32_t)c->cfg.chunk_bytes;
         p.n_chunks = g.n_chunks;
-        p.offs = c->offs.as<int32_t>() + (size_t)s * ns * max_chunks;
+        p.offs = c->offs.as<int32_t>() + ((size_t)s * ns_all + w0) * max_chunks;
         p.offs_stride = max_chunks;
-        p.first_bad = c->d_first_bad + s;
+        p.first_bad = c->d_first_bad + (size_t)w0 * 2 + s;
         p.first_bad_stride = 2;
         p.n_misaligned = &c->d_counters->n_misaligned;
         p.any_misaligned = &c->d_counters->any_misaligned;
@@ -412,6 +414,7 @@ caribou_cuda_ctx* caribou_cuda_create(const caribou_cuda_config* cfg_in)
         c->own_stream = true;
     }
     const size_t ns = (size_t)cfg.n_streams;
+    c->win0 = 0; c->win_cnt = (uint32_t)ns;
     if (!cuda_ok(cudaMalloc(&c->d_ticket, 16), "cudaMalloc") ||
         !cuda_ok(cudaMalloc(&c->d_counters, sizeof(Counters)), "cudaMalloc") ||
         !cuda_ok(cudaMalloc(&c->d_first_bad, ns * 2 * 4), "cudaMalloc") ||
@@ -431,7 +434,8 @@ caribou_cuda_ctx* caribou_cuda_create(const caribou_cuda_config* cfg_in)
         if (!cuda_ok(cudaMalloc(&c->d_plane, P.plane.size() * 8), "cudaMalloc") ||
             !cuda_ok(cudaMalloc(&c->d_mtile_pow, P.mtile_pow.size() * 8), "cudaMalloc") ||
             !cuda_ok(cudaMalloc(&c->d_state, ns * 2 * P.S * 8), "cudaMalloc") ||
-            !cuda_ok(cudaMalloc(&c->d_state_next, ns * 2 * P.S * 8), "cudaMalloc")) return fail();
+            !cuda_ok(cudaMalloc(&c->d_state_next, ns * 2 * P.S * 8), "cudaMalloc") ||
+            !cuda_ok(cudaMalloc(&c->d_state_backup, ns * 2 * P.S * 8), "cudaMalloc")) return fail();
         cudaMemcpy(c->d_plane, P.plane.data(), P.plane.size() * 8, cudaMemcpyHostToDevice);
         cudaMemcpy(c->d_mtile_pow, P.mtile_pow.data(), P.mtile_pow.size() * 8, cudaMemcpyHostToDevice);
         cudaMemset(c->d_state, 0, ns * 2 * P.S * 8);
@@ -455,6 +459,10 @@ void caribou_cuda_destroy(caribou_cuda_ctx* c)
     if (c->d_mtile_pow) cudaFree(c->d_mtile_pow);
     if (c->d_state) cudaFree(c->d_state);
     if (c->d_state_next) cudaFree(c->d_state_next);
+    if (c->d_state_backup) cudaFree(c->d_state_backup);
+    for (cudaEvent_t e : c->pipe_ev) if (e) cudaEventDestroy(e);
+    if (c->h2d_stream) cudaStreamDestroy(c->h2d_stream);
+    if (c->d2h_stream) cudaStreamDestroy(c->d2h_stream);
     if (c->d_ticket) cudaFree(c->d_ticket);
     if (c->d_counters) cudaFree(c->d_counters);
     if (c->d_first_bad) cudaFree(c->d_first_bad);
@@ -716,15 +724,69 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
 
     const void* d_bytes = bytes;
     void* d_out = filt_out;
+    c->pipelined_last = false;
     if (mem != CARIBOU_CUDA_MEM_DEVICE) {
         if (uo) { set_error("rx_submit with unpack outputs needs device memory"); return CARIBOU_CUDA_ERR; }
         if (ns > 1 && (stride_bytes < nbytes || filt_stride < nout)) { set_error("stream stride smaller than the stream"); return CARIBOU_CUDA_ERR; }
         if (!c->stage_in.reserve(ns * stride_bytes + 64) || !c->stage_filt.reserve(ns * filt_stride * c->out_elem + 64)) return CARIBOU_CUDA_ERR;
+        d_bytes = c->stage_in.p;
+        d_out = c->stage_filt.p;
+        if (mem == CARIBOU_CUDA_MEM_HOST_PINNED && ns >= 4) {
+            // ---- pipelined: the batch goes through in groups of streams; group g+1 is on its way up while
+            // group g is being filtered and group g-1 is on its way down (both copy engines and the SMs busy)
+            const int kGroups = 8;
+            const size_t per = (ns + kGroups - 1) / kGroups;
+            const int ng = (int)((ns + per - 1) / per);
+            if (!c->h2d_stream) {
+                CBL_CHECK(cudaStreamCreateWithFlags(&c->h2d_stream, cudaStreamNonBlocking));
+                CBL_CHECK(cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
+                c->pipe_ev.resize(2 * kGroups + 2, nullptr);
+                for (cudaEvent_t& e : c->pipe_ev) CBL_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            }
+            cudaEvent_t ev_start = c->pipe_ev[2 * kGroups], ev_done = c->pipe_ev[2 * kGroups + 1];
+            // the staging buffers may still be in use by the previous submit on the main stream
+            CBL_CHECK(cudaMemcpyAsync(c->d_state_backup, c->d_state, ns * 2 * P.S * 8, cudaMemcpyDeviceToDevice, c->stream));
+            CBL_CHECK(cudaEventRecord(ev_start, c->stream));
+            CBL_CHECK(cudaStreamWaitEvent(c->h2d_stream, ev_start, 0));
+            CBL_CHECK(cudaStreamWaitEvent(c->d2h_stream, ev_start, 0));
+            const uint8_t* hb = reinterpret_cast<const uint8_t*>(bytes);
+            uint8_t* ho = reinterpret_cast<uint8_t*>(filt_out);
+            uint8_t* db = reinterpret_cast<uint8_t*>(c->stage_in.p);
+            uint8_t* dob = reinterpret_cast<uint8_t*>(c->stage_filt.p);
+            int rc = CARIBOU_CUDA_OK;
+            for (int g = 0; g < ng && rc == CARIBOU_CUDA_OK; g++) {
+                const size_t s0 = (size_t)g * per, cnt = std::min(per, ns - s0);
+                CBL_CHECK(cudaMemcpyAsync(db + s0 * stride_bytes, hb + s0 * stride_bytes, (cnt - 1) * stride_bytes + nbytes,
+                                          cudaMemcpyHostToDevice, c->h2d_stream));
+                CBL_CHECK(cudaEventRecord(c->pipe_ev[2 * g], c->h2d_stream));
+                CBL_CHECK(cudaStreamWaitEvent(c->stream, c->pipe_ev[2 * g], 0));
+                c->win0 = (uint32_t)s0; c->win_cnt = (uint32_t)cnt;
+                const int mcg = run_find_offsets(c, db + s0 * stride_bytes, nbytes, stride_bytes);
+                if (mcg < 0) { rc = mcg; break; }
+                rc = run_iir(c, IN_WORDS, db + s0 * stride_bytes, n, stride_bytes / 4, dob + s0 * filt_stride * c->out_elem, filt_stride,
+                             &c->d_counters->any_misaligned, true, 0);
+                if (rc != CARIBOU_CUDA_OK) break;
+                CBL_CHECK(cudaEventRecord(c->pipe_ev[2 * g + 1], c->stream));
+                CBL_CHECK(cudaStreamWaitEvent(c->d2h_stream, c->pipe_ev[2 * g + 1], 0));
+                CBL_CHECK(cudaMemcpyAsync(ho + s0 * filt_stride * c->out_elem, dob + s0 * filt_stride * c->out_elem,
+                                          ((cnt - 1) * filt_stride + nout) * c->out_elem, cudaMemcpyDeviceToHost, c->d2h_stream));
+            }
+            c->win0 = 0; c->win_cnt = (uint32_t)ns;
+            if (rc != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+            CBL_CHECK(cudaEventRecord(ev_done, c->d2h_stream));
+            CBL_CHECK(cudaStreamWaitEvent(c->stream, ev_done, 0));      // waiting for the context now covers the copies
+            if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+            c->pipelined_last = true;
+            c->pending.active = true;
+            c->pending.bytes = bytes; c->pending.nbytes = nbytes; c->pending.stride = stride_bytes; c->pending.mem = mem;
+            c->pending.filt_out = filt_out; c->pending.filt_stride = filt_stride;
+            c->pending.d_bytes = d_bytes; c->pending.d_out = d_out;
+            c->pos += n;
+            return CARIBOU_CUDA_OK;
+        }
         // the batch keeps its host layout (same strides) in the device staging buffers
         const size_t in_span = (ns - 1) * stride_bytes + nbytes;
         CBL_CHECK(cudaMemcpyAsync(c->stage_in.p, bytes, in_span, cudaMemcpyHostToDevice, c->stream));
-        d_bytes = c->stage_in.p;
-        d_out = c->stage_filt.p;
     }
     const int mc = run_find_offsets(c, d_bytes, nbytes, stride_bytes);
     if (mc < 0) return mc;
@@ -758,6 +820,9 @@ static int rx_fallback(caribou_cuda_ctx* c)
     const size_t n = q.nbytes / 4;
     const size_t sstride = (n + 3) & ~size_t(3);
     if (!c->scratch_cs16.reserve(ns * sstride * 4 + 64)) return CARIBOU_CUDA_ERR;
+    // a pipelined submit gates group by group: groups seen before the first misaligned chunk have already been
+    // filtered and have advanced their states - everything is redone from the states the submit started with
+    if (c->pipelined_last) CBL_CHECK(cudaMemcpyAsync(c->d_state, c->d_state_backup, ns * 2 * P.S * 8, cudaMemcpyDeviceToDevice, c->stream));
     CBL_CHECK(cudaMemsetAsync(c->scratch_cs16.p, 0, ns * sstride * 4, c->stream));
     caribou_cuda_unpack_out o;
     memset(&o, 0, sizeof(o));

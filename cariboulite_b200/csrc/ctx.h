@@ -82,6 +82,14 @@ struct caribou_cuda_ctx {
     // staging for host memory
     cbl::DevBuf stage_in, stage_cs16[2], stage_meta[2], stage_cf32[2], stage_filt, stage_inv, stage_syn, scratch_cs16;
 
+    // window of streams the launch helpers work on (pipelined host-buffer submits walk the batch group by group)
+    uint32_t win0 = 0, win_cnt = 0;
+    // copy engines' streams and events of the pipelined host-buffer path (created on first use)
+    cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
+    std::vector<cudaEvent_t> pipe_ev;
+    double* d_state_backup = nullptr;   // filter state before a pipelined submit (restored if it has to be redone)
+    bool pipelined_last = false;
+
     // synth
     int16_t* d_tone = nullptr;
 

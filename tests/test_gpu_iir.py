@@ -195,3 +195,35 @@ def test_scan_reordering_error_in_fp64(cb, po, torch_cuda, name):
     print("\nreordering error %s: rel-rms %s, max/rms %.3g, form %d, parallel-form design error %.3g"
           % (name, err, mx, fi.form, fi.parallel_form_error))
     assert np.all(err <= 1e-9), err
+
+
+@pytest.mark.parametrize("bad_stream", [None, 0, 9])
+def test_pinned_host_batch_is_pipelined_and_exact(cb, po, torch_cuda, bad_stream):
+    """Host-buffer path of the batched fused call (pinned memory, >= 4 streams): groups of streams are copied
+    up, filtered and copied down in a pipeline.  Two calls in a row (state carries), compared stream by stream
+    with the oracle; a misaligned chunk in an early or a late group makes the whole submit take the
+    unpack -> CS16 -> IIR route from the states the submit started with."""
+    torch = torch_cuda
+    ns, n, D = 11, 2 * 16384, 8
+    sos = po.butter_lowpass_sos(4, 4e6, 250e3)
+    calls = 2
+    ws = [[po.gen_words(n, n0=c * n, seed=s) for s in range(ns)] for c in range(calls)]
+    if bad_stream is not None:
+        ws[1][bad_stream][16384] ^= 0x80000000          # second call, chunk 1 of that stream starts with a bad header
+    h_w = torch.empty((ns, n), dtype=torch.int32).pin_memory()
+    h_out = torch.zeros((ns, n // D, 2), dtype=torch.float32).pin_memory()
+    outs = []
+    with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32, n_streams=ns, chunk_bytes=65536) as ctx:
+        for c in range(calls):
+            h_w.copy_(torch.from_numpy(np.stack(ws[c]).view(np.int32)))
+            ctx.rx_submit(h_w, n * 4, h_out, stride_bytes=n * 4, filt_stride=n // D, mem=cb.MEM_HOST_PINNED)
+            ret, res = ctx.wait()
+            assert ret == n
+            assert res.n_misaligned_chunks == (1 if (bad_stream is not None and c == 1) else 0)
+            outs.append(h_out.numpy().copy())
+    for s in range(ns):
+        ci, cq = po.Cascade(sos), po.Cascade(sos)
+        for c in range(calls):
+            _, cs16, _, _ = po.smi_read(ws[c][s].view(np.uint8), n, 0, 65536)
+            ref = po.filter_cf32_f32(sos, po.cs16_to_cf32(cs16[:n]), ci, cq)[::D]
+            assert np.all(rel_rms(outs[c][s], ref) <= TOL), (s, c)
