@@ -20,7 +20,7 @@
 #pragma once
 #include "iir.cuh"
 #ifndef CBL_P3_UNROLL
-#define CBL_P3_UNROLL 2
+#define CBL_P3_UNROLL 4
 #endif
 #ifndef CBL_P1_UNROLL
 #define CBL_P1_UNROLL 8

@@ -227,3 +227,51 @@ def test_pinned_host_batch_is_pipelined_and_exact(cb, po, torch_cuda, bad_stream
             _, cs16, _, _ = po.smi_read(ws[c][s].view(np.uint8), n, 0, 65536)
             ref = po.filter_cf32_f32(sos, po.cs16_to_cf32(cs16[:n]), ci, cq)[::D]
             assert np.all(rel_rms(outs[c][s], ref) <= TOL), (s, c)
+
+
+def _sos_rows(sos_scipy):
+    """scipy rows (b0,b1,b2,a0,a1,a2) are already the layout Iir::Custom::SOSCascade takes (Custom.h:90-112)."""
+    return np.ascontiguousarray(sos_scipy, dtype=np.float64)
+
+
+@pytest.mark.parametrize("kind", ["butter5", "butter3", "cheby1_6", "cheby2_4", "ellip_4", "bessel_4", "highpass_4",
+                                  "repeated_poles"])
+@pytest.mark.parametrize("D", [1, 8])
+def test_other_filter_families_and_odd_orders(cb, po, torch_cuda, kind, D):
+    """kernel (b) consumes arbitrary SOS.  Odd Butterworth orders (a first-order last section),
+    other iir1/scipy families, a high-pass (H(1) = 0) and a cascade with a repeated pole pair (no partial
+    fractions: the library must fall back to the cascade realisation) against the oracle's DF-II cascade."""
+    from scipy import signal
+    torch = torch_cuda
+    n = 1 << 18
+    if kind == "butter5":
+        sos = po.butter_lowpass_sos(5, 4e6, 100e3)
+    elif kind == "butter3":
+        sos = po.butter_lowpass_sos(3, 4e6, 400e3)
+    elif kind == "cheby1_6":
+        sos = _sos_rows(signal.cheby1(6, 1.0, 0.05, output="sos"))
+    elif kind == "cheby2_4":
+        sos = _sos_rows(signal.cheby2(4, 40.0, 0.2, output="sos"))
+    elif kind == "ellip_4":
+        sos = _sos_rows(signal.ellip(4, 0.5, 50.0, 0.1, output="sos"))
+    elif kind == "bessel_4":
+        sos = _sos_rows(signal.bessel(4, 0.1, output="sos"))
+    elif kind == "highpass_4":
+        sos = _sos_rows(signal.butter(4, 0.05, btype="highpass", output="sos"))
+    else:
+        one = signal.butter(2, 0.1, output="sos")
+        sos = _sos_rows(np.concatenate([one, one]))
+    w = po.gen_words(n)
+    x = po.cs16_to_cf32(_words_to_cs16(po, w))
+    ref = po.filter_cf32_f32(sos, x)[::D]
+    out = torch.zeros((n // D, 2), dtype=torch.float32, device="cuda:0")
+    with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32) as ctx:
+        ctx.filter_submit(cb.IN_WORDS, _dev(torch, w.view(np.int32)), n, out)
+        ctx.wait()
+        fi = ctx.filter_info()
+    if kind == "repeated_poles":
+        assert fi.form == cb.FORM_CASCADE, fi.note
+    got = out.cpu().numpy().astype(np.float64)
+    scale = max(np.sqrt(np.mean(ref.astype(np.float64) ** 2)), 1e-3)     # a high-pass leaves little signal: floor the scale
+    err = np.sqrt(np.mean((got - ref) ** 2, axis=0)) / scale
+    assert np.all(err <= TOL), (kind, err, fi.form, fi.note)
