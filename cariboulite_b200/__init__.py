@@ -106,6 +106,7 @@ def lib():
         "caribou_cuda_rxstream_set_filter": (None, [vp, i]),
         "caribou_cuda_rxstream_mtu": (sz, [vp]),
         "caribou_cuda_rxstream_read": (i, [vp, vp, sz, C.c_long]),
+        "caribou_cuda_pump": (i64, [vp, i, i, i, sz, i64]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)
@@ -126,7 +127,7 @@ EXPORTED_SYMBOLS = [
     "caribou_cuda_synth_words", "caribou_cuda_smi_open", "caribou_cuda_smi_close", "caribou_cuda_smi_read",
     "caribou_cuda_smi_get_native_batch_samples", "caribou_cuda_rxstream_create",
     "caribou_cuda_rxstream_destroy", "caribou_cuda_rxstream_set_format", "caribou_cuda_rxstream_set_filter",
-    "caribou_cuda_rxstream_mtu", "caribou_cuda_rxstream_read",
+    "caribou_cuda_rxstream_mtu", "caribou_cuda_rxstream_read", "caribou_cuda_pump",
 ]
 
 
@@ -291,6 +292,13 @@ class Context:
 
     def reset(self):
         self._check(lib().caribou_cuda_reset(self.h))
+
+    def pump(self, in_kind, in_fd, out_fd, block_samples, max_samples=0):
+        """Capture pump (file / pipe in, file / pipe out); returns input samples consumed or a negative code."""
+        r = lib().caribou_cuda_pump(self.h, in_kind, in_fd, out_fd, block_samples, max_samples)
+        if r == ERR:
+            raise CaribouCudaError(last_error())
+        return r
 
     def filter_info(self):
         fi = FilterInfo()

@@ -7,6 +7,7 @@
 #include <poll.h>
 #include <string.h>
 #include <unistd.h>
+#include <algorithm>
 #include <functional>
 #include <new>
 #include "ctx.h"
@@ -296,6 +297,99 @@ int caribou_cuda_rxstream_read(caribou_cuda_rxstream* s, void* buffer, size_t nu
     if (!cuda_ok(cudaGetLastError(), "convert_cs16_kernel")) return 0;
     if (!cuda_ok(cudaMemcpy(buffer, s->conv.p, (size_t)res * es, cudaMemcpyDeviceToHost), "D2H")) return 0;
     return res;
+}
+
+// ------------------------------------------------------------------ capture pump
+namespace {
+// read until `want` bytes, EOF (returns what it has) or error (-1)
+ssize_t read_full(int fd, uint8_t* buf, size_t want)
+{
+    size_t got = 0;
+    while (got < want) {
+        const ssize_t r = read(fd, buf + got, want - got);
+        if (r < 0) { if (errno == EINTR) continue; return -1; }
+        if (r == 0) break;
+        got += (size_t)r;
+    }
+    return (ssize_t)got;
+}
+bool write_full(int fd, const uint8_t* buf, size_t n)
+{
+    size_t put = 0;
+    while (put < n) {
+        const ssize_t r = write(fd, buf + put, n - put);
+        if (r < 0) { if (errno == EINTR) continue; return false; }
+        put += (size_t)r;
+    }
+    return true;
+}
+}  // namespace
+
+int64_t caribou_cuda_pump(caribou_cuda_ctx* c, int in_kind, int in_fd, int out_fd, size_t block_samples, int64_t max_samples)
+{
+    if (!c || in_kind < 0 || in_kind > 2 || block_samples == 0) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    if (c->cfg.n_streams != 1 || c->cfg.interleave_block_words) { set_error("pump: single-stream, single-channel contexts only"); return CARIBOU_CUDA_ERR; }
+    if (!c->has_filter && in_kind != CARIBOU_CUDA_IN_WORDS) { set_error("pump: a context without filter takes raw SMI words"); return CARIBOU_CUDA_ERR; }
+    const size_t D = c->has_filter ? (size_t)c->plan.D : 1;
+    if (block_samples % D) { set_error("pump: block_samples must be a multiple of the decimation factor"); return CARIBOU_CUDA_ERR; }
+    const size_t in_es = in_kind == CARIBOU_CUDA_IN_CF32 ? 8 : 4;
+    const size_t out_es = c->has_filter ? c->out_elem : 4;
+    uint8_t* hin[2] = {nullptr, nullptr};
+    uint8_t* hout[2] = {nullptr, nullptr};
+    auto cleanup = [&]() { for (int i = 0; i < 2; i++) { caribou_cuda_host_free(hin[i]); caribou_cuda_host_free(hout[i]); } };
+    for (int i = 0; i < 2; i++) {
+        hin[i] = (uint8_t*)caribou_cuda_host_alloc(block_samples * in_es + 64);
+        hout[i] = (uint8_t*)caribou_cuda_host_alloc(block_samples / D * out_es + 64);
+        if (!hin[i] || !hout[i]) { cleanup(); return CARIBOU_CUDA_ERR; }
+    }
+    int64_t consumed = 0, rc = 0;
+    size_t prev_out_bytes = 0;      // output of the block before the one in flight, not yet written
+    int prev_slot = -1;
+    // block 0 is read up front; afterwards block k+1 is read while block k is on the device
+    auto want_bytes = [&](void) -> size_t {
+        size_t w = block_samples;
+        if (max_samples > 0) w = (size_t)std::min<int64_t>((int64_t)w, max_samples - consumed);
+        return w * in_es;
+    };
+    ssize_t have = read_full(in_fd, hin[0], want_bytes());
+    int slot = 0;
+    while (have > 0) {
+        size_t n = (size_t)have / in_es;
+        n -= n % D;                                     // a tail shorter than D is not processed
+        if (n == 0) break;
+        // ---- block `slot` goes to the device (asynchronous for pinned memory)
+        int sr;
+        if (!c->has_filter) {
+            caribou_cuda_unpack_out o;
+            memset(&o, 0, sizeof(o));
+            o.cs16 = hout[slot];
+            sr = caribou_cuda_unpack_submit(c, hin[slot], n * 4, 0, CARIBOU_CUDA_MEM_HOST_PINNED, &o);
+        } else if (in_kind == CARIBOU_CUDA_IN_WORDS) {
+            sr = caribou_cuda_rx_submit(c, hin[slot], n * 4, 0, CARIBOU_CUDA_MEM_HOST_PINNED, nullptr, hout[slot], 0);
+        } else {
+            sr = caribou_cuda_filter_submit(c, in_kind, hin[slot], n, 0, CARIBOU_CUDA_MEM_HOST_PINNED, hout[slot], 0);
+        }
+        if (sr != CARIBOU_CUDA_OK) { rc = CARIBOU_CUDA_ERR; break; }
+        consumed += (int64_t)n;
+        // ---- meanwhile on the host: write the previous block's result, read the next block
+        if (prev_slot >= 0 && !write_full(out_fd, hout[prev_slot], prev_out_bytes)) { set_error("pump: write failed (%s)", strerror(errno)); rc = CARIBOU_CUDA_ERR; prev_slot = -1; break; }
+        prev_slot = -1;
+        ssize_t next_have = 0;
+        if (!(max_samples > 0 && consumed >= max_samples) && (size_t)have == block_samples * in_es)
+            next_have = read_full(in_fd, hin[slot ^ 1], want_bytes());
+        // ---- the block in flight
+        const int64_t wr = caribou_cuda_wait(c, nullptr);
+        if (wr < 0) { rc = wr; break; }
+        prev_slot = slot;
+        prev_out_bytes = (size_t)(c->has_filter ? c->last_n_filtered : wr) * out_es;
+        if (next_have < 0) { set_error("pump: read failed (%s)", strerror(errno)); rc = CARIBOU_CUDA_ERR; break; }
+        have = next_have;
+        slot ^= 1;
+    }
+    if (have < 0 && rc == 0) { set_error("pump: read failed (%s)", strerror(errno)); rc = CARIBOU_CUDA_ERR; }
+    if (prev_slot >= 0 && rc >= 0 && !write_full(out_fd, hout[prev_slot], prev_out_bytes)) { set_error("pump: write failed (%s)", strerror(errno)); rc = CARIBOU_CUDA_ERR; }
+    cleanup();
+    return rc < 0 ? rc : consumed;
 }
 
 }  // extern "C"

@@ -242,6 +242,22 @@ size_t caribou_cuda_rxstream_mtu(caribou_cuda_rxstream* s);                     
 int    caribou_cuda_rxstream_read(caribou_cuda_rxstream* s, void* buffer, size_t num_elements,
                                   long timeout_us);                                  /* Stream::ReadSamplesGen */
 
+/* ---------------------------------------------------------------- capture pump (file / pipe to file / pipe)
+ * The capture loop of cariboulite_util (LC/cariboulite_util.c:340-361: read a block, fwrite ret*4 bytes of raw
+ * little-endian CS16) with the sample path on the GPU and the wire format kept.  Reads blocks of `block_samples`
+ * elements of `in_kind` (raw SMI words, or CS16 / CF32 samples of an earlier capture) from in_fd until EOF or
+ * max_samples (<= 0: no limit), runs the context's path and writes the result to out_fd:
+ *   context without filter, IN_WORDS: unpack -> raw CS16 (4 bytes per sample; metadata is dropped exactly as the
+ *                                      reference drops it, cariboulite_util.c:349);
+ *   context with filter:               filtered, decimated elements of cfg.out_format.
+ * Host I/O overlaps the GPU: two page-locked input and output buffers, block k+1 is read and block k-1 written
+ * while block k is on the device.  block_samples must be a multiple of the decimation factor (and should be a
+ * multiple of chunk_bytes/4 for IN_WORDS so that chunk boundaries fall where the reference's reads put them);
+ * a tail shorter than the decimation factor is not processed.  Single-stream contexts only.
+ * Returns the number of input samples consumed, -1 on I/O / CUDA failure, -3 when a block lost word sync. */
+int64_t caribou_cuda_pump(caribou_cuda_ctx* ctx, int in_kind, int in_fd, int out_fd, size_t block_samples,
+                          int64_t max_samples);
+
 #ifdef __cplusplus
 }
 #endif

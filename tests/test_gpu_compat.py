@@ -133,3 +133,63 @@ def test_device_generator_matches_host_generator(cb, po, torch_cuda, hif):
             ctx.wait()
             ref = po.gen_words(n, n0=n0, channel=hif, seed=seed)
             np.testing.assert_array_equal(d.cpu().numpy().view(np.uint32), ref)
+
+
+def _out_fd():
+    return os.memfd_create("out")
+
+
+def _read_all(fd, dtype):
+    size = os.lseek(fd, 0, os.SEEK_END)
+    os.lseek(fd, 0, os.SEEK_SET)
+    return np.frombuffer(os.read(fd, size), dtype=dtype).copy()
+
+
+def test_pump_words_to_cs16_is_the_cariboulite_util_capture(cb, po, torch_cuda):
+    """caribou_cuda_pump without filter = the capture loop of cariboulite_util (cariboulite_util.c:340-361): the
+    output file is the raw little-endian CS16 the reference would have written, bit for bit (ragged last block)."""
+    n = 5 * 131072 + 4000
+    w = po.gen_words(n)
+    fin, fout = _memfd(w), _out_fd()
+    with cb.Context() as ctx:
+        r = ctx.pump(cb.IN_WORDS, fin, fout, 2 * 131072)
+    assert r == n
+    got = _read_all(fout, np.int16).reshape(-1, 2)
+    ref_ret, ref_cs16, _, _ = po.smi_read(w.view(np.uint8), n, 0)
+    assert ref_ret == n
+    np.testing.assert_array_equal(got, ref_cs16[:n])
+    os.close(fin); os.close(fout)
+
+
+@pytest.mark.parametrize("in_kind", ["words", "cs16"])
+def test_pump_filtered_decimated_stream(cb, po, torch_cuda, in_kind):
+    """Filtered pump over several blocks (state carries from block to block), max_samples honoured."""
+    from tests.test_gpu_iir import rel_rms, TOL
+    n, D, limit = 6 * 131072, 8, 5 * 131072
+    sos = po.butter_lowpass_sos(6, 4e6, 25e3)
+    w = po.gen_words(n)
+    _, cs16, _, _ = po.smi_read(w.view(np.uint8), n, 0)
+    ref = po.filter_cf32_f32(sos, po.cs16_to_cf32(cs16[:limit]))[::D]
+    fin = _memfd(w if in_kind == "words" else cs16[:n])
+    fout = _out_fd()
+    with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32) as ctx:
+        r = ctx.pump(cb.IN_WORDS if in_kind == "words" else cb.IN_CS16, fin, fout, 2 * 131072, max_samples=limit)
+    assert r == limit
+    got = _read_all(fout, np.float32).reshape(-1, 2)
+    assert got.shape[0] == limit // D
+    assert np.all(rel_rms(got, ref) <= TOL)
+    os.close(fin); os.close(fout)
+
+
+def test_pump_reports_lost_sync(cb, po, torch_cuda):
+    n = 4 * 131072
+    w = po.gen_words(n).copy()
+    w[2 * 131072:3 * 131072] = 0
+    fin, fout = _memfd(w), _out_fd()
+    with cb.Context() as ctx:
+        r = ctx.pump(cb.IN_WORDS, fin, fout, 131072)
+    assert r == cb.ERR_SYNC
+    got = _read_all(fout, np.int16).reshape(-1, 2)
+    _, ref_cs16, _, _ = po.smi_read(w.view(np.uint8), 2 * 131072, 0)
+    np.testing.assert_array_equal(got, ref_cs16[:2 * 131072])       # the blocks before the bad one were delivered
+    os.close(fin); os.close(fout)
