@@ -415,12 +415,12 @@ caribou_cuda_ctx* caribou_cuda_create(const caribou_cuda_config* cfg_in)
     }
     const size_t ns = (size_t)cfg.n_streams;
     c->win0 = 0; c->win_cnt = (uint32_t)ns;
-    if (!cuda_ok(cudaMalloc(&c->d_ticket, 16), "cudaMalloc") ||
+    if (!cuda_ok(cudaMalloc(&c->d_ticket, 256), "cudaMalloc") ||
         !cuda_ok(cudaMalloc(&c->d_counters, sizeof(Counters)), "cudaMalloc") ||
         !cuda_ok(cudaMalloc(&c->d_first_bad, ns * 2 * 4), "cudaMalloc") ||
         !cuda_ok(cudaMallocHost(&c->h_counters, sizeof(Counters)), "cudaMallocHost") ||
         !cuda_ok(cudaMallocHost(&c->h_first_bad, ns * 2 * 4), "cudaMallocHost")) return fail();
-    cudaMemset(c->d_ticket, 0, 16);
+    cudaMemset(c->d_ticket, 0, 256);
     cudaMemset(c->d_counters, 0, sizeof(Counters));
     cudaMemset(c->d_first_bad, 0x7f, ns * 2 * 4);
     memset(c->h_counters, 0, sizeof(Counters));

@@ -76,7 +76,7 @@ struct IirParams {
     const double* plane;        // [S*S][33]        plane[e*33 + t] = (M^t)[e]
     double*   desc_agg;         // [total_tiles][2S]  zero-state tile end states; every double validates itself:
     double*   desc_incl;        // [total_tiles][2S]  true tile end states         the arrays are pre-set to kDescEmpty
-    uint32_t* ticket;           // zeroed per launch
+    uint32_t* ticket;           // word 0 zeroed per launch; words 32..63 are zeros the kernel reads (iir_kernel.cuh take_ticket)
     const double* state_in;     // [n_streams][2S] kernel coordinates
     double*   state_out;        // [n_streams][2S]
     void*     out;              // kept outputs, NK per run, streams out_stride elements apart

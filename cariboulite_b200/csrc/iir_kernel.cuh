@@ -74,8 +74,9 @@ __device__ __forceinline__ void st_desc(double* p, double x)
     if (v == kDescEmpty) v = kDescEmpty - 1;      // still a NaN, no longer "empty"
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-// ticket: plain PTX atomic (atomicAdd() is compiled into a warp-aggregated sequence whose shuffle waits for the
-// atomic's round trip on the spot; here the value is not looked at until one tile later)
+// ticket: plain PTX atomic.  atomicAdd() - and a PTX atom on an address ptxas can prove uniform - is compiled into
+// a warp-aggregated sequence whose shuffle waits for the atomic's round trip on the spot; the kernel therefore
+// adds a zero it loaded from memory to the ticket address, and the value is not looked at until one tile later.
 __device__ __forceinline__ uint32_t take_ticket(uint32_t* p)
 {
     uint32_t v;
@@ -286,9 +287,10 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     // its round trip never sits on the critical path.  next / next2 are meaningful in lane 0 only.
     uint32_t gstep = 0;    // steps consumed by this warp so far (ring position / parity)
     uint32_t tile = 0xFFFFFFFFu, next = 0xFFFFFFFFu;
+    uint32_t* const ticket = P.ticket + __ldg(P.ticket + 32 + lane);      // words 32..63 of the ticket block stay zero
     if (lane == 0) {
-        tile = take_ticket(P.ticket);
-        next = take_ticket(P.ticket);
+        tile = take_ticket(ticket);
+        next = take_ticket(ticket);
     }
     tile = __shfl_sync(0xffffffffu, tile, 0);
     uint32_t stream = tile / tps, tis = tile - stream * tps;
@@ -313,7 +315,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
         double f[2][S];
         double va[K][2], vb[K][2];
         if (have) {
-            if (lane == 0) next2 = take_ticket(P.ticket);      // the tile after `next`; consumed one iteration later
+            if (lane == 0) next2 = take_ticket(ticket);      // the tile after `next`; consumed one iteration later
             nstream = next / tps;
             ntis = next - nstream * tps;
             const uint32_t ystage = ystage0 + buf * C::YSTAGE_BYTES;
@@ -329,6 +331,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                 const uint32_t st = gstep % C::STAGES;
                 mbar_wait(bar_u32 + 8 * st, (gstep / C::STAGES) & 1u);
                 const uint32_t row = ring_u32 + st * 4096 + lane * 128;
+                const uint32_t rowx = row + ((lane & 7) << 4);       // bits 6:4 of row are zero (128-byte rows)
                 // the 128-byte row in groups of U 16-byte pieces: the group body is unrolled, the group loop is
                 // not (the whole row unrolled is ~9 KiB of code per kernel, which the instruction cache feels)
                 constexpr int U = kP1Unroll;                     // 16-byte pieces per group
@@ -340,7 +343,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                     const int gbase = step * C::SPS + co * GS;   // first sample of the group within the run
                     uint4 q[U];
 #pragma unroll
-                    for (int ci = 0; ci < U; ci++) q[ci] = lds128(row + (((co * U + ci) ^ (lane & 7)) << 4));
+                    for (int ci = 0; ci < U; ci++) q[ci] = lds128(rowx ^ (uint32_t)((co * U + ci) << 4));   // = row + ((c ^ (lane & 7)) << 4): one XOR per piece
 #pragma unroll
                     for (int ci = 0; ci < U; ci++) {
                         const uint32_t wv[4] = {q[ci].x, q[ci].y, q[ci].z, q[ci].w};
