@@ -1,5 +1,6 @@
 // libcaribou_cuda C ABI (include/caribou_cuda.h): context, submit paths, state, utilities.
 #include <limits.h>
+#include <math.h>
 #include <stdarg.h>
 #include <stdlib.h>
 #include <string.h>
@@ -199,8 +200,23 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
         p.scan_rounds = P.scan_rounds;
         // CF32 output without int16 truncation: the float-staged kernel (half the shared memory per warp, more
         // warps per SM).  It stages gain * y_zs, so its R table carries the gain as well.
-        const bool y32 = c->out_mode == OUT_F32 && iir_has_y32(P.K, P.par);
+        const bool y32 = P.y32;        // decided with the plan (it fixes the run length)
         IirTables Tl = T;
+        if (y32 && in_kind != IN_CF32) {
+            // fixed-point staging of the integer-fed float-staged kernels: |gain * y_zs| <= |gain| * l1_zs * max|x|
+            // must fit 31 bits below the binary point F (float input, whose range is unknown, is staged as floats)
+            const double xmax = in_kind == IN_CS16 ? 32768.0 : 4096.0;
+            const double bound = fabs(T.gain) * P.l1_zs * xmax * 1.0001;
+            int e = 900;                                                  // a non-finite bound overflows the output anyway
+            if (std::isfinite(bound)) { e = 0; if (bound > 0) frexp(bound, &e); e = std::min(std::max(e, -900), 900); }   // bound < 2^e
+            const double magic = ldexp(1.5, 21 + e);                 // F = 31 - e: 1.5 * 2^(52-F)
+            const double mo = magic + ldexp(1.0, e);                 // + 2^(31-F): staged words are non-negative
+            unsigned long long mb;
+            memcpy(&mb, &magic, 8);
+            Tl.stage_mo = mo;
+            Tl.stage_hi = (uint32_t)(mb >> 32);
+            Tl.out_bias = T.out_bias + mo;
+        }
         if (y32)
             for (int m = 0; m < kMaxNK; m++)
                 for (int i = 0; i < kMaxS; i++) Tl.R[m][i] *= T.gain;
@@ -428,8 +444,8 @@ caribou_cuda_ctx* caribou_cuda_create(const caribou_cuda_config* cfg_in)
 
     if (cfg.n_sos > 0) {
         const char* msg = "";
-        if (!make_filter_plan(cfg.n_sos, cfg.sos, cfg.decimation, cfg.kernel_form == CARIBOU_CUDA_FORM_CASCADE, &c->plan, &msg)) { set_error("%s", msg); return fail(); }
         if (!resolve_out_mode(cfg.parity, cfg.out_format, &c->out_mode, &c->out_elem)) { set_error("unsupported parity/out_format combination"); return fail(); }
+        if (!make_filter_plan(cfg.n_sos, cfg.sos, cfg.decimation, cfg.kernel_form == CARIBOU_CUDA_FORM_CASCADE, c->out_mode == OUT_F32, &c->plan, &msg)) { set_error("%s", msg); return fail(); }
         const FilterPlan& P = c->plan;
         if (!cuda_ok(cudaMalloc(&c->d_plane, P.plane.size() * 8), "cudaMalloc") ||
             !cuda_ok(cudaMalloc(&c->d_mtile_pow, P.mtile_pow.size() * 8), "cudaMalloc") ||

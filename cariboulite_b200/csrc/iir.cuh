@@ -57,6 +57,11 @@ struct IirTables {
     double sbias[kMaxS];                  // s*: state every run starts from (0 when the input carries no offset)
     double Mp[5][kMaxS * kMaxS];          // M^(2^j), row-major S x S (S = 2K)
     double R[kMaxNK][kMaxS];              // R[m] = Cu A^(m D)
+    // fixed-point staging of the float-output kernels fed with integers: phase 1 stores the low word of
+    // gain * y_zs + stage_mo (stage_mo = 1.5 * 2^(52-F) + 2^(31-F), folded into out_bias), phase 3 rebuilds the
+    // double from that word and stage_hi and subtracts stage_mo again - no FP64<->FP32 conversion on the way
+    double stage_mo;
+    uint32_t stage_hi, stage_pad;
 };
 
 struct IirParams {
@@ -103,7 +108,17 @@ struct IirTailParams {
 #ifndef CBL_IIR_LTMAX
 #define CBL_IIR_LTMAX 128
 #endif
-__host__ __device__ constexpr int iir_run_len(int D) { return D == 1 ? 32 : (D == 2 ? 64 : CBL_IIR_LTMAX); }
+#ifndef CBL_IIR_LTMAX32
+#define CBL_IIR_LTMAX32 256
+#endif
+// run length (samples one thread filters sequentially) for a cascade of K sections and a decimation factor; at
+// most kMaxNK kept outputs per run.  The float-staged kernels (y32) afford 256: half the per-tile work (scan,
+// look-back, ticket) per sample.  It pays from D = 16 on and, at D = 8, for K >= 3 (measured: profiles/r1_sweeps.txt).
+__host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
+{
+    return D == 1 ? 32 : (D == 2 ? 64 : ((y32 && (D >= 16 || (D == 8 && K >= 3))) ? CBL_IIR_LTMAX32
+                                                                                   : (CBL_IIR_LTMAX < 128 ? CBL_IIR_LTMAX : 128)));
+}
 #ifndef CBL_IIR_WPC
 #define CBL_IIR_WPC 3
 #endif

@@ -111,6 +111,16 @@ __device__ __forceinline__ void sts_f32x2(uint32_t a, float x, float y)
 {
     asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(x), "f"(y) : "memory");
 }
+__device__ __forceinline__ void sts_u32x2(uint32_t a, uint32_t x, uint32_t y)
+{
+    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(a), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ uint2 lds_u32x2(uint32_t a)
+{
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a) : "memory");
+    return v;
+}
 __device__ __forceinline__ float2 lds_f32x2(uint32_t a)
 {
     float2 v;
@@ -182,7 +192,7 @@ __device__ __forceinline__ void sample_to_f64(uint32_t w0, uint32_t w1, double& 
 template <int K, int D, int IN, bool Y32>
 struct IirCfg {
     static constexpr int S     = 2 * K;                       // state dimension per rail
-    static constexpr int LT    = iir_run_len(D);              // samples per run
+    static constexpr int LT    = iir_run_len(K, D, Y32);         // samples per run
     static constexpr int NK    = LT / D;                      // kept outputs per run
     static constexpr int SPS   = (IN == IN_CF32) ? 16 : 32;   // samples per 128-byte row step
     static constexpr int NSTEP = LT / SPS;
@@ -241,6 +251,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     using C = IirCfg<K, D, IN, Y32>;
     constexpr int S = C::S;
     constexpr bool INJECT = PAR && IN != IN_CF32;
+    constexpr bool FIXED = IN != IN_CF32;      // float-staged kernels fed with integers stage fixed-point words
     extern __shared__ uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // shared-memory carve-up, as 32-bit shared-window addresses (1024-byte aligned for the 128B swizzle)
@@ -371,7 +382,11 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                                 if (kept) {
                                     // slot m = (gbase + j) / D: 2 rails x 32 lanes x 8 bytes, or 32 lanes x float2
                                     const uint32_t ya_addr = ylane + (uint32_t)(gbase / D) * C::YSLOT_BYTES + (uint32_t)((D <= GS) ? (j / D) : 0) * C::YSLOT_BYTES;
-                                    if (Y32) {
+                                    if (Y32 && FIXED) {
+                                        // T.out_bias carries stage_mo here: the low words are the staged fixed-point values
+                                        sts_u32x2(ya_addr, (uint32_t)__double2loint(fma(ya, T.gain, T.out_bias)),
+                                                  (uint32_t)__double2loint(fma(yb, T.gain, T.out_bias)));
+                                    } else if (Y32) {
                                         sts_f32x2(ya_addr, (float)fma(ya, T.gain, T.out_bias), (float)fma(yb, T.gain, T.out_bias));
                                     } else {
                                         sts64(ya_addr, ya);
@@ -549,8 +564,15 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                     float2* o = reinterpret_cast<float2*>(P.out) + o0;
 #pragma unroll (kP3Unroll)
                     for (int m = 0; m < C::NK; m++) {
-                        const float2 z = lds_f32x2(ystage + m * 256 + lane * 8);
-                        double yi = swap ? (double)z.y : (double)z.x, yq = swap ? (double)z.x : (double)z.y;
+                        double yi, yq;
+                        if (FIXED) {
+                            const uint2 z = lds_u32x2(ystage + m * 256 + lane * 8);
+                            yi = __hiloint2double((int)T.stage_hi, (int)z.x) - T.stage_mo;      // exact
+                            yq = __hiloint2double((int)T.stage_hi, (int)z.y) - T.stage_mo;
+                        } else {
+                            const float2 z = lds_f32x2(ystage + m * 256 + lane * 8);
+                            yi = (double)z.x; yq = (double)z.y;
+                        }
 #pragma unroll
                         for (int c = 0; c < S; c++) {
                             yi = fma(T.R[m][c], si[c], yi);

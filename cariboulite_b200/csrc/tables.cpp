@@ -312,7 +312,7 @@ bool state_map(const Realisation& Rc, const std::vector<ld>& sc, const Realisati
 }
 }  // namespace
 
-bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, FilterPlan* P, const char** msg)
+bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, bool want_y32, FilterPlan* P, const char** msg)
 {
     static const char* e_k = "n_sos must be 1..4";
     static const char* e_d = "decimation must be one of 1,2,4,8,16,32";
@@ -321,8 +321,6 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, 
     if (!(D == 1 || D == 2 || D == 4 || D == 8 || D == 16 || D == 32)) { *msg = e_d; return false; }
     const int S = 2 * K;
     P->K = K; P->D = D; P->S = S;
-    P->LT = iir_run_len(D);
-    P->NK = P->LT / D;
     std::memset(&P->tables, 0, sizeof(P->tables));
     Form Fc;
     Fc.K = K; Fc.par = false;
@@ -416,6 +414,10 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, 
         }
     }
     if (!P->par) { for (int i = 0; i < kMaxS; i++) P->sstar[i] = 0; P->hn1 = 1; }
+    // the float-staged kernels exist for the preferred realisation only; they afford longer runs
+    P->y32 = want_y32 && iir_has_y32(K, P->par);
+    P->LT = iir_run_len(K, D, P->y32);
+    P->NK = P->LT / D;
     for (int k = 0; k < K; k++) {
         P->tables.a1[k] = (double)F.a1[k]; P->tables.a2[k] = (double)F.a2[k];
         P->tables.c1[k] = (double)F.c1[k]; P->tables.c2[k] = (double)F.c2[k];
@@ -439,6 +441,17 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, 
     for (int i = 0; i < S; i++) for (int j = 0; j < S; j++) P->A[i][j] = A.a[i][j];
     P->scale = scale;
 
+    // l1_zs = sum_{k < LT} |hn[k]|, hn = impulse response of y / G: bounds a run's zero-state outputs by
+    // l1_zs * max|x| (the fixed-point staging of the float-output kernels is sized with it)
+    {
+        ld s[kMaxS] = {0}, ns[kMaxS], out, acc = 0;
+        for (int n = 0; n < P->LT; n++) {
+            form_step(F, s, n == 0 ? 1 : 0, ns, &out);
+            acc += fabsl(out);
+            for (int i = 0; i < S; i++) s[i] = ns[i];
+        }
+        P->l1_zs = (double)acc;
+    }
     // R[m] = Cu A^(mD): walk the row vector through the run
     {
         ld r[kMaxS];

@@ -13,6 +13,7 @@ int butter_lowpass_sos(int order, double fs, double fc, double* sos);
 // Everything the kernels need for one (cascade, decimation) pair.
 struct FilterPlan {
     int K = 0, D = 1, LT = 32, NK = 32, S = 0;
+    bool y32 = false;             // float-staged kernels (plain CF32 output, preferred realisation)
     bool par = false;             // kernels run the parallel (partial-fraction) realisation, else the cascade
     const char* form_note = "";   // why the cascade was chosen, when it was
     double par_err = 0;           // parallel vs cascade, rel. rms over a long-double simulation (0 if not tried)
@@ -20,6 +21,7 @@ struct FilterPlan {
     IirTables tables;             // constant-bank tables (gain left at G, sbias/out_bias at 0: the launch fills them)
     double sstar[kMaxS];          // steady state under a unit constant input, kernel coordinates
     double hn1 = 1;               // H(1) / G
+    double l1_zs = 0;             // sum of |impulse response of y / G| over one run: zero-state outputs <= l1_zs * max|x|
     long double Tkr[kMaxS][kMaxS];// kernel state <- reference (DF-II v1,v2) state, per rail
     long double Trk[kMaxS][kMaxS];// reference state <- kernel state
     std::vector<double> plane;    // [S*S][33]  (M^t)[e] at plane[e*33 + t]
@@ -33,7 +35,8 @@ struct FilterPlan {
 };
 
 // false (with msg) if the cascade cannot be handled (b0 == 0, non-finite coefficients, ...)
-bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, FilterPlan* plan, const char** msg);
+// want_y32: the output is plain CF32 (float-staged kernels, longer runs) - plan->y32 says whether they will be used
+bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, bool want_y32, FilterPlan* plan, const char** msg);
 
 // A^n in REFERENCE state coordinates (row-major S x S doubles)
 void plan_shard_matrix(const FilterPlan& plan, uint64_t n, double* m);

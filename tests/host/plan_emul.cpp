@@ -38,7 +38,7 @@ extern "C" {
 int emul_plan_info(int K, const double* sos, int D, int force_cascade, double* info)
 {
     FilterPlan P; const char* msg = "";
-    if (!make_filter_plan(K, (const double(*)[6])sos, D, force_cascade != 0, &P, &msg)) return -1;
+    if (!make_filter_plan(K, (const double(*)[6])sos, D, force_cascade != 0, false, &P, &msg)) return -1;
     info[0] = P.par; info[1] = P.window; info[2] = P.chained; info[3] = (double)P.decay_samples;
     info[4] = P.par_err; info[5] = P.hn1;
     return 0;
@@ -50,7 +50,7 @@ int emul_run(int K, const double* sos, int D, int force_cascade, double bias, do
              const double* x, size_t n, const double* state_ref_in, double* out, double* state_ref_out)
 {
     FilterPlan P; const char* msg = "";
-    if (!make_filter_plan(K, (const double(*)[6])sos, D, force_cascade != 0, &P, &msg)) return -1;
+    if (!make_filter_plan(K, (const double(*)[6])sos, D, force_cascade != 0, false, &P, &msg)) return -1;
     if (!P.par) bias = 0;
     const int S = P.S, LT = P.LT, NK = P.NK;
     if (n % LT) return -2;
@@ -90,7 +90,7 @@ int emul_run(int K, const double* sos, int D, int force_cascade, double bias, do
 double emul_check_powers(int K, const double* sos, int D, int force_cascade)
 {
     FilterPlan P; const char* msg = "";
-    if (!make_filter_plan(K, (const double(*)[6])sos, D, force_cascade != 0, &P, &msg)) return -1;
+    if (!make_filter_plan(K, (const double(*)[6])sos, D, force_cascade != 0, false, &P, &msg)) return -1;
     const int S = P.S;
     double worst = 0;
     for (int j = 0; j < 5; j++)
