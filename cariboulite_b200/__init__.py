@@ -96,6 +96,9 @@ def lib():
         "caribou_cuda_filter_fixup": (i, [vp, i, vp, sz, sz, i, vp, sz, vp]),
         "caribou_cuda_butter_lowpass": (i, [i, C.c_double, C.c_double, vp]),
         "caribou_cuda_synth_words": (i, [vp, vp, u64, sz, i, u64, vp, vp]),
+        "caribou_cuda_tx_pack_submit": (i, [vp, i, vp, sz, i, vp]),
+        "caribou_cuda_smi_write": (i, [vp, i, vp, sz]),
+        "caribou_cuda_txstream_write": (i, [vp, i, C.c_char_p, vp, sz]),
         "caribou_cuda_smi_open": (vp, [i, sz, i]),
         "caribou_cuda_smi_close": (None, [vp]),
         "caribou_cuda_smi_read": (i, [vp, i, vp, vp, sz]),
@@ -128,6 +131,7 @@ EXPORTED_SYMBOLS = [
     "caribou_cuda_smi_get_native_batch_samples", "caribou_cuda_rxstream_create",
     "caribou_cuda_rxstream_destroy", "caribou_cuda_rxstream_set_format", "caribou_cuda_rxstream_set_filter",
     "caribou_cuda_rxstream_mtu", "caribou_cuda_rxstream_read", "caribou_cuda_pump",
+    "caribou_cuda_tx_pack_submit", "caribou_cuda_smi_write", "caribou_cuda_txstream_write",
 ]
 
 
@@ -320,6 +324,14 @@ class Context:
         assert ti.size == 800 and tq.size == 800
         return self._check(lib().caribou_cuda_synth_words(self.h, _ptr(dev_words), n0, n, hif_layout, seed,
                                                           ti.ctypes.data, tq.ctypes.data))
+
+    # -- kernel (c): TX direction
+    def tx_pack_submit(self, in_format, samples, n, words, mem=None):
+        """n samples of `in_format` (FMT_*) -> n SMI TX words; numpy arrays are host memory, torch CUDA tensors
+        device memory (include/caribou_cuda.h, caribou_cuda_tx_pack_submit)."""
+        if mem is None:
+            mem = MEM_HOST if isinstance(samples, np.ndarray) else MEM_DEVICE
+        return self._check(lib().caribou_cuda_tx_pack_submit(self.h, in_format, _ptr(samples), n, mem, _ptr(words)))
 
 
 def build(force=False):

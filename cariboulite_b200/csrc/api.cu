@@ -966,6 +966,53 @@ int caribou_cuda_reset(caribou_cuda_ctx* c)
     return CARIBOU_CUDA_OK;
 }
 
+// ------------------------------------------------------------------ TX direction (kernel (c), tx.cu)
+int caribou_cuda_tx_pack_submit(caribou_cuda_ctx* c, int in_format, const void* samples, size_t n, int mem, void* words)
+{
+    if (!c || (n && (!samples || !words))) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    size_t es = 0;
+    switch (in_format) {
+        case CARIBOU_CUDA_FMT_CS16: es = 4; break;
+        case CARIBOU_CUDA_FMT_CS8:  es = 2; break;
+        case CARIBOU_CUDA_FMT_CF32: es = 8; break;
+        case CARIBOU_CUDA_FMT_CF64: es = 16; break;
+        default: set_error("unknown sample format"); return CARIBOU_CUDA_ERR;
+    }
+    CBL_CHECK(cudaSetDevice(c->device));
+    c->pending.active = false;
+    c->last_is_unpack = false;
+    c->last_n_filtered = 0;
+    c->last_ret = (int64_t)n;
+    if (n == 0) return CARIBOU_CUDA_OK;
+    TxParams p;
+    memset(&p, 0, sizeof(p));
+    p.n = n;
+    p.fmt = in_format;
+    if (mem == CARIBOU_CUDA_MEM_DEVICE) {
+        if ((reinterpret_cast<uintptr_t>(samples) | reinterpret_cast<uintptr_t>(words)) & 15) {
+            set_error("device buffers must be 16-byte aligned");
+            return CARIBOU_CUDA_ERR;
+        }
+        p.in = samples;
+        p.out = static_cast<uint32_t*>(words);
+    } else {
+        if (!c->stage_in.reserve(n * es + 64) || !c->stage_filt.reserve(n * 4 + 64)) return CARIBOU_CUDA_ERR;
+        CBL_CHECK(cudaMemcpyAsync(c->stage_in.p, samples, n * es, cudaMemcpyHostToDevice, c->stream));
+        p.in = c->stage_in.p;
+        p.out = c->stage_filt.as<uint32_t>();
+    }
+    prof_mark(c, 0);
+    const int e = launch_tx_pack(p, c->num_sms, c->stream);
+    prof_mark(c, 1);
+    if (e != 0) { cuda_ok((cudaError_t)e, "tx_pack_kernel launch"); return CARIBOU_CUDA_ERR; }
+    c->launches++;
+    if (mem != CARIBOU_CUDA_MEM_DEVICE) {
+        CBL_CHECK(cudaMemcpyAsync(words, p.out, n * 4, cudaMemcpyDeviceToHost, c->stream));
+        if (mem == CARIBOU_CUDA_MEM_HOST) CBL_CHECK(cudaStreamSynchronize(c->stream));
+    }
+    return CARIBOU_CUDA_OK;
+}
+
 // ------------------------------------------------------------------ synthetic words
 int caribou_cuda_synth_words(caribou_cuda_ctx* c, void* dev_words, uint64_t n0, size_t n, int hif_layout, uint64_t seed,
                              const int16_t* tone_i, const int16_t* tone_q)

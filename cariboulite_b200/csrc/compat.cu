@@ -392,4 +392,53 @@ int64_t caribou_cuda_pump(caribou_cuda_ctx* c, int in_kind, int in_fd, int out_f
     return rc < 0 ? rc : consumed;
 }
 
+// ------------------------------------------------------------------ TX shims
+// caribou_smi_write (caribou_smi.c:720-762): pack on the GPU, then hand native_batch_len bytes at a time to the fd
+// exactly as the reference's loop does.  `format` selects the Stream::WriteSamples conversion that runs first
+// (CaribouliteStream.cpp:199-244); CS16 is caribou_smi_write itself.
+static int tx_write(caribou_cuda_smi* d, int channel, int format, const void* buffer, size_t n)
+{
+    if (!d) { set_error("null device"); return CARIBOU_CUDA_ERR; }
+    caribou_cuda_ctx* c = smi_ctx(d, channel);
+    if (!c) return CARIBOU_CUDA_ERR;
+    if (n == 0) return 0;
+    if (!buffer) { set_error("null buffer"); return CARIBOU_CUDA_ERR; }
+    if (!stage_reserve(d, n * 4)) return CARIBOU_CUDA_ERR;
+    if (caribou_cuda_tx_pack_submit(c, format, buffer, n, CARIBOU_CUDA_MEM_HOST, d->h_stage) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (caribou_cuda_wait(c, nullptr) < 0) return CARIBOU_CUDA_ERR;
+    size_t left = n * CARIBOU_CUDA_BYTES_PER_SAMPLE, written = 0;           // bytes, samples (caribou_smi.c:723-724)
+    while (left) {
+        size_t cur = left > d->native_batch_len ? d->native_batch_len : left;
+        cur &= ~size_t(3);                                                  // :745
+        if (!cur) break;
+        if (!write_full(d->fd, d->h_stage + written * 4, cur)) { set_error("smi write failed (%s)", strerror(errno)); return CARIBOU_CUDA_ERR; }
+        written += cur / CARIBOU_CUDA_BYTES_PER_SAMPLE;
+        left -= cur;
+    }
+    return (int)written;
+}
+
+int caribou_cuda_smi_write(caribou_cuda_smi* d, int channel, const caribou_cuda_sample_complex_int16* samples,
+                           size_t length_samples)
+{
+    return tx_write(d, channel, CARIBOU_CUDA_FMT_CS16, samples, length_samples);
+}
+
+// Stream::WriteSamplesGen (CaribouliteStream.cpp:246-258): formats other than CS16 are clamped to the MTU (:199,214,229),
+// negative results of the CS16 write become 0 (:183-194).
+int caribou_cuda_txstream_write(caribou_cuda_smi* d, int channel, const char* fmt, const void* buffer, size_t num_elements)
+{
+    if (!d || !fmt) { set_error("bad argument"); return 0; }
+    int format = CARIBOU_CUDA_FMT_CS16;
+    if (!strcmp(fmt, "CS16")) format = CARIBOU_CUDA_FMT_CS16;
+    else if (!strcmp(fmt, "CS8")) format = CARIBOU_CUDA_FMT_CS8;
+    else if (!strcmp(fmt, "CF32")) format = CARIBOU_CUDA_FMT_CF32;
+    else if (!strcmp(fmt, "CF64")) format = CARIBOU_CUDA_FMT_CF64;
+    else { set_error("unknown format %s", fmt); return 0; }
+    const size_t mtu = caribou_cuda_smi_get_native_batch_samples(d);
+    if (format != CARIBOU_CUDA_FMT_CS16 && num_elements > mtu) num_elements = mtu;
+    const int ret = tx_write(d, channel, format, buffer, num_elements);
+    return ret < 0 ? 0 : ret;
+}
+
 }  // extern "C"

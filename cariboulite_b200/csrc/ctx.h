@@ -9,6 +9,7 @@
 #include "iir.cuh"
 #include "tables.h"
 #include "unpack.cuh"
+#include "tx.cuh"
 
 namespace cbl {
 

@@ -242,6 +242,24 @@ size_t caribou_cuda_rxstream_mtu(caribou_cuda_rxstream* s);                     
 int    caribou_cuda_rxstream_read(caribou_cuda_rxstream* s, void* buffer, size_t num_elements,
                                   long timeout_us);                                  /* Stream::ReadSamplesGen */
 
+/* ---------------------------------------------------------------- TX direction
+ * Samples -> 32-bit SMI TX words: [SOF TXC CTX I12..I8][0 I7..I1][0 I0 Q12..Q7][0 Q6..Q0], byte 0 first
+ * (caribou_smi_generate_data, LC/caribou_smi/caribou_smi.c:688-717 - as committed the reference packs a constant
+ * test pattern, ii = 0xFFFF / qq = 0, with the sample read commented out; this is that loop reading the samples).
+ * in_format is a caribou_cuda_format: CS16 is the native pair; CS8 (<< 5), CF32 and CF64 ((int16_t)(x * 4096))
+ * are converted first as Stream::WriteSamples does (LC/soapy_api/CaribouliteStream.cpp:199-244).  `words`
+ * receives n_samples uint32.  Device buffers must be 16-byte aligned.  caribou_cuda_wait returns n_samples. */
+int caribou_cuda_tx_pack_submit(caribou_cuda_ctx* ctx, int in_format, const void* samples, size_t n_samples,
+                                int mem, void* words);
+/* int caribou_smi_write(caribou_smi_st*, caribou_smi_channel_en, caribou_smi_sample_complex_int16*, size_t)
+ *                                                                   LC/caribou_smi/caribou_smi.c:720-762 */
+int caribou_cuda_smi_write(caribou_cuda_smi* dev, int channel,
+                           const caribou_cuda_sample_complex_int16* samples, size_t length_samples);
+/* Stream::WriteSamplesGen (CaribouliteStream.cpp:246-258) for the format named like Stream::setFormat names it:
+ * MTU clamp for the converted formats, failures reported as 0 elements. */
+int caribou_cuda_txstream_write(caribou_cuda_smi* dev, int channel, const char* fmt, const void* buffer,
+                                size_t num_elements);
+
 /* ---------------------------------------------------------------- capture pump (file / pipe to file / pipe)
  * The capture loop of cariboulite_util (LC/cariboulite_util.c:340-361: read a block, fwrite ret*4 bytes of raw
  * little-endian CS16) with the sample path on the GPU and the wire format kept.  Reads blocks of `block_samples`

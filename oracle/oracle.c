@@ -152,3 +152,47 @@ void orc_cs16_to_cs8(const int16_t* iq, int8_t* out, size_t n)
 {
     for (size_t k = 0; k < 2 * n; k++) out[k] = (int8_t)((iq[k] >> 5) & 0x00FF);   /* :362-363 */
 }
+
+/* ---- TX direction.  caribou_smi_generate_data, caribou_smi.c:688-717: the reference's loop with
+ * the sample read it has commented out (`cmplx_vec[i].i` / `.q`) put back - as committed it packs the constant
+ * ii = 0xFFFF, qq = 0, which orc_tx_pack reproduces for the sample (i = -1, q = 0); that word is the one vector
+ * the reference pins.  Layout comment caribou_smi.c:693-696:
+ *   [SOF TXC CTX I12..I8] [0 I7..I1] [0 I0 Q12..Q7] [0 Q6..Q0], byte 0 first on the wire (bswap32 on a
+ *   little-endian host). */
+void orc_tx_pack(const int16_t* iq, size_t n, uint32_t* out)
+{
+    for (size_t k = 0; k < n; k++) {
+        int32_t ii = iq[2 * k], qq = iq[2 * k + 1];
+        ii &= 0x1FFF;
+        qq &= 0x1FFF;
+        uint32_t s = (1u << 2) | (1u << 1) | (1u << 0);   /* SMI_TX_SAMPLE_SOF | MODEM_TX_CTRL | COND_TX_CTRL */
+        s <<= 5; s |= (uint32_t)(ii >> 8) & 0x1Fu;
+        s <<= 8; s |= (uint32_t)(ii >> 1) & 0x7Fu;
+        s <<= 2; s |= (uint32_t)(ii & 0x1);
+        s <<= 6; s |= (uint32_t)(qq >> 7) & 0x3Fu;
+        s <<= 8; s |= (uint32_t)(qq & 0x7F);
+        out[k] = __builtin_bswap32(s);
+    }
+}
+/* Stream::WriteSamples conversions to the native int16 pair, CaribouliteStream.cpp:199-244.  The reference's
+ * (int16_t)(x * 4096) is undefined outside the int range; here, as on x86-64 and on the GPU within +-2^31/4096,
+ * it is truncation toward zero to int32 followed by keeping the low 16 bits. */
+static int16_t tx_i16_from_f64(double v)
+{
+    if (!(v > -2147483648.0 && v < 2147483648.0)) return 0;   /* cvttsd2si's "integer indefinite" 0x80000000: low half 0 */
+    return (int16_t)(int32_t)v;
+}
+void orc_tx_from_cf32(const float* x, size_t n, int16_t* iq)
+{
+    const float max_val = 4096.0f;                                      /* :202 */
+    for (size_t k = 0; k < 2 * n; k++) iq[k] = tx_i16_from_f64((double)(x[k] * max_val));
+}
+void orc_tx_from_cf64(const double* x, size_t n, int16_t* iq)
+{
+    const double max_val = 4096.0;                                      /* :217 */
+    for (size_t k = 0; k < 2 * n; k++) iq[k] = tx_i16_from_f64(x[k] * max_val);
+}
+void orc_tx_from_cs8(const int8_t* x, size_t n, int16_t* iq)
+{
+    for (size_t k = 0; k < 2 * n; k++) iq[k] = (int16_t)(((int16_t)x[k]) << 5);     /* :236-237 */
+}

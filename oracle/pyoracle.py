@@ -79,6 +79,9 @@ def lib():
         for f in ("orc_cs16_to_cf32", "orc_cs16_to_cf64", "orc_cs16_to_cs8"):
             getattr(L, f).argtypes = [_p, _p, C.c_size_t]
             getattr(L, f).restype = None
+        for f in ("orc_tx_pack", "orc_tx_from_cf32", "orc_tx_from_cf64", "orc_tx_from_cs8"):
+            getattr(L, f).argtypes = [_p, C.c_size_t, _p]
+            getattr(L, f).restype = None
         _lib = L
     return _lib
 
@@ -172,6 +175,25 @@ def cs16_to_cs8(iq):
     iq = _arr(iq, np.int16)
     out = np.empty(iq.shape, dtype=np.int8)
     lib().orc_cs16_to_cs8(_ptr(iq), _ptr(out), iq.size // 2)
+    return out
+
+
+# ------------------------------------------------------------------ TX direction
+def tx_pack(iq):
+    """caribou_smi_generate_data (caribou_smi.c:688-717) on real samples: CS16 pairs -> 32-bit TX words."""
+    iq = _arr(iq, np.int16)
+    out = np.empty(iq.size // 2, dtype=np.uint32)
+    lib().orc_tx_pack(_ptr(iq), iq.size // 2, _ptr(out))
+    return out
+
+
+def tx_to_cs16(x, fmt):
+    """Stream::WriteSamples conversions (CaribouliteStream.cpp:199-244): CF32 / CF64 / CS8 -> native int16 pairs."""
+    dt, fn = {"CF32": (np.float32, "orc_tx_from_cf32"), "CF64": (np.float64, "orc_tx_from_cf64"),
+              "CS8": (np.int8, "orc_tx_from_cs8")}[fmt]
+    x = _arr(x, dt)
+    out = np.empty(x.shape, dtype=np.int16)
+    getattr(lib(), fn)(_ptr(x), x.size // 2, _ptr(out))
     return out
 
 
@@ -317,6 +339,10 @@ def ref():
         for f in ("ref_dev_smi_read", "ref_dev_radio_read"):
             getattr(R, f).restype = C.c_int
             getattr(R, f).argtypes = [_p, _p, _p, C.c_size_t]
+        R.ref_dev_smi_write.restype = C.c_int
+        R.ref_dev_smi_write.argtypes = [_p, _p, C.c_size_t]
+        R.ref_dev_read_back.restype = C.c_long
+        R.ref_dev_read_back.argtypes = [_p, _p, C.c_size_t]
         R.ref_stream_open.argtypes = [_p]
         R.ref_stream_set_format.argtypes = [_p, C.c_char_p]
         R.ref_stream_set_format.restype = C.c_int
@@ -370,6 +396,15 @@ class RefDev:
                 meta[:] = sentinel & 0xFF
         ret = ref().ref_dev_smi_read(self.h, _ptr(cs16), _ptr(meta), n)
         return ret, cs16, meta
+
+    def smi_write(self, cs16):
+        """The reference's caribou_smi_write on the memfd: (return value, the 32-bit words it handed to the fd)."""
+        cs16 = _arr(cs16, np.int16)
+        n = cs16.size // 2
+        ret = ref().ref_dev_smi_write(self.h, _ptr(cs16), n)
+        out = np.zeros(n * 4 + 16, dtype=np.uint8)
+        got = ref().ref_dev_read_back(self.h, _ptr(out), out.size)
+        return ret, out[:got].view(np.uint32).copy() if got % 4 == 0 else out[:got].copy()
 
     def stream_open(self):
         ref().ref_stream_open(self.h)

@@ -29,6 +29,9 @@ extern "C" {
 
 // ---------------------------------------------------------------- hardware stubs
 extern "C" void io_utils_set_gpio_mode(int gpio, io_utils_alt_en mode) { (void)gpio; (void)mode; }
+// The TX path announces its direction to the kernel driver with an ioctl (caribou_smi.c:30-40) a memfd does not
+// implement; inside this library (linked -Bsymbolic-functions) the driver says yes.  The RX path makes no ioctl.
+extern "C" int ioctl(int fd, unsigned long req, ...) { (void)fd; (void)req; return 0; }
 
 // ---------------------------------------------------------------- radio shims
 // Same forwarding the reference does in cariboulite_radio.c:1258-1315.
@@ -97,6 +100,7 @@ void ref_dev_close(void* h)
     if (d->stream) delete d->stream;
     close(d->sys->smi.filedesc);
     free(d->sys->smi.read_temp_buffer);
+    free(d->sys->smi.write_temp_buffer);
     free(d->sys);
     delete d;
 }
@@ -111,6 +115,34 @@ int ref_dev_smi_read(void* h, int16_t* cs16, uint8_t* meta, size_t length_sample
     return caribou_smi_read(&d->sys->smi, (caribou_smi_channel_en)d->radio->smi_channel_id,
                             (caribou_smi_sample_complex_int16*)cs16, (caribou_smi_sample_meta*)meta,
                             length_samples);
+}
+
+// caribou_smi_write (caribou_smi.c:720-762), unmodified: the memfd receives what the reference would hand to the
+// driver.  write_temp_buffer is what caribou_smi_init allocates (caribou_smi.c:565-571).  The fd is rewound
+// first; returns the reference's return value, the bytes it wrote are read back with ref_dev_read_back.
+int ref_dev_smi_write(void* h, const int16_t* cs16, size_t length_samples)
+{
+    RefDev* d = (RefDev*)h;
+    caribou_smi_st* smi = &d->sys->smi;
+    if (!smi->write_temp_buffer) smi->write_temp_buffer = (uint8_t*)malloc(smi->native_batch_len + 1024);
+    if (ftruncate(smi->filedesc, 0) != 0) return -100;
+    lseek(smi->filedesc, 0, SEEK_SET);
+    return caribou_smi_write(smi, (caribou_smi_channel_en)d->radio->smi_channel_id,
+                             (caribou_smi_sample_complex_int16*)cs16, length_samples);
+}
+long ref_dev_read_back(void* h, uint8_t* out, size_t cap)
+{
+    RefDev* d = (RefDev*)h;
+    const int fd = d->sys->smi.filedesc;
+    const off_t size = lseek(fd, 0, SEEK_END);
+    lseek(fd, 0, SEEK_SET);
+    size_t done = 0;
+    while (done < cap && done < (size_t)size) {
+        ssize_t r = read(fd, out + done, ((size_t)size < cap ? (size_t)size : cap) - done);
+        if (r <= 0) break;
+        done += (size_t)r;
+    }
+    return (long)done;
 }
 
 // cariboulite_radio_read_samples-shaped call (through the shim above).

@@ -3,7 +3,7 @@
 for a handful of shapes, through the C ABI, CUDA events on the launching stream.  One JSON line per case.
 
     python profiles/probe.py [case ...]     cases: fused:<captures>:<log2 words>:<order>:<D>  cf32:<log2 n>:<order>:<D>
-                                                   unpack:<log2 words>:<B>
+                                                   unpack:<log2 words>:<B>  tx:<log2 n>:<CS16|CS8|CF32|CF64>
 """
 import json, os, sys
 import numpy as np
@@ -103,6 +103,22 @@ def main():
             print(json.dumps({"case": case, "ms_median": med, "ms_min": mn, "kernel_ms_avg": ka, "GBps": nbytes / (ka / 1e3) / 1e9,
                               "frac": nbytes / (ka / 1e3) / 1e9 / PEAK, "Gsps": n / (ka / 1e3) / 1e9}), flush=True)
             ctx.close(); del d_w, bufs
+        elif f[0] == "tx":
+            lg, fmt = int(f[1]), f[2]
+            n = 1 << lg
+            dt, es = {"CS16": (torch.int16, 4), "CS8": (torch.int8, 2), "CF32": (torch.float32, 8), "CF64": (torch.float64, 16)}[fmt]
+            x = (torch.rand((n, 2), device=dev) * 2 - 1)
+            x = (x * (4095 if fmt == "CS16" else 127)).to(dt) if fmt in ("CS16", "CS8") else x.to(dt)
+            out = torch.zeros(n, dtype=torch.int32, device=dev)
+            ctx = cb.Context(cuda_stream=stream.cuda_stream)
+            ctx.set_profiling(True)
+            med, mn = timeit(stream, lambda: ctx.tx_pack_submit(getattr(cb, "FMT_" + fmt), x, n, out))
+            k = ctx.read_profile()
+            ka = float(np.mean(k[-20:]))
+            nbytes = n * (es + 4)
+            print(json.dumps({"case": case, "ms_median": med, "ms_min": mn, "kernel_ms_avg": ka, "GBps": nbytes / (ka / 1e3) / 1e9,
+                              "frac": nbytes / (ka / 1e3) / 1e9 / PEAK, "Gsps": n / (ka / 1e3) / 1e9}), flush=True)
+            ctx.close(); del x, out
 
 
 if __name__ == "__main__":
