@@ -99,6 +99,20 @@ def lib():
         "caribou_cuda_tx_pack_submit": (i, [vp, i, vp, sz, i, vp]),
         "caribou_cuda_smi_write": (i, [vp, i, vp, sz]),
         "caribou_cuda_txstream_write": (i, [vp, i, C.c_char_p, vp, sz]),
+        "caribou_cuda_ring_create": (vp, [sz, sz, i, i]),
+        "caribou_cuda_ring_destroy": (None, [vp]),
+        "caribou_cuda_ring_put": (sz, [vp, vp, sz]),
+        "caribou_cuda_ring_get": (sz, [vp, vp, sz, C.c_long]),
+        "caribou_cuda_ring_reset": (None, [vp]),
+        "caribou_cuda_ring_size": (sz, [vp]),
+        "caribou_cuda_ring_capacity": (sz, [vp]),
+        "caribou_cuda_ring_dropped": (u64, [vp]),
+        "caribou_cuda_async_open": (vp, [vp, i, sz]),
+        "caribou_cuda_async_activate": (None, [vp, i]),
+        "caribou_cuda_async_read": (sz, [vp, vp, sz, C.c_long]),
+        "caribou_cuda_async_idle": (i, [vp]),
+        "caribou_cuda_async_ring": (vp, [vp]),
+        "caribou_cuda_async_close": (None, [vp]),
         "caribou_cuda_smi_open": (vp, [i, sz, i]),
         "caribou_cuda_smi_close": (None, [vp]),
         "caribou_cuda_smi_read": (i, [vp, i, vp, vp, sz]),
@@ -132,6 +146,10 @@ EXPORTED_SYMBOLS = [
     "caribou_cuda_rxstream_destroy", "caribou_cuda_rxstream_set_format", "caribou_cuda_rxstream_set_filter",
     "caribou_cuda_rxstream_mtu", "caribou_cuda_rxstream_read", "caribou_cuda_pump",
     "caribou_cuda_tx_pack_submit", "caribou_cuda_smi_write", "caribou_cuda_txstream_write",
+    "caribou_cuda_ring_create", "caribou_cuda_ring_destroy", "caribou_cuda_ring_put", "caribou_cuda_ring_get",
+    "caribou_cuda_ring_reset", "caribou_cuda_ring_size", "caribou_cuda_ring_capacity", "caribou_cuda_ring_dropped",
+    "caribou_cuda_async_open", "caribou_cuda_async_activate", "caribou_cuda_async_read", "caribou_cuda_async_idle",
+    "caribou_cuda_async_ring", "caribou_cuda_async_close",
 ]
 
 

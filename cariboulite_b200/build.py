@@ -14,7 +14,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 CU = ["unpack.cu", "iir.cu", "iir_k1.cu", "iir_k2.cu", "iir_k3.cu", "iir_k4.cu", "iir_k1y.cu", "iir_k2y.cu", "iir_k3y.cu",
       "iir_k4y.cu", "tx.cu", "api.cu", "compat.cu"]
-CPP = ["tables.cpp"]
+CPP = ["tables.cpp", "ring.cpp"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall"]
 
 

@@ -276,6 +276,37 @@ int caribou_cuda_txstream_write(caribou_cuda_smi* dev, int channel, const char* 
 int64_t caribou_cuda_pump(caribou_cuda_ctx* ctx, int in_kind, int in_fd, int out_fd, size_t block_samples,
                           int64_t max_samples);
 
+/* ---------------------------------------------------------------- continuous streaming
+ * The sample queue of the reference's async RX path and its reader thread.
+ * caribou_cuda_ring = circular_buffer<T>(size, override_write, block_read), LC/datatypes/circular_buffer.h:16-92:
+ * capacity rounded up to a power of two; put() drops the oldest elements when override_write is set and the
+ * writer outruns the reader, otherwise takes what fits; get() waits up to timeout_us for `length` elements and
+ * returns 0 without taking any when they did not arrive (block_read), or returns what is there (non-blocking);
+ * data == NULL consumes without copying.  (A put longer than the capacity overruns the reference's buffer; here
+ * it keeps the newest `capacity` elements.)  Elements are elem_bytes wide. */
+typedef struct caribou_cuda_ring caribou_cuda_ring;
+caribou_cuda_ring* caribou_cuda_ring_create(size_t capacity, size_t elem_bytes, int override_write, int block_read);
+void     caribou_cuda_ring_destroy(caribou_cuda_ring* r);
+size_t   caribou_cuda_ring_put(caribou_cuda_ring* r, const void* data, size_t length);
+size_t   caribou_cuda_ring_get(caribou_cuda_ring* r, void* data, size_t length, long timeout_us);
+void     caribou_cuda_ring_reset(caribou_cuda_ring* r);
+size_t   caribou_cuda_ring_size(caribou_cuda_ring* r);
+size_t   caribou_cuda_ring_capacity(caribou_cuda_ring* r);
+uint64_t caribou_cuda_ring_dropped(caribou_cuda_ring* r);      /* elements overwritten before they were read */
+/* ReaderThread + rx_queue of SoapySDR::Stream (LC/soapy_api/CaribouliteStream.cpp:8,16-49,71,94-113,263): a thread
+ * reads one MTU at a time through caribou_cuda_smi_read (the GPU path) and puts the samples into a ring of
+ * capacity_samples (0: 10 MTUs as the reference); caribou_cuda_async_read is rx_queue->get.  The stream starts
+ * inactive (activateStream).  caribou_cuda_async_idle is 1 after a read that returned nothing (a capture file or
+ * pipe that ran dry). */
+typedef struct caribou_cuda_async caribou_cuda_async;
+caribou_cuda_async* caribou_cuda_async_open(caribou_cuda_smi* dev, int channel, size_t capacity_samples);
+void   caribou_cuda_async_activate(caribou_cuda_async* q, int active);
+size_t caribou_cuda_async_read(caribou_cuda_async* q, caribou_cuda_sample_complex_int16* buffer, size_t num_samples,
+                               long timeout_us);
+int    caribou_cuda_async_idle(caribou_cuda_async* q);
+caribou_cuda_ring* caribou_cuda_async_ring(caribou_cuda_async* q);
+void   caribou_cuda_async_close(caribou_cuda_async* q);
+
 #ifdef __cplusplus
 }
 #endif

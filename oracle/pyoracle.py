@@ -343,6 +343,17 @@ def ref():
         R.ref_dev_smi_write.argtypes = [_p, _p, C.c_size_t]
         R.ref_dev_read_back.restype = C.c_long
         R.ref_dev_read_back.argtypes = [_p, _p, C.c_size_t]
+        R.ref_ring_create.restype = _p
+        R.ref_ring_create.argtypes = [C.c_size_t, C.c_int, C.c_int]
+        R.ref_ring_destroy.argtypes = [_p]
+        R.ref_ring_put.restype = C.c_size_t
+        R.ref_ring_put.argtypes = [_p, _p, C.c_size_t]
+        R.ref_ring_get.restype = C.c_size_t
+        R.ref_ring_get.argtypes = [_p, _p, C.c_size_t, C.c_int]
+        for f in ("ref_ring_size", "ref_ring_capacity"):
+            getattr(R, f).restype = C.c_size_t
+            getattr(R, f).argtypes = [_p]
+        R.ref_ring_reset.argtypes = [_p]
         R.ref_stream_open.argtypes = [_p]
         R.ref_stream_set_format.argtypes = [_p, C.c_char_p]
         R.ref_stream_set_format.restype = C.c_int

@@ -315,3 +315,26 @@ extern "C" long ref_rx_path_f32(void* h, void* fi, void* fq, int D, float* out, 
     free(cs16); free(meta);
     return rc < 0 ? rc : (long)m;
 }
+
+// ---------------------------------------------------------------- circular_buffer<T>, unmodified
+// (LC/datatypes/circular_buffer.h, header-only; reaches this file through Cariboulite.hpp.)  Elements are the
+// 4-byte native samples the reference queues (CaribouliteStream.cpp:71).
+extern "C" {
+typedef circular_buffer<cariboulite_sample_complex_int16> RefRing;
+void* ref_ring_create(size_t size, int override_write, int block_read)
+{
+    return new (std::nothrow) RefRing(size, override_write != 0, block_read != 0);
+}
+void ref_ring_destroy(void* r) { delete (RefRing*)r; }
+size_t ref_ring_put(void* r, const void* data, size_t length)
+{
+    return ((RefRing*)r)->put((const cariboulite_sample_complex_int16*)data, length);
+}
+size_t ref_ring_get(void* r, void* data, size_t length, int timeout_us)
+{
+    return ((RefRing*)r)->get((cariboulite_sample_complex_int16*)data, length, timeout_us);
+}
+size_t ref_ring_size(void* r) { return ((RefRing*)r)->size(); }
+size_t ref_ring_capacity(void* r) { return ((RefRing*)r)->capacity(); }
+void ref_ring_reset(void* r) { ((RefRing*)r)->reset(); }
+}  // extern "C"

@@ -193,3 +193,79 @@ def test_pump_reports_lost_sync(cb, po, torch_cuda):
     _, ref_cs16, _, _ = po.smi_read(w.view(np.uint8), 2 * 131072, 0)
     np.testing.assert_array_equal(got, ref_cs16[:2 * 131072])       # the blocks before the bad one were delivered
     os.close(fin); os.close(fout)
+
+
+def _oracle_mtu_reads(po, raw, mtu, channel=0):
+    """What the reader thread queues: caribou_smi_read of one MTU at a time until the capture runs dry."""
+    out, cursor = [], 0
+    buf = np.zeros((mtu + 1, 2), dtype=np.int16)        # one buffer reused like interm_native_buffer1: slots a
+    meta = np.zeros(mtu + 1, dtype=np.uint8)            # misaligned chunk leaves untouched keep the previous block
+    while True:
+        r, _, _, cursor = po.smi_read(raw, mtu, channel, mtu * 4, cursor, cs16=buf, meta=meta)
+        if r <= 0:
+            break
+        out.append(buf[:r].copy())
+    return np.concatenate(out)
+
+
+@pytest.mark.parametrize("drop", [0, 3])
+def test_async_reader_delivers_the_stream_in_order(cb, po, torch_cuda, drop):
+    """ReaderThread + rx_queue->get (CaribouliteStream.cpp:16-49, 263): inactive until activated, then every MTU the
+    GPU path decodes arrives once and in order; a read that cannot be satisfied in time takes nothing."""
+    import time
+    L = cb.lib()
+    mtu = 8192
+    raw = np.ascontiguousarray(po.gen_words(mtu * 7 + 100).view(np.uint8)[drop:])
+    ref = _oracle_mtu_reads(po, raw, mtu)
+    s = Smi(cb, raw, nbl=mtu * 4)
+    q = L.caribou_cuda_async_open(s.h, 0, 0)
+    assert q, cb.last_error()
+    try:
+        ring = L.caribou_cuda_async_ring(q)
+        assert L.caribou_cuda_ring_capacity(ring) == 131072                 # 10 MTUs rounded up to a power of two
+        buf = np.zeros((4096, 2), dtype=np.int16)
+        assert L.caribou_cuda_async_read(q, buf.ctypes.data, 100, 30000) == 0     # not active yet
+        L.caribou_cuda_async_activate(q, 1)
+        got, total = [], 0
+        for n in [100, 4096, 1, 3000, 4096, 4096, 4096] * 4:
+            n = min(n, ref.shape[0] - total)
+            if n == 0:
+                break
+            assert L.caribou_cuda_async_read(q, buf.ctypes.data, n, 5000000) == n
+            got.append(buf[:n].copy()); total += n
+        np.testing.assert_array_equal(np.concatenate(got), ref)
+        t0 = time.time()
+        while not L.caribou_cuda_async_idle(q) and time.time() - t0 < 5:
+            time.sleep(0.01)
+        assert L.caribou_cuda_async_idle(q) == 1
+        assert L.caribou_cuda_async_read(q, buf.ctypes.data, 1, 20000) == 0       # the capture ran dry
+    finally:
+        L.caribou_cuda_async_close(q)
+        s.close()
+
+
+def test_async_reader_overrides_the_oldest_samples(cb, po, torch_cuda):
+    """USE_ASYNC_OVERRIDE_WRITES (CaribouliteStream.cpp:11): a consumer that does not read loses the oldest samples,
+    never the newest."""
+    import time
+    L = cb.lib()
+    mtu = 8192
+    raw = po.gen_words(mtu * 6).view(np.uint8)
+    ref = _oracle_mtu_reads(po, raw, mtu)
+    s = Smi(cb, raw, nbl=mtu * 4)
+    q = L.caribou_cuda_async_open(s.h, 0, 2 * mtu)
+    assert q, cb.last_error()
+    try:
+        L.caribou_cuda_async_activate(q, 1)
+        t0 = time.time()
+        while not L.caribou_cuda_async_idle(q) and time.time() - t0 < 10:
+            time.sleep(0.01)
+        ring = L.caribou_cuda_async_ring(q)
+        assert L.caribou_cuda_ring_size(ring) == 2 * mtu
+        assert L.caribou_cuda_ring_dropped(ring) == 4 * mtu
+        buf = np.zeros((2 * mtu, 2), dtype=np.int16)
+        assert L.caribou_cuda_async_read(q, buf.ctypes.data, 2 * mtu, 100000) == 2 * mtu
+        np.testing.assert_array_equal(buf, ref[-2 * mtu:])
+    finally:
+        L.caribou_cuda_async_close(q)
+        s.close()
