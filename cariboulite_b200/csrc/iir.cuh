@@ -104,6 +104,10 @@ struct IirTailParams {
     const int32_t* gate;                    // optional: no-op when *gate != 0
 };
 
+// run length of the float-staged order-3/4 kernels at decimation 8
+#ifndef CBL_IIR_LT_K2D8
+#define CBL_IIR_LT_K2D8 160
+#endif
 // run length for a decimation factor
 #ifndef CBL_IIR_LTMAX
 #define CBL_IIR_LTMAX 128
@@ -117,28 +121,16 @@ struct IirTailParams {
 __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
 {
     return D == 1 ? 32 : (D == 2 ? 64 : ((y32 && (D >= 16 || (D == 8 && K >= 3))) ? CBL_IIR_LTMAX32
-                                                                                   : (CBL_IIR_LTMAX < 128 ? CBL_IIR_LTMAX : 128)));
+                        : ((y32 && D == 8 && K == 2) ? CBL_IIR_LT_K2D8 : (CBL_IIR_LTMAX < 128 ? CBL_IIR_LTMAX : 128))));
 }
-#ifndef CBL_IIR_WPC
-#define CBL_IIR_WPC 3
-#endif
 #ifndef CBL_IIR_STAGES
 #define CBL_IIR_STAGES 2
-#endif
-#ifndef CBL_IIR_WPC32
-#define CBL_IIR_WPC32 2
 #endif
 #ifndef CBL_IIR_STAGES32
 #define CBL_IIR_STAGES32 2
 #endif
-#ifndef CBL_IIR_MINCTAS32
-#define CBL_IIR_MINCTAS32 1
-#endif
-constexpr int kIirMinCtas32 = CBL_IIR_MINCTAS32;    // __launch_bounds__ min CTAs per SM of the float-staged kernels (register cap)
-constexpr int kIirWarpsPerCta = CBL_IIR_WPC;        // double-staged kernels: 3 warps x ~25 KiB, 3 CTAs per SM
-constexpr int kIirRingStages  = CBL_IIR_STAGES;
-constexpr int kIirWarpsPerCta32 = CBL_IIR_WPC32;    // float-staged kernels: 2 warps x ~16 KiB, 6 CTAs per SM (sweep: profiles/r1_sweeps.txt)
-constexpr int kIirRingStages32  = CBL_IIR_STAGES32;
+constexpr int kIirRingStages   = CBL_IIR_STAGES;      // TMA ring depth per warp, double-staged kernels
+constexpr int kIirRingStages32 = CBL_IIR_STAGES32;    // float-staged kernels (sweep: profiles/r1_sweeps.txt)
 // look-back descriptors: a slot holds this bit pattern (a NaN no computation produces) until its owner
 // has written it; a value that happens to equal it is nudged to the neighbouring NaN pattern
 constexpr unsigned long long kDescEmpty = 0xFFFFFFFFFFFFFFFFull;

@@ -189,7 +189,20 @@ __device__ __forceinline__ void sample_to_f64(uint32_t w0, uint32_t w1, double& 
 
 // Y32: the zero-state outputs are staged as (already scaled) floats instead of doubles - half the shared memory
 // per warp, which buys occupancy; used when the output itself is CF32 without the int16 truncation.
-template <int K, int D, int IN, bool Y32>
+// One CTA per SM holding as many warps as shared memory and the register file allow: the same number of warps
+// in six 2-warp CTAs is 7 % slower (profiles/r1_sweeps.txt, sweep 18).  The register file is four banks of 16K,
+// one per SMSP, and warp w of a CTA lives on SMSP w % 4: up to 8 warps (2 per SMSP) a thread may use 255
+// registers, from 9 on (3 on some SMSP) 168.  Registers per thread (cuobjdump -res-usage): parallel form
+// 120-168 for K <= 2 with float staging, up to 190 with double staging, ~205 (K = 3), ~250 (K = 4); the cascade
+// form of K > 1 and the D = 1 kernels (32 kept outputs per run) 200-250.
+__host__ __device__ constexpr int iir_reg_warps(int K, int D, bool par, bool y32)
+{
+    return ((!par && K > 1) || K >= 3 || D == 1) ? 8 : ((K == 2 && !y32) ? 8 : 12);
+}
+#ifndef CBL_IIR_WPC_CAP
+#define CBL_IIR_WPC_CAP 16
+#endif
+template <int K, int D, int IN, bool PAR, bool Y32>
 struct IirCfg {
     static constexpr int S     = 2 * K;                       // state dimension per rail
     static constexpr int LT    = iir_run_len(K, D, Y32);         // samples per run
@@ -198,12 +211,17 @@ struct IirCfg {
     static constexpr int NSTEP = LT / SPS;
     static constexpr int RSTG  = Y32 ? kIirRingStages32 : kIirRingStages;
     static constexpr int STAGES = (NSTEP < RSTG) ? NSTEP : RSTG;
-    static constexpr int WPC   = Y32 ? kIirWarpsPerCta32 : kIirWarpsPerCta;
     static constexpr int RING_BYTES    = STAGES * 4096;
     static constexpr int YSLOT_BYTES   = Y32 ? 256 : 512;      // one kept output of all 32 lanes: float2 / 2 doubles each
     static constexpr int YSTAGE_BYTES  = NK * YSLOT_BYTES;     // one tile's zero-state outputs; two of them per warp
     static constexpr int SCRATCH_BYTES = 2 * S * 8 * 2;        // S_in broadcast + spare
     static constexpr int WARP_BYTES = RING_BYTES + 2 * YSTAGE_BYTES + SCRATCH_BYTES;
+    // 227 KiB per CTA minus the alignment slack of the carve-up
+    static constexpr int SMEM_WARPS = (232448 - 1024) / (WARP_BYTES + STAGES * 8);
+    static constexpr int REG_WARPS  = iir_reg_warps(K, D, PAR, Y32);
+    static constexpr int WPC_ = SMEM_WARPS < REG_WARPS ? SMEM_WARPS : REG_WARPS;
+    static constexpr int WPC  = WPC_ < CBL_IIR_WPC_CAP ? WPC_ : CBL_IIR_WPC_CAP;     // warps per CTA = per SM
+    static_assert(WPC >= 1, "a warp's buffers do not fit shared memory");
 #ifndef CBL_EXP_SMEM_PAD
 #define CBL_EXP_SMEM_PAD 0
 #endif
@@ -244,11 +262,11 @@ template <bool PAR> __device__ __forceinline__ constexpr int col_lo(int row) { r
 __device__ __forceinline__ constexpr int col_hi(int row) { return 2 * (row / 2 + 1); }
 
 template <int K, int D, int IN, bool PAR, bool Y32>
-__global__ void __launch_bounds__((IirCfg<K, D, IN, Y32>::WPC) * 32, (Y32 ? kIirMinCtas32 : 1))
+__global__ void __launch_bounds__((IirCfg<K, D, IN, PAR, Y32>::WPC) * 32, 1)
 iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ IirParams P,
                 const __grid_constant__ IirTables T)
 {
-    using C = IirCfg<K, D, IN, Y32>;
+    using C = IirCfg<K, D, IN, PAR, Y32>;
     constexpr int S = C::S;
     constexpr bool INJECT = PAR && IN != IN_CF32;
     constexpr bool FIXED = IN != IN_CF32;      // float-staged kernels fed with integers stage fixed-point words
@@ -651,7 +669,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
 template <int K, int D, int IN, bool PAR, bool Y32>
 int launch_iir_t(const CUtensorMap& tmap, const IirParams& p, const IirTables& t, int num_sms, cudaStream_t st)
 {
-    using C = IirCfg<K, D, IN, Y32>;
+    using C = IirCfg<K, D, IN, PAR, Y32>;
     auto kern = iir_scan_kernel<K, D, IN, PAR, Y32>;
     static int occ = 0;
     if (occ == 0) {
