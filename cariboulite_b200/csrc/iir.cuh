@@ -104,24 +104,26 @@ struct IirTailParams {
     const int32_t* gate;                    // optional: no-op when *gate != 0
 };
 
-// run length of the float-staged order-3/4 kernels at decimation 8
-#ifndef CBL_IIR_LT_K2D8
-#define CBL_IIR_LT_K2D8 160
+// Run length LT (samples one thread filters sequentially) for a cascade of K sections and a decimation factor D.
+// Longer runs mean less per-tile work (scan, look-back, ticket) per sample, but a warp stages two tiles' kept
+// outputs (LT / D slots each) in shared memory, and the CTA wants all the warps the register file allows
+// (iir_kernel.cuh: 12 for the float-staged kernels of K <= 2, else 8): LT is the longest multiple of 32 whose
+// stage still lets that many warps fit, at most kMaxNK kept outputs per run (profiles/r1_sweeps.txt, sweeps 17-19).
+#ifndef CBL_IIR_LT_D4
+#define CBL_IIR_LT_D4 128        // measured: 128 at 9 warps beats the formula's 64 at 12 (sweep 19)
 #endif
-// run length for a decimation factor
-#ifndef CBL_IIR_LTMAX
-#define CBL_IIR_LTMAX 128
-#endif
-#ifndef CBL_IIR_LTMAX32
-#define CBL_IIR_LTMAX32 256
-#endif
-// run length (samples one thread filters sequentially) for a cascade of K sections and a decimation factor; at
-// most kMaxNK kept outputs per run.  The float-staged kernels (y32) afford 256: half the per-tile work (scan,
-// look-back, ticket) per sample.  It pays from D = 16 on and, at D = 8, for K >= 3 (measured: profiles/r1_sweeps.txt).
+__host__ __device__ constexpr int iir_target_warps(int K, bool y32) { return (K <= 2 && y32) ? 12 : 8; }
 __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
 {
-    return D == 1 ? 32 : (D == 2 ? 64 : ((y32 && (D >= 16 || (D == 8 && K >= 3))) ? CBL_IIR_LTMAX32
-                        : ((y32 && D == 8 && K == 2) ? CBL_IIR_LT_K2D8 : (CBL_IIR_LTMAX < 128 ? CBL_IIR_LTMAX : 128))));
+    if (D == 1) return 32;
+    if (D == 2) return 64;
+    if (D == 4 && CBL_IIR_LT_D4 != 0) return CBL_IIR_LT_D4;
+    const int slot = y32 ? 256 : 512;                                    // bytes per kept output of a warp
+    const int per_warp = (232448 - 1024) / iir_target_warps(K, y32) - 2 * 4096 - 2 * 2 * kMaxK * 8 - 16;   // minus ring, scratch, barriers
+    int nk = per_warp / (2 * slot);
+    if (nk > kMaxNK) nk = kMaxNK;
+    int lt = (nk * D / 32) * 32;
+    return lt < 32 ? 32 : lt;
 }
 #ifndef CBL_IIR_STAGES
 #define CBL_IIR_STAGES 2
