@@ -112,7 +112,10 @@ struct IirTailParams {
 #ifndef CBL_IIR_LT_D4
 #define CBL_IIR_LT_D4 128        // measured: 128 at 9 warps beats the formula's 64 at 12 (sweep 19)
 #endif
-__host__ __device__ constexpr int iir_target_warps(int K, bool y32) { return (K <= 2 && y32) ? 12 : 8; }
+#ifndef CBL_IIR_K3_WARPS
+#define CBL_IIR_K3_WARPS 12      // float-staged parallel-form kernels of 3 sections: 8 (255 registers) or 12 (168, small spills)
+#endif
+__host__ __device__ constexpr int iir_target_warps(int K, bool y32) { return (K <= 2 && y32) ? 12 : ((K == 3 && y32) ? CBL_IIR_K3_WARPS : 8); }
 __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
 {
     if (D == 1) return 32;

@@ -197,7 +197,8 @@ __device__ __forceinline__ void sample_to_f64(uint32_t w0, uint32_t w1, double& 
 // form of K > 1 and the D = 1 kernels (32 kept outputs per run) 200-250.
 __host__ __device__ constexpr int iir_reg_warps(int K, int D, bool par, bool y32)
 {
-    return ((!par && K > 1) || K >= 3 || D == 1) ? 8 : ((K == 2 && !y32) ? 8 : 12);
+    return (K == 3 && par && y32 && D != 1) ? CBL_IIR_K3_WARPS
+         : (((!par && K > 1) || K >= 3 || D == 1) ? 8 : ((K == 2 && !y32) ? 8 : 12));
 }
 #ifndef CBL_IIR_WPC_CAP
 #define CBL_IIR_WPC_CAP 16
