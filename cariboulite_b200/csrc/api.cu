@@ -198,6 +198,7 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
         p.inj_mul = 1u << 31;
         p.inj_xor = in_kind == IN_WORDS ? 0x82602000u : 0x82808000u;
         p.scan_rounds = P.scan_rounds;
+        p.out_vec = ((reinterpret_cast<uintptr_t>(d_out) & 31) == 0 && (out_stride & 3) == 0) ? 1 : 0;
         // CF32 output without int16 truncation: the float-staged kernel (half the shared memory per warp, more
         // warps per SM).  It stages gain * y_zs, so its R table carries the gain as well.
         const bool y32 = P.y32;        // decided with the plan (it fixes the run length)

@@ -90,6 +90,7 @@ struct IirParams {
     // mantissa injection (iir_kernel.cuh inject_f64): sign-flip | exponent << 1 word, and the multiplier 2^31
     uint32_t  inj_xor, inj_mul;
     int       scan_rounds;      // Kogge-Stone rounds of the warp scan that can still contribute (<= 5)
+    int       out_vec;          // CF32 output may be stored 32 bytes at a time (base and stream stride 32-byte aligned)
 };
 
 struct IirTailParams {
@@ -125,6 +126,7 @@ __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
     const int per_warp = (232448 - 1024) / iir_target_warps(K, y32) - 2 * 4096 - 2 * 2 * kMaxK * 8 - 16;   // minus ring, scratch, barriers
     int nk = per_warp / (2 * slot);
     if (nk > kMaxNK) nk = kMaxNK;
+    nk &= ~3;                                                             // phase 3 works in chunks of 4 kept outputs
     int lt = (nk * D / 32) * 32;
     return lt < 32 ? 32 : lt;
 }

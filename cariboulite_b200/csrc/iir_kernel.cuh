@@ -19,9 +19,6 @@
 // behind, which otherwise synchronises all warps of the GPU into one convoy.
 #pragma once
 #include "iir.cuh"
-#ifndef CBL_P3_UNROLL
-#define CBL_P3_UNROLL 4
-#endif
 #ifndef CBL_P1_UNROLL
 #define CBL_P1_UNROLL 8
 #endif
@@ -30,7 +27,7 @@ namespace cbl { constexpr int kP3GenUnroll = 4; }
 #else
 namespace cbl { constexpr int kP3GenUnroll = 1; }
 #endif
-namespace cbl { constexpr int kP3Unroll = CBL_P3_UNROLL; constexpr int kP1Unroll = CBL_P1_UNROLL; }
+namespace cbl { constexpr int kP1Unroll = CBL_P1_UNROLL; }
 
 namespace cbl {
 
@@ -126,6 +123,13 @@ __device__ __forceinline__ float2 lds_f32x2(uint32_t a)
     float2 v;
     asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a) : "memory");
     return v;
+}
+// 32-byte streaming store: four consecutive CF32 outputs of one lane = one full sector (STG.256).  A warp's
+// outputs are NK * 8 bytes apart from lane to lane, so 8-byte stores touch each sector four times.
+__device__ __forceinline__ void stg_cf32x4(float2* p, float2 a, float2 b, float2 c, float2 d)
+{
+    asm volatile("st.global.cs.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 ::"l"(p), "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y), "f"(d.x), "f"(d.y) : "memory");
 }
 __device__ __forceinline__ double shfl_up_f64(double v, int d)
 {
@@ -581,37 +585,60 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                 if (Y32) {
                     // staged values are gain * y_zs already, T.R is gain * R (run_iir scales it for these launches)
                     float2* o = reinterpret_cast<float2*>(P.out) + o0;
-#pragma unroll (kP3Unroll)
-                    for (int m = 0; m < C::NK; m++) {
-                        double yi, yq;
-                        if (FIXED) {
-                            const uint2 z = lds_u32x2(ystage + m * 256 + lane * 8);
-                            yi = __hiloint2double((int)T.stage_hi, (int)z.x) - T.stage_mo;      // exact
-                            yq = __hiloint2double((int)T.stage_hi, (int)z.y) - T.stage_mo;
-                        } else {
-                            const float2 z = lds_f32x2(ystage + m * 256 + lane * 8);
-                            yi = (double)z.x; yq = (double)z.y;
-                        }
+                    static_assert(C::NK % 4 == 0, "kept outputs per run come in chunks of 4");
+#pragma unroll 1
+                    for (int m0 = 0; m0 < C::NK; m0 += 4) {
+                        float2 r[4];
 #pragma unroll
-                        for (int c = 0; c < S; c++) {
-                            yi = fma(T.R[m][c], si[c], yi);
-                            yq = fma(T.R[m][c], sq[c], yq);
+                        for (int i = 0; i < 4; i++) {
+                            const int m = m0 + i;
+                            double yi, yq;
+                            if (FIXED) {
+                                const uint2 z = lds_u32x2(ystage + m * 256 + lane * 8);
+                                yi = __hiloint2double((int)T.stage_hi, (int)z.x) - T.stage_mo;      // exact
+                                yq = __hiloint2double((int)T.stage_hi, (int)z.y) - T.stage_mo;
+                            } else {
+                                const float2 z = lds_f32x2(ystage + m * 256 + lane * 8);
+                                yi = (double)z.x; yq = (double)z.y;
+                            }
+#pragma unroll
+                            for (int c = 0; c < S; c++) {
+                                yi = fma(T.R[m][c], si[c], yi);
+                                yq = fma(T.R[m][c], sq[c], yq);
+                            }
+                            r[i] = make_float2((float)yi, (float)yq);
                         }
-                        __stcs(o + m, make_float2((float)yi, (float)yq));
+                        if (P.out_vec) {
+                            stg_cf32x4(o + m0, r[0], r[1], r[2], r[3]);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 4; i++) __stcs(o + m0 + i, r[i]);
+                        }
                     }
                 } else if (P.out_mode == OUT_F32) {
                     float2* o = reinterpret_cast<float2*>(P.out) + o0;
-#pragma unroll (kP3Unroll)
-                    for (int m = 0; m < C::NK; m++) {
-                        double yi = lds64(yi0 + m * 512), yq = lds64(yq0 + m * 512);
+#pragma unroll 1
+                    for (int m0 = 0; m0 < C::NK; m0 += 4) {
+                        float2 r[4];
 #pragma unroll
-                        for (int c = 0; c < S; c++) {
-                            yi = fma(T.R[m][c], si[c], yi);
-                            yq = fma(T.R[m][c], sq[c], yq);
+                        for (int i = 0; i < 4; i++) {
+                            const int m = m0 + i;
+                            double yi = lds64(yi0 + m * 512), yq = lds64(yq0 + m * 512);
+#pragma unroll
+                            for (int c = 0; c < S; c++) {
+                                yi = fma(T.R[m][c], si[c], yi);
+                                yq = fma(T.R[m][c], sq[c], yq);
+                            }
+                            yi = fma(yi, T.gain, T.out_bias);
+                            yq = fma(yq, T.gain, T.out_bias);
+                            r[i] = make_float2((float)yi, (float)yq);
                         }
-                        yi = fma(yi, T.gain, T.out_bias);
-                        yq = fma(yq, T.gain, T.out_bias);
-                        __stcs(o + m, make_float2((float)yi, (float)yq));
+                        if (P.out_vec) {
+                            stg_cf32x4(o + m0, r[0], r[1], r[2], r[3]);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 4; i++) __stcs(o + m0 + i, r[i]);
+                        }
                     }
                 } else if (!Y32) {
 #pragma unroll (kP3GenUnroll)
@@ -701,13 +728,13 @@ int launch_iir_t(const CUtensorMap& tmap, const IirParams& p, const IirTables& t
 
 typedef int (*iir_launch_fn)(const CUtensorMap&, const IirParams&, const IirTables&, int, cudaStream_t);
 
-// K == 1 has a single section: the parallel form is the cascade, only the cascade kernel is built.
-// The float-staged (Y32) kernels exist for the preferred realisation only (parallel for K > 1).
+// The float-staged (Y32) kernels exist for the preferred realisation only: the parallel form, also for a single
+// section (x + alpha v1 + beta v2 is what lets the integer inputs enter by mantissa injection).
 template <int KK, bool Y32>
 iir_launch_fn iir_pick_launch(int D, int in_kind, bool par)
 {
-    constexpr bool PREF = KK > 1;        // the realisation AUTO picks when the poles allow it
-    if (par == PREF || (par && KK == 1)) {
+    constexpr bool PREF = true;          // the realisation AUTO picks when the poles allow it
+    if (par == PREF) {
         if (in_kind == IN_WORDS) { CBL_IIR_DISPATCH_D(KK, IN_WORDS, PREF, Y32) }
         if (in_kind == IN_WORDS_HIF) { CBL_IIR_DISPATCH_D(KK, IN_WORDS_HIF, PREF, Y32) }
         if (in_kind == IN_CS16)  { CBL_IIR_DISPATCH_D(KK, IN_CS16, PREF, Y32) }

@@ -347,7 +347,6 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, 
     Mat Tp = mat_eye(S);          // kernel <- normalised cascade coordinates
     P->par = false; P->par_err = 0; P->form_note = "";
     if (force_cascade) P->form_note = "cascade form requested";
-    else if (K == 1) P->form_note = "single section";
     else {
         Form Fp = Fc;
         Fp.par = true;
