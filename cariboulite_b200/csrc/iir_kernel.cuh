@@ -22,11 +22,6 @@
 #ifndef CBL_P1_UNROLL
 #define CBL_P1_UNROLL 8
 #endif
-#ifdef CBL_NO_FASTPATH
-namespace cbl { constexpr int kP3GenUnroll = 4; }
-#else
-namespace cbl { constexpr int kP3GenUnroll = 1; }
-#endif
 namespace cbl { constexpr int kP1Unroll = CBL_P1_UNROLL; }
 
 namespace cbl {
@@ -130,6 +125,10 @@ __device__ __forceinline__ void stg_cf32x4(float2* p, float2 a, float2 b, float2
 {
     asm volatile("st.global.cs.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
                  ::"l"(p), "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y), "f"(d.x), "f"(d.y) : "memory");
+}
+__device__ __forceinline__ void stg_f64x4(double* p, double a, double b, double c, double d)
+{
+    asm volatile("st.global.cs.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
 }
 __device__ __forceinline__ double shfl_up_f64(double v, int d)
 {
@@ -641,34 +640,84 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                         }
                     }
                 } else if (!Y32) {
-#pragma unroll (kP3GenUnroll)
-                    for (int m = 0; m < C::NK; m++) {
-                        double yi = lds64(yi0 + m * 512), yq = lds64(yq0 + m * 512);
+                    // the Soapy formats and CF64: chunks of 4 outputs per lane, one vector store per chunk where
+                    // the buffer allows it (out_vec)
+#pragma unroll 1
+                    for (int m0 = 0; m0 < C::NK; m0 += 4) {
+                        double yi[4], yq[4];
 #pragma unroll
-                        for (int c = 0; c < S; c++) {
-                            yi = fma(T.R[m][c], si[c], yi);
-                            yq = fma(T.R[m][c], sq[c], yq);
+                        for (int i = 0; i < 4; i++) {
+                            const int m = m0 + i;
+                            double a = lds64(yi0 + m * 512), b = lds64(yq0 + m * 512);
+#pragma unroll
+                            for (int c = 0; c < S; c++) {
+                                a = fma(T.R[m][c], si[c], a);
+                                b = fma(T.R[m][c], sq[c], b);
+                            }
+                            yi[i] = fma(a, T.gain, T.out_bias);
+                            yq[i] = fma(b, T.gain, T.out_bias);
                         }
-                        yi = fma(yi, T.gain, T.out_bias);
-                        yq = fma(yq, T.gain, T.out_bias);
-                        const uint64_t o = o0 + m;
+                        const uint64_t o = o0 + m0;
                         if (P.out_mode == OUT_F64) {
-                            __stcs(reinterpret_cast<double2*>(P.out) + o, make_double2(yi, yq));
+                            double2* op = reinterpret_cast<double2*>(P.out) + o;
+                            if (P.out_vec) {
+                                stg_f64x4(&op[0].x, yi[0], yq[0], yi[1], yq[1]);
+                                stg_f64x4(&op[2].x, yi[2], yq[2], yi[3], yq[3]);
+                            } else {
+#pragma unroll
+                                for (int i = 0; i < 4; i++) __stcs(op + i, make_double2(yi[i], yq[i]));
+                            }
                         } else {
                             // (int16_t)(float)y, CaribouliteStream.cpp:295-296: round to float, truncate toward zero
-                            const int qi = (int)(int16_t)__float2int_rz((float)yi);
-                            const int qq = (int)(int16_t)__float2int_rz((float)yq);
+                            int qi[4], qq[4];
+#pragma unroll
+                            for (int i = 0; i < 4; i++) {
+                                qi[i] = (int)(int16_t)__float2int_rz((float)yi[i]);
+                                qq[i] = (int)(int16_t)__float2int_rz((float)yq[i]);
+                            }
                             if (P.out_mode == OUT_Q16_CS16) {
-                                reinterpret_cast<uint32_t*>(P.out)[o] = ((uint32_t)qi & 0xFFFFu) | ((uint32_t)qq << 16);
+                                uint32_t w[4];
+#pragma unroll
+                                for (int i = 0; i < 4; i++) w[i] = ((uint32_t)qi[i] & 0xFFFFu) | ((uint32_t)qq[i] << 16);
+                                uint32_t* op = reinterpret_cast<uint32_t*>(P.out) + o;
+                                if (P.out_vec) {
+                                    __stcs(reinterpret_cast<uint4*>(op), make_uint4(w[0], w[1], w[2], w[3]));
+                                } else {
+#pragma unroll
+                                    for (int i = 0; i < 4; i++) op[i] = w[i];
+                                }
                             } else if (P.out_mode == OUT_Q16_CF32) {
-                                __stcs(reinterpret_cast<float2*>(P.out) + o,
-                                       make_float2((float)qi * (1.0f / 4096.0f), (float)qq * (1.0f / 4096.0f)));
+                                float2 r[4];
+#pragma unroll
+                                for (int i = 0; i < 4; i++) r[i] = make_float2((float)qi[i] * (1.0f / 4096.0f), (float)qq[i] * (1.0f / 4096.0f));
+                                float2* op = reinterpret_cast<float2*>(P.out) + o;
+                                if (P.out_vec) {
+                                    stg_cf32x4(op, r[0], r[1], r[2], r[3]);
+                                } else {
+#pragma unroll
+                                    for (int i = 0; i < 4; i++) __stcs(op + i, r[i]);
+                                }
                             } else if (P.out_mode == OUT_Q16_CF64) {
-                                __stcs(reinterpret_cast<double2*>(P.out) + o,
-                                       make_double2((double)qi * (1.0 / 4096.0), (double)qq * (1.0 / 4096.0)));
+                                double2* op = reinterpret_cast<double2*>(P.out) + o;
+                                const double k = 1.0 / 4096.0;
+                                if (P.out_vec) {
+                                    stg_f64x4(&op[0].x, (double)qi[0] * k, (double)qq[0] * k, (double)qi[1] * k, (double)qq[1] * k);
+                                    stg_f64x4(&op[2].x, (double)qi[2] * k, (double)qq[2] * k, (double)qi[3] * k, (double)qq[3] * k);
+                                } else {
+#pragma unroll
+                                    for (int i = 0; i < 4; i++) __stcs(op + i, make_double2((double)qi[i] * k, (double)qq[i] * k));
+                                }
                             } else {   // OUT_Q16_CS8, CaribouliteStream.cpp:362-363
-                                reinterpret_cast<uint16_t*>(P.out)[o] =
-                                    (uint16_t)(((uint32_t)(qi >> 5) & 0xFFu) | (((uint32_t)(qq >> 5) & 0xFFu) << 8));
+                                uint32_t h[4];
+#pragma unroll
+                                for (int i = 0; i < 4; i++) h[i] = ((uint32_t)(qi[i] >> 5) & 0xFFu) | (((uint32_t)(qq[i] >> 5) & 0xFFu) << 8);
+                                uint16_t* op = reinterpret_cast<uint16_t*>(P.out) + o;
+                                if (P.out_vec) {
+                                    __stcs(reinterpret_cast<uint2*>(op), make_uint2(h[0] | (h[1] << 16), h[2] | (h[3] << 16)));
+                                } else {
+#pragma unroll
+                                    for (int i = 0; i < 4; i++) op[i] = (uint16_t)h[i];
+                                }
                             }
                         }
                     }

@@ -275,3 +275,28 @@ def test_other_filter_families_and_odd_orders(cb, po, torch_cuda, kind, D):
     scale = max(np.sqrt(np.mean(ref.astype(np.float64) ** 2)), 1e-3)     # a high-pass leaves little signal: floor the scale
     err = np.sqrt(np.mean((got - ref) ** 2, axis=0)) / scale
     assert np.all(err <= TOL), (kind, err, fi.form, fi.note)
+
+
+@pytest.mark.parametrize("fmt", ["CF32", "CS16", "CF64", "CS8"])
+def test_output_buffers_without_vector_alignment(cb, po, torch_cuda, fmt):
+    """Phase 3 stores four outputs per lane as one vector when the buffer is 32-byte aligned; a buffer that is not
+    (here: one element into an allocation) must give the same bits through the scalar stores."""
+    torch = torch_cuda
+    n, D = 1 << 18, 8
+    sos = po.butter_lowpass_sos(4, 4e6, 250e3)
+    d_w = _dev(torch, po.gen_words(n).view(np.int32))
+    dt = {"CF32": torch.float32, "CS16": torch.int16, "CF64": torch.float64, "CS8": torch.int8}[fmt]
+    parity = cb.PARITY_F32 if fmt in ("CF32", "CF64") else cb.PARITY_Q16
+    big = torch.zeros((n // D + 1, 2), dtype=dt, device="cuda:0")
+    aligned, shifted = big[: n // D], big[1:]
+    results = []
+    for out in (aligned, shifted):
+        big.zero_()
+        torch.cuda.synchronize()
+        with cb.Context(sos=sos, decimation=D, parity=parity, out_format=getattr(cb, "FMT_" + fmt)) as ctx:
+            ctx.filter_submit(cb.IN_WORDS, d_w, n, out)
+            ret, res = ctx.wait()
+            assert ret == n and res.n_filtered == n // D
+        results.append(out.clone())
+    assert torch.equal(results[0], results[1])
+    assert float(results[0].double().abs().max()) > 0
