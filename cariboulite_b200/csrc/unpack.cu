@@ -12,9 +12,11 @@
 namespace cbl {
 
 // ------------------------------------------------------------------ alignment search (A2)
-// One CTA per chunk.  Candidate 0 is tested first (the aligned common case); otherwise the CTA
-// sweeps the chunk 1024 candidates at a time and stops at the first hit.
-__global__ void __launch_bounds__(256) find_offsets_kernel(OffsetsParams p)
+// One small CTA per chunk (thousands of chunks per submit, and the aligned common case is four loads by one
+// thread: many CTAs per SM keep that latency-bound pass short).  Candidate 0 is tested first; otherwise the CTA
+// sweeps the chunk 4 * blockDim candidates at a time and stops at the first hit.
+constexpr int kFindThreads = 64;
+__global__ void __launch_bounds__(kFindThreads) find_offsets_kernel(OffsetsParams p)
 {
     __shared__ int s_found;
     const uint32_t c = blockIdx.x;
@@ -36,7 +38,7 @@ __global__ void __launch_bounds__(256) find_offsets_kernel(OffsetsParams p)
         result = s_found;
         if (result != 0) {
             const uint32_t ncand = len - 16;        // candidates offs in [0, len-16), caribou_smi.c:248
-            for (uint32_t base = 0; base < ncand; base += 1024) {
+            for (uint32_t base = 0; base < ncand; base += 4 * kFindThreads) {
                 // this thread: candidates base + 4*tid + {0,1,2,3}; they share aligned words w[0..4]
                 const uint32_t o0 = base + 4 * threadIdx.x;
                 if (o0 < ncand) {
@@ -76,7 +78,7 @@ __global__ void __launch_bounds__(256) find_offsets_kernel(OffsetsParams p)
 void launch_find_offsets(const OffsetsParams& p, cudaStream_t st)
 {
     if (p.n_chunks == 0 || p.n_streams == 0) return;
-    find_offsets_kernel<<<dim3(p.n_chunks, p.n_streams), 256, 0, st>>>(p);
+    find_offsets_kernel<<<dim3(p.n_chunks, p.n_streams), kFindThreads, 0, st>>>(p);
 }
 
 // ------------------------------------------------------------------ decode helpers (A3)
