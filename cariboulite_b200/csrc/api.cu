@@ -319,7 +319,7 @@ static int run_unpack(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, s
     const uint64_t n_raw_words = (nbytes + 3) / 4;
     const uint32_t n_tiles = (uint32_t)((n_raw_words + kUnpackTileWords - 1) / kUnpackTileWords);
     if (n_tiles == 0) return CARIBOU_CUDA_OK;
-    const bool want_flags = getenv("CBL_EXP_NOFLAGS") == nullptr;   // counts are always reported (the switch is a timing experiment)
+    const bool want_flags = true;
     if (n_raw_words > (1ull << 31)) { set_error("unpack: at most 2^31 words per stream and submit"); return CARIBOU_CUDA_ERR; }
     // per-tile counts, their scan, work list (+ its length); running totals per stream launch
     if (!c->desc_inv.reserve((size_t)n_tiles * 20 + 16) || !c->desc_syn.reserve(((size_t)ns + 1) * 16)) return CARIBOU_CUDA_ERR;

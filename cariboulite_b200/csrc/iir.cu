@@ -6,7 +6,6 @@ namespace cbl {
 iir_launch_fn iir_launch_k1(int, int, bool, bool); iir_launch_fn iir_launch_k2(int, int, bool, bool);
 iir_launch_fn iir_launch_k3(int, int, bool, bool); iir_launch_fn iir_launch_k4(int, int, bool, bool);
 
-bool iir_has_y32(int K, bool par) { (void)K; return par; }
 
 int launch_iir(int K, int D, int in_kind, bool par, bool y32, const CUtensorMap& tmap, const IirParams& p,
                const IirTables& t, int num_sms, cudaStream_t st)

@@ -146,7 +146,8 @@ constexpr double kBiasWords = 1052672.0;   // 2^20 + 2^12
 constexpr double kBiasCs16  = 2129920.0;   // 2^21 + 2^15
 
 // returns cudaError_t as int; y32 selects the float-staged kernel (iir_has_y32 says whether one exists)
-bool iir_has_y32(int K, bool par);
+// float-staged kernels are built for the parallel realisation only
+inline bool iir_has_y32(int K, bool par) { (void)K; return par; }
 int launch_iir(int K, int D, int in_kind, bool par, bool y32, const CUtensorMap& tmap, const IirParams& p,
                const IirTables& t, int num_sms, cudaStream_t st);
 void launch_iir_tail(const IirTailParams& p, cudaStream_t st);

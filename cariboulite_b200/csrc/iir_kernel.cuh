@@ -226,10 +226,7 @@ struct IirCfg {
     static constexpr int WPC_ = SMEM_WARPS < REG_WARPS ? SMEM_WARPS : REG_WARPS;
     static constexpr int WPC  = WPC_ < CBL_IIR_WPC_CAP ? WPC_ : CBL_IIR_WPC_CAP;     // warps per CTA = per SM
     static_assert(WPC >= 1, "a warp's buffers do not fit shared memory");
-#ifndef CBL_EXP_SMEM_PAD
-#define CBL_EXP_SMEM_PAD 0
-#endif
-    static constexpr int SMEM_BYTES = WPC * WARP_BYTES + WPC * STAGES * 8 + 1024 + ((D == 32) ? CBL_EXP_SMEM_PAD : 0);   // + mbarriers + alignment slack
+    static constexpr int SMEM_BYTES = WPC * WARP_BYTES + WPC * STAGES * 8 + 1024;   // + mbarriers + alignment slack
 };
 
 // One filter step on one rail.  v = (v1,v2) per section.  Returns y/G at this sample if NEED_OUT.
@@ -385,11 +382,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                             const int j = ci * PER + e;              // sample index within the group
                             double xa, xb;
                             if (INJECT) {
-#ifdef CBL_EXP_NOCONV
-                                xa = __longlong_as_double(((long long)inj_xor << 32) | wv[e]); xb = xa;   // timing experiment only
-#else
                                 inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
-#endif
                             } else if (IN == IN_CF32) {
                                 sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
                             } else {
@@ -436,10 +429,8 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
         // L2 round trip hides behind the scan.
         const int comp = lane < 2 * S ? lane : 0;
         unsigned long long pre = kDescEmpty;
-#ifndef CBL_NO_PREFETCH
         if (owe && ptis != 0 && lane < 2 * S)
             pre = ld_desc((P.chained ? P.desc_incl : P.desc_agg) + (size_t)(ptile - 1) * (2 * S) + comp);
-#endif
 
         if (have) {
             // ---- phase 2: warp scan of run end states: E_t = sum_{j<=t} M^(t-j) f_j
@@ -450,11 +441,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             }
 #pragma unroll
             for (int j = 0; j < 5; j++) {
-#ifdef CBL_NO_ROUNDS
-                {
-#else
                 if (j < P.scan_rounds) {      // later rounds multiply by a matrix that is numerically zero
-#endif
                     const int d = 1 << j;
                     double g[2][S];
 #pragma unroll

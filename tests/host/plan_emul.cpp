@@ -34,23 +34,23 @@ static void step(const FilterPlan& P, double* v, double x, double* out)
 
 extern "C" {
 
-// info[0]=par, [1]=window, [2]=chained, [3]=decay, [4]=par_err, [5]=hn1
-int emul_plan_info(int K, const double* sos, int D, int force_cascade, double* info)
+// info[0]=par, [1]=window, [2]=chained, [3]=decay, [4]=par_err, [5]=hn1, [6]=run length, [7]=kept per run, [8]=y32
+int emul_plan_info(int K, const double* sos, int D, int force_cascade, int want_y32, double* info)
 {
     FilterPlan P; const char* msg = "";
-    if (!make_filter_plan(K, (const double(*)[6])sos, D, force_cascade != 0, false, &P, &msg)) return -1;
+    if (!make_filter_plan(K, (const double(*)[6])sos, D, force_cascade != 0, want_y32 != 0, &P, &msg)) return -1;
     info[0] = P.par; info[1] = P.window; info[2] = P.chained; info[3] = (double)P.decay_samples;
-    info[4] = P.par_err; info[5] = P.hn1;
+    info[4] = P.par_err; info[5] = P.hn1; info[6] = P.LT; info[7] = P.NK; info[8] = P.y32;
     return 0;
 }
 
 // One rail: x[n] integer-valued samples, bias as the kernel would add it (0 = converted input).
 // out[n/D] = gain * y at kept samples; state_ref_in/out in reference (DF-II) coordinates.
-int emul_run(int K, const double* sos, int D, int force_cascade, double bias, double out_scale,
+int emul_run(int K, const double* sos, int D, int force_cascade, int want_y32, double bias, double out_scale,
              const double* x, size_t n, const double* state_ref_in, double* out, double* state_ref_out)
 {
     FilterPlan P; const char* msg = "";
-    if (!make_filter_plan(K, (const double(*)[6])sos, D, force_cascade != 0, false, &P, &msg)) return -1;
+    if (!make_filter_plan(K, (const double(*)[6])sos, D, force_cascade != 0, want_y32 != 0, &P, &msg)) return -1;
     if (!P.par) bias = 0;
     const int S = P.S, LT = P.LT, NK = P.NK;
     if (n % LT) return -2;
@@ -86,21 +86,25 @@ int emul_run(int K, const double* sos, int D, int force_cascade, double bias, do
     return P.par ? 1 : 0;
 }
 
-// max |Mp[j] - M^(2^j)| relative, and sparsity check of the pattern the kernel assumes
-double emul_check_powers(int K, const double* sos, int D, int force_cascade)
+// max |Mp[j] - M^(2^j)| relative to the largest entry of that power, and sparsity check of the pattern the kernel assumes
+double emul_check_powers(int K, const double* sos, int D, int force_cascade, int want_y32)
 {
     FilterPlan P; const char* msg = "";
-    if (!make_filter_plan(K, (const double(*)[6])sos, D, force_cascade != 0, false, &P, &msg)) return -1;
+    if (!make_filter_plan(K, (const double(*)[6])sos, D, force_cascade != 0, want_y32 != 0, &P, &msg)) return -1;
     const int S = P.S;
     double worst = 0;
-    for (int j = 0; j < 5; j++)
+    for (int j = 0; j < 5; j++) {
+        double diff = 0, mx = 0;
         for (int i = 0; i < S; i++)
             for (int c = 0; c < S; c++) {
                 const double a = P.tables.Mp[j][i * S + c], b = P.plane[(size_t)(i * S + c) * 33 + (1 << j)];
-                worst = fmax(worst, fabs(a - b));
+                diff = fmax(diff, fabs(a - b));
+                mx = fmax(mx, fmax(fabs(a), fabs(b)));
                 const bool in_pattern = P.par ? (c / 2 == i / 2) : (c < 2 * (i / 2 + 1));
                 if (!in_pattern && (a != 0.0 || b != 0.0)) return 1e300;
             }
+        if (mx > 0) worst = fmax(worst, diff / mx);
+    }
     return worst;
 }
 }
