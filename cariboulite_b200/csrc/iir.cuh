@@ -130,6 +130,28 @@ __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
     int lt = (nk * D / 32) * 32;
     return lt < 32 ? 32 : lt;
 }
+// Full-rate and lightly decimated streams of the parallel realisation take the rerun kernel (iir_rerun.cuh): the
+// input tile stays in shared memory and is filtered a second time from the true entry state, so the run length is
+// set by the input (two tiles of LT * 128 bytes per warp), not by a stage of kept outputs.
+#ifndef CBL_RR_MAXD
+#define CBL_RR_MAXD 1            // largest decimation that takes the rerun kernel (0: never; at most 2)
+#endif
+#ifndef CBL_RR_LT
+#define CBL_RR_LT 64
+#endif
+#ifndef CBL_RR_WARPS
+#define CBL_RR_WARPS 12
+#endif
+#ifndef CBL_RR_WARPS3
+#define CBL_RR_WARPS3 12
+#endif
+#ifndef CBL_RR_NBUF
+#define CBL_RR_NBUF 2
+#endif
+constexpr int kRerunMaxD = CBL_RR_MAXD;
+constexpr int kRerunLT   = CBL_RR_LT;
+static_assert(kRerunMaxD <= 2, "rerun kernels exist for D = 1 and D = 2");
+inline bool iir_is_rerun(int D, bool par) { return par && D <= kRerunMaxD; }
 #ifndef CBL_IIR_STAGES
 #define CBL_IIR_STAGES 2
 #endif

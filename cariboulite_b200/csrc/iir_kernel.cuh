@@ -751,18 +751,26 @@ int launch_iir_t(const CUtensorMap& tmap, const IirParams& p, const IirTables& t
     return (int)cudaGetLastError();
 }
 
+typedef int (*iir_launch_fn)(const CUtensorMap&, const IirParams&, const IirTables&, int, cudaStream_t);
+
+// the staged kernel for (K, D, ...), unless that combination belongs to the rerun kernel (iir_rerun.cuh)
+template <int K, int D, int IN, bool PAR, bool Y32>
+iir_launch_fn staged_launch()
+{
+    if constexpr (PAR && D <= kRerunMaxD) return nullptr;
+    else return &launch_iir_t<K, D, IN, PAR, Y32>;
+}
+
 #define CBL_IIR_DISPATCH_D(KK, IN_, PAR_, Y32_)                       \
     switch (D) {                                                     \
-        case 1:  return &launch_iir_t<KK, 1, IN_, PAR_, Y32_>;        \
-        case 2:  return &launch_iir_t<KK, 2, IN_, PAR_, Y32_>;        \
-        case 4:  return &launch_iir_t<KK, 4, IN_, PAR_, Y32_>;        \
-        case 8:  return &launch_iir_t<KK, 8, IN_, PAR_, Y32_>;        \
-        case 16: return &launch_iir_t<KK, 16, IN_, PAR_, Y32_>;       \
-        case 32: return &launch_iir_t<KK, 32, IN_, PAR_, Y32_>;       \
+        case 1:  return staged_launch<KK, 1, IN_, PAR_, Y32_>();      \
+        case 2:  return staged_launch<KK, 2, IN_, PAR_, Y32_>();      \
+        case 4:  return staged_launch<KK, 4, IN_, PAR_, Y32_>();      \
+        case 8:  return staged_launch<KK, 8, IN_, PAR_, Y32_>();      \
+        case 16: return staged_launch<KK, 16, IN_, PAR_, Y32_>();     \
+        case 32: return staged_launch<KK, 32, IN_, PAR_, Y32_>();     \
         default: return nullptr;                                     \
     }
-
-typedef int (*iir_launch_fn)(const CUtensorMap&, const IirParams&, const IirTables&, int, cudaStream_t);
 
 // The float-staged (Y32) kernels exist for the preferred realisation only: the parallel form, also for a single
 // section (x + alpha v1 + beta v2 is what lets the integer inputs enter by mantissa injection).

@@ -1,0 +1,456 @@
+// Kernel (b), full-rate and lightly decimated form (D <= kRerunMaxD, parallel realisation): the "rerun" kernel.
+//
+// The staged kernel (iir_kernel.cuh) keeps the zero-state outputs of a run in shared memory and corrects each
+// kept one with R[m] . s0 later.  That pays when few outputs are kept; at D = 1 every sample is kept, the stage
+// limits a run to 32 samples (five times the per-tile work of the D = 8 kernel per sample) and every output costs
+// a shared-memory round trip plus 2S correction FMAs.  Here the INPUT tile stays in shared memory instead (4 bytes
+// per sample, not 8-16): phase 1 filters the run from the steady state for its end state only (2K FMAs per rail
+// and sample, no outputs), phases 2 and the look-back are those of the staged kernel, and phase 3 filters the
+// same run again from its true entry state s0 - now in exactly the reference's sample order - producing the
+// outputs straight into 32-byte stores.  FP64 work per complex sample at D = 1: 4K + 8K + 2 instead of
+// 8K + 4K + 2 plus the per-tile work of 32-sample runs; shared memory per warp: two input tiles.
+//
+//   iteration i of a warp:   phase 1-2 of tile i (ring slot i % NBUF)
+//                            look-back + phase 3 of tile i-1 (the slot before)     <- one tile late, as before
+//                            that slot is free: the TMA boxes of tile i + NBUF - 1 are requested into it
+// With two slots the request is consumed right away by the next iteration's phase 1 and the other warps of the
+// SMSP cover its latency; with three it has a whole iteration of slack at the price of fewer warps per SM.
+#pragma once
+#include "iir_kernel.cuh"
+
+namespace cbl {
+
+template <int K, int D, int IN>
+struct RerunCfg {
+    static constexpr int S     = 2 * K;
+    static constexpr int LT    = kRerunLT;
+    static constexpr int NK    = LT / D;
+    static constexpr int SPS   = (IN == IN_CF32) ? 16 : 32;   // samples per 128-byte row step
+    static constexpr int NSTEP = LT / SPS;                    // 4 KiB boxes per tile
+    static constexpr int NBUF  = CBL_RR_NBUF;                 // input tiles a warp holds: 2, or 3 to request a tile a whole iteration ahead
+    static constexpr int HALF_BYTES    = NSTEP * 4096;        // one tile
+    static constexpr int RING_BYTES    = NBUF * HALF_BYTES;
+    static constexpr int SCRATCH_BYTES = 2 * S * 8 * 2;
+    static constexpr int WARP_BYTES = RING_BYTES + SCRATCH_BYTES;
+    static constexpr int SMEM_WARPS = (232448 - 1024) / (WARP_BYTES + NBUF * NSTEP * 8);
+    // registers (cuobjdump -res-usage): ~144 (K <= 2), ~180 (K = 3), ~235 (K = 4); 12 warps allow 168, 8 allow 255
+    static constexpr int REG_WARPS  = (K <= 2) ? CBL_RR_WARPS : (K == 3 ? CBL_RR_WARPS3 : 8);
+    static constexpr int WPC = SMEM_WARPS < REG_WARPS ? SMEM_WARPS : REG_WARPS;
+    static_assert(WPC >= 1, "a warp's buffers do not fit shared memory");
+    static_assert(LT % 32 == 0 && (D == 1 || D == 2), "phase 3 works in groups of 8 or 16 samples: whole chunks of 4 kept outputs");
+    static_assert(NBUF == 2 || NBUF == 3, "two or three input tiles per warp");
+    static constexpr int SMEM_BYTES = WPC * WARP_BYTES + WPC * NBUF * NSTEP * 8 + 1024;
+};
+
+// four consecutive outputs of one lane, already scaled (y = gain * y/G + out_bias), in the stream's output format
+__device__ __forceinline__ void store_out4(const IirParams& P, uint64_t o, const double (&yi)[4], const double (&yq)[4])
+{
+    if (P.out_mode == OUT_F32) {
+        float2* op = reinterpret_cast<float2*>(P.out) + o;
+        if (P.out_vec) {
+            stg_cf32x4(op, make_float2((float)yi[0], (float)yq[0]), make_float2((float)yi[1], (float)yq[1]),
+                       make_float2((float)yi[2], (float)yq[2]), make_float2((float)yi[3], (float)yq[3]));
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; i++) __stcs(op + i, make_float2((float)yi[i], (float)yq[i]));
+        }
+    } else if (P.out_mode == OUT_F64) {
+        double2* op = reinterpret_cast<double2*>(P.out) + o;
+        if (P.out_vec) {
+            stg_f64x4(&op[0].x, yi[0], yq[0], yi[1], yq[1]);
+            stg_f64x4(&op[2].x, yi[2], yq[2], yi[3], yq[3]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; i++) __stcs(op + i, make_double2(yi[i], yq[i]));
+        }
+    } else {
+        // (int16_t)(float)y, CaribouliteStream.cpp:295-296: round to float, truncate toward zero
+        int qi[4], qq[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            qi[i] = (int)(int16_t)__float2int_rz((float)yi[i]);
+            qq[i] = (int)(int16_t)__float2int_rz((float)yq[i]);
+        }
+        if (P.out_mode == OUT_Q16_CS16) {
+            uint32_t w[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) w[i] = ((uint32_t)qi[i] & 0xFFFFu) | ((uint32_t)qq[i] << 16);
+            uint32_t* op = reinterpret_cast<uint32_t*>(P.out) + o;
+            if (P.out_vec) {
+                __stcs(reinterpret_cast<uint4*>(op), make_uint4(w[0], w[1], w[2], w[3]));
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; i++) op[i] = w[i];
+            }
+        } else if (P.out_mode == OUT_Q16_CF32) {
+            float2* op = reinterpret_cast<float2*>(P.out) + o;
+            const float k = 1.0f / 4096.0f;
+            if (P.out_vec) {
+                stg_cf32x4(op, make_float2((float)qi[0] * k, (float)qq[0] * k), make_float2((float)qi[1] * k, (float)qq[1] * k),
+                           make_float2((float)qi[2] * k, (float)qq[2] * k), make_float2((float)qi[3] * k, (float)qq[3] * k));
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; i++) __stcs(op + i, make_float2((float)qi[i] * k, (float)qq[i] * k));
+            }
+        } else if (P.out_mode == OUT_Q16_CF64) {
+            double2* op = reinterpret_cast<double2*>(P.out) + o;
+            const double k = 1.0 / 4096.0;
+            if (P.out_vec) {
+                stg_f64x4(&op[0].x, (double)qi[0] * k, (double)qq[0] * k, (double)qi[1] * k, (double)qq[1] * k);
+                stg_f64x4(&op[2].x, (double)qi[2] * k, (double)qq[2] * k, (double)qi[3] * k, (double)qq[3] * k);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; i++) __stcs(op + i, make_double2((double)qi[i] * k, (double)qq[i] * k));
+            }
+        } else {   // OUT_Q16_CS8, CaribouliteStream.cpp:362-363
+            uint32_t h[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) h[i] = ((uint32_t)(qi[i] >> 5) & 0xFFu) | (((uint32_t)(qq[i] >> 5) & 0xFFu) << 8);
+            uint16_t* op = reinterpret_cast<uint16_t*>(P.out) + o;
+            if (P.out_vec) {
+                __stcs(reinterpret_cast<uint2*>(op), make_uint2(h[0] | (h[1] << 16), h[2] | (h[3] << 16)));
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; i++) op[i] = (uint16_t)h[i];
+            }
+        }
+    }
+}
+
+template <int K, int D, int IN>
+__global__ void __launch_bounds__((RerunCfg<K, D, IN>::WPC) * 32, 1)
+iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ IirParams P,
+                 const __grid_constant__ IirTables T)
+{
+    using C = RerunCfg<K, D, IN>;
+    constexpr int S = C::S;
+    constexpr bool PAR = true;
+    constexpr bool INJECT = IN != IN_CF32;
+    extern __shared__ uint8_t smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t ring_u32 = base + warp * C::RING_BYTES;
+    const uint32_t scratch = base + C::WPC * C::RING_BYTES + warp * C::SCRATCH_BYTES;
+    const uint32_t bar_u32 = base + C::WPC * C::WARP_BYTES + warp * (C::NBUF * C::NSTEP) * 8;
+
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < C::NBUF * C::NSTEP; s++) mbar_init(bar_u32 + 8 * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncwarp();
+
+    if (P.gate != nullptr && __ldg(P.gate) != 0) return;
+
+    const uint32_t tps = P.tiles_per_stream;
+
+    const uint32_t inj_xor = P.inj_xor, inj_mul = P.inj_mul;
+
+    // all boxes of tile (stream, tis) into ring slot `half` (lane 0 only)
+    auto issue_tile = [&](uint32_t stream, uint32_t tis, uint32_t half) {
+#pragma unroll
+        for (int s = 0; s < C::NSTEP; s++) {
+            const uint32_t bar = bar_u32 + 8 * (half * C::NSTEP + s);
+            mbar_expect_tx(bar, 4096);
+            tma_load_3d(ring_u32 + half * C::HALF_BYTES + s * 4096, &tmap, s * 32, (int)tis * 32, (int)stream, bar);
+        }
+    };
+
+    // 16-byte piece c of this lane's row in box `box_u32`, and its samples as (rail A, rail B) doubles
+    auto row_piece = [&](uint32_t box_u32, int c) {
+        return lds128((box_u32 + lane * 128 + ((lane & 7) << 4)) ^ (uint32_t)(c << 4));
+    };
+
+    uint32_t slot = 0, par = 0;    // ring slot of the tile in phases 1-2 and the parity its barriers complete with
+    uint32_t tile = 0xFFFFFFFFu, next = 0xFFFFFFFFu;
+    uint32_t* const ticket = P.ticket + __ldg(P.ticket + 32 + lane);      // words 32..63 of the ticket block stay zero
+    if (lane == 0) {
+        tile = take_ticket(ticket);
+        next = take_ticket(ticket);
+    }
+    tile = __shfl_sync(0xffffffffu, tile, 0);
+    uint32_t stream = tile / tps, tis = tile - stream * tps;
+    if (lane == 0 && tile < P.total_tiles) issue_tile(stream, tis, 0u);
+    if (C::NBUF == 3 && lane == 0 && next < P.total_tiles) issue_tile(next / tps, next % tps, 1u);
+
+    bool owe = false;
+    uint32_t ptile = 0, pstream = 0, ptis = 0;
+    double pf[2][S];
+#pragma unroll
+    for (int r = 0; r < 2; r++)
+#pragma unroll
+        for (int c = 0; c < S; c++) pf[r][c] = 0.0;
+
+    for (;;) {
+        const bool have = tile < P.total_tiles;
+        const uint32_t half = slot;
+        const uint32_t prev = slot == 0 ? (uint32_t)C::NBUF - 1u : slot - 1u;     // the owed tile's slot
+        uint32_t next2 = 0xFFFFFFFFu, nstream = 0, ntis = 0;
+        double f[2][S];
+        if (have) {
+            if (lane == 0) next2 = take_ticket(ticket);
+            nstream = next / tps;
+            ntis = next - nstream * tps;
+
+            // ---- phase 1: the run from the steady state, end state only
+            double va[K][2], vb[K][2];
+#pragma unroll
+            for (int k = 0; k < K; k++) {
+                va[k][0] = vb[k][0] = T.sbias[2 * k];
+                va[k][1] = vb[k][1] = T.sbias[2 * k + 1];
+            }
+#pragma unroll 1
+            for (int step = 0; step < C::NSTEP; step++) {
+                mbar_wait(bar_u32 + 8 * (half * C::NSTEP + step), par);
+                const uint32_t box = ring_u32 + half * C::HALF_BYTES + step * 4096;
+                uint4 q[8];
+#pragma unroll
+                for (int ci = 0; ci < 8; ci++) q[ci] = row_piece(box, ci);
+#pragma unroll
+                for (int ci = 0; ci < 8; ci++) {
+                    const uint32_t wv[4] = {q[ci].x, q[ci].y, q[ci].z, q[ci].w};
+#pragma unroll
+                    for (int e = 0; e < (IN == IN_CF32 ? 2 : 4); e++) {
+                        double xa, xb;
+                        if (INJECT) inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
+                        else sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
+                        filter_step<K, PAR, false>(T, va, xa);
+                        filter_step<K, PAR, false>(T, vb, xb);
+                    }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < K; k++) {
+                f[0][2 * k] = va[k][0] - T.sbias[2 * k]; f[0][2 * k + 1] = va[k][1] - T.sbias[2 * k + 1];
+                f[1][2 * k] = vb[k][0] - T.sbias[2 * k]; f[1][2 * k + 1] = vb[k][1] - T.sbias[2 * k + 1];
+            }
+        }
+
+        // the owed tile's first look-back descriptor: its L2 round trip hides behind the scan
+        const int comp = lane < 2 * S ? lane : 0;
+        unsigned long long pre = kDescEmpty;
+        if (owe && ptis != 0 && lane < 2 * S)
+            pre = ld_desc((P.chained ? P.desc_incl : P.desc_agg) + (size_t)(ptile - 1) * (2 * S) + comp);
+
+        if (have) {
+            // ---- phase 2: warp scan of run end states: E_t = sum_{j<=t} M^(t-j) f_j
+#pragma unroll
+            for (int j = 0; j < 5; j++) {
+                if (j < P.scan_rounds) {
+                    const int d = 1 << j;
+                    double g[2][S];
+#pragma unroll
+                    for (int r = 0; r < 2; r++)
+#pragma unroll
+                        for (int c = 0; c < S; c++) g[r][c] = shfl_up_f64(f[r][c], d);
+                    if (lane >= d) {
+#pragma unroll
+                        for (int r = 0; r < 2; r++)
+#pragma unroll
+                            for (int row = 0; row < S; row++) {
+                                double acc = f[r][row];
+#pragma unroll
+                                for (int col = col_lo<PAR>(row); col < col_hi(row); col++) acc = fma(T.Mp[j][row * S + col], g[r][col], acc);
+                                f[r][row] = acc;
+                            }
+                    }
+                }
+            }
+            if (lane == 31 && !P.chained) {
+                double* agg = P.desc_agg + (size_t)tile * (2 * S);
+#pragma unroll
+                for (int r = 0; r < 2; r++)
+#pragma unroll
+                    for (int c = 0; c < S; c++) st_desc(agg + r * S + c, f[r][c]);
+            }
+        }
+
+        // ---- the owed tile: decoupled look-back, then phase 3 out of its ring slot
+        if (owe) {
+            const int crail = comp / S, crow = comp % S;
+            if (lane < 2 * S) {
+                double sin_c = 0.0;
+                if (ptis == 0) {
+                    sin_c = P.state_in[(size_t)pstream * (2 * S) + crail * S + crow];
+                } else {
+                    const double* first = (P.chained ? P.desc_incl : P.desc_agg) + (size_t)(ptile - 1) * (2 * S) + comp;
+                    while (pre == kDescEmpty) { __nanosleep(32); pre = ld_desc(first); }
+                    sin_c = __longlong_as_double((long long)pre);
+                    if (!P.chained) {
+                        const int depth = (int)ptis < P.window ? (int)ptis : P.window;
+                        for (int j = 2; j <= depth; j++) {
+                            const double* a = P.desc_agg + (size_t)(ptile - j) * (2 * S) + crail * S;
+                            const double* mp = P.mtile_pow + (size_t)(j - 1) * (S * S) + crow * S;
+                            unsigned long long dv[S];
+#pragma unroll
+                            for (int col = 0; col < S; col++) dv[col] = ld_desc(a + col);
+#pragma unroll
+                            for (int col = 0; col < S; col++) {
+                                while (dv[col] == kDescEmpty) { __nanosleep(32); dv[col] = ld_desc(a + col); }
+                                sin_c = fma(__ldg(mp + col), __longlong_as_double((long long)dv[col]), sin_c);
+                            }
+                        }
+                        if ((int)ptis <= P.window) {     // the window reaches the start of the stream
+                            const double* a = P.state_in + (size_t)pstream * (2 * S) + crail * S;
+                            const double* mp = P.mtile_pow + (size_t)ptis * (S * S) + crow * S;
+#pragma unroll
+                            for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), __ldg(a + col), sin_c);
+                        }
+                    }
+                }
+                sts64(scratch + lane * 8, sin_c);
+            }
+            __syncwarp();
+            double sin[2][S];
+#pragma unroll
+            for (int r = 0; r < 2; r++)
+#pragma unroll
+                for (int c = 0; c < S; c++) sin[r][c] = lds64(scratch + (r * S + c) * 8);
+
+            // true state entering this lane's run: s0 = M^lane S_in + E_{lane-1}
+            double s0[2][S];
+#pragma unroll
+            for (int r = 0; r < 2; r++)
+#pragma unroll
+                for (int c = 0; c < S; c++) {
+                    const double e = shfl_up_f64(pf[r][c], 1);
+                    s0[r][c] = lane == 0 ? 0.0 : e;
+                }
+#pragma unroll
+            for (int row = 0; row < S; row++)
+#pragma unroll
+                for (int col = col_lo<PAR>(row); col < col_hi(row); col++) {
+                    const double m = __ldg(P.plane + (row * S + col) * 33 + lane);      // (M^lane)[row][col]
+                    s0[0][row] = fma(m, sin[0][col], s0[0][row]);
+                    s0[1][row] = fma(m, sin[1][col], s0[1][row]);
+                }
+
+            // true end state of the tile (chained mode) / of the stream (last tile)
+            const bool last_tile = (ptis == tps - 1);
+            if (P.chained || (last_tile && P.write_state)) {
+                const int lastl = last_tile && P.write_state ? (int)P.last_tile_runs - 1 : 31;
+                if (lane == lastl) {
+                    double* incl = P.desc_incl + (size_t)ptile * (2 * S);
+#pragma unroll
+                    for (int row = 0; row < S; row++) {
+                        double ea = pf[0][row], eb = pf[1][row];
+#pragma unroll
+                        for (int col = col_lo<PAR>(row); col < col_hi(row); col++) {
+                            const double m = __ldg(P.plane + (row * S + col) * 33 + lastl + 1);
+                            ea = fma(m, sin[0][col], ea);
+                            eb = fma(m, sin[1][col], eb);
+                        }
+                        if (P.chained) { st_desc(incl + row, ea); st_desc(incl + S + row, eb); }
+                        if (last_tile && P.write_state) {
+                            P.state_out[(size_t)pstream * (2 * S) + row] = ea;
+                            P.state_out[(size_t)pstream * (2 * S) + S + row] = eb;
+                        }
+                    }
+                }
+            }
+
+            // ---- phase 3: the run again, from its true entry state (offset by the steady state the injected
+            // inputs imply), outputs at the kept positions
+            const uint32_t run = ptis * 32u + lane;
+            if (run < P.n_runs) {
+                double va[K][2], vb[K][2];
+#pragma unroll
+                for (int k = 0; k < K; k++) {
+                    va[k][0] = T.sbias[2 * k] + s0[0][2 * k];     va[k][1] = T.sbias[2 * k + 1] + s0[0][2 * k + 1];
+                    vb[k][0] = T.sbias[2 * k] + s0[1][2 * k];     vb[k][1] = T.sbias[2 * k + 1] + s0[1][2 * k + 1];
+                }
+                uint64_t o = (uint64_t)pstream * P.out_stride + (uint64_t)run * C::NK;
+                const uint32_t ohalf = prev;
+                constexpr int PER = (IN == IN_CF32) ? 2 : 4;      // samples per 16 bytes
+#pragma unroll 1
+                for (int step = 0; step < C::NSTEP; step++) {
+                    const uint32_t box = ring_u32 + ohalf * C::HALF_BYTES + step * 4096;
+                    // the row in two groups of four pieces: the group body is unrolled (kept positions are static)
+#pragma unroll 1
+                    for (int co = 0; co < 2; co++) {
+                        uint4 q[4];
+#pragma unroll
+                        for (int ci = 0; ci < 4; ci++) q[ci] = row_piece(box, co * 4 + ci);
+                        double yi[4], yq[4];
+#pragma unroll
+                        for (int ci = 0; ci < 4; ci++) {
+                            const uint32_t wv[4] = {q[ci].x, q[ci].y, q[ci].z, q[ci].w};
+#pragma unroll
+                            for (int e = 0; e < PER; e++) {
+                                const int j = ci * PER + e;          // sample within the group (group starts on a multiple of D)
+                                double xa, xb;
+                                if (INJECT) inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
+                                else sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
+                                if (j % D == 0) {
+                                    const int m = (j / D) & 3;
+                                    yi[m] = fma(filter_step<K, PAR, true>(T, va, xa), T.gain, T.out_bias);
+                                    yq[m] = fma(filter_step<K, PAR, true>(T, vb, xb), T.gain, T.out_bias);
+                                    if (m == 3) { store_out4(P, o, yi, yq); o += 4; }
+                                } else {
+                                    filter_step<K, PAR, false>(T, va, xa);
+                                    filter_step<K, PAR, false>(T, vb, xb);
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+            __syncwarp();   // the owed tile's ring slot and the scratch are free again
+        }
+        if (!have) break;
+        // the slot the owed tile just left takes the tile NBUF - 1 tickets ahead
+        if (C::NBUF == 2) {
+            if (lane == 0 && next < P.total_tiles) issue_tile(nstream, ntis, prev);
+        } else {
+            if (lane == 0 && next2 < P.total_tiles) issue_tile(next2 / tps, next2 % tps, prev);
+        }
+        owe = true;
+        ptile = tile; pstream = stream; ptis = tis;
+#pragma unroll
+        for (int r = 0; r < 2; r++)
+#pragma unroll
+            for (int c = 0; c < S; c++) pf[r][c] = f[r][c];
+        if (++slot == (uint32_t)C::NBUF) { slot = 0; par ^= 1u; }
+        tile = __shfl_sync(0xffffffffu, next, 0);
+        stream = __shfl_sync(0xffffffffu, nstream, 0);
+        tis = __shfl_sync(0xffffffffu, ntis, 0);
+        next = next2;
+    }
+}
+
+template <int K, int D, int IN>
+int launch_rerun_t(const CUtensorMap& tmap, const IirParams& p, const IirTables& t, int num_sms, cudaStream_t st)
+{
+    using C = RerunCfg<K, D, IN>;
+    auto kern = iir_rerun_kernel<K, D, IN>;
+    static bool ready = false;
+    if (!ready) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+        if (e != cudaSuccess) return (int)e;
+        ready = true;
+    }
+    const uint64_t want = ((uint64_t)p.total_tiles + C::WPC - 1) / C::WPC;
+    const int grid = (int)(want < (uint64_t)num_sms ? want : (uint64_t)num_sms);
+    kern<<<grid, C::WPC * 32, C::SMEM_BYTES, st>>>(tmap, p, t);
+    return (int)cudaGetLastError();
+}
+
+template <int KK>
+iir_launch_fn rerun_pick_launch(int D, int in_kind)
+{
+#define CBL_RR_CASE(DD)                                                                  \
+    if (D == DD && DD <= kRerunMaxD) {                                                   \
+        constexpr int DE = DD <= kRerunMaxD ? DD : 1;                                    \
+        if (in_kind == IN_WORDS) return &launch_rerun_t<KK, DE, IN_WORDS>;               \
+        if (in_kind == IN_WORDS_HIF) return &launch_rerun_t<KK, DE, IN_WORDS_HIF>;       \
+        if (in_kind == IN_CS16) return &launch_rerun_t<KK, DE, IN_CS16>;                 \
+        if (in_kind == IN_CF32) return &launch_rerun_t<KK, DE, IN_CF32>;                 \
+    }
+    CBL_RR_CASE(1)
+    CBL_RR_CASE(2)
+#undef CBL_RR_CASE
+    return nullptr;
+}
+
+}  // namespace cbl

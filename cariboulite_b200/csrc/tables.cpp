@@ -414,8 +414,10 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, 
     }
     if (!P->par) { for (int i = 0; i < kMaxS; i++) P->sstar[i] = 0; P->hn1 = 1; }
     // the float-staged kernels exist for the preferred realisation only; they afford longer runs
-    P->y32 = want_y32 && iir_has_y32(K, P->par);
-    P->LT = iir_run_len(K, D, P->y32);
+    // (the rerun kernel of full-rate streams stages nothing: its run length comes from the input tile)
+    P->rerun = iir_is_rerun(D, P->par);
+    P->y32 = !P->rerun && want_y32 && iir_has_y32(K, P->par);
+    P->LT = P->rerun ? kRerunLT : iir_run_len(K, D, P->y32);
     P->NK = P->LT / D;
     for (int k = 0; k < K; k++) {
         P->tables.a1[k] = (double)F.a1[k]; P->tables.a2[k] = (double)F.a2[k];
@@ -456,7 +458,7 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, 
         ld r[kMaxS];
         for (int i = 0; i < S; i++) r[i] = Cu[i];
         for (int n = 0; n < P->LT; n++) {
-            if (n % D == 0) for (int i = 0; i < S; i++) P->tables.R[n / D][i] = (double)r[i];
+            if (n % D == 0 && n / D < kMaxNK) for (int i = 0; i < S; i++) P->tables.R[n / D][i] = (double)r[i];
             ld t[kMaxS];
             for (int j = 0; j < S; j++) {
                 ld acc = 0;

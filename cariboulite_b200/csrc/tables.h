@@ -13,6 +13,7 @@ int butter_lowpass_sos(int order, double fs, double fc, double* sos);
 // Everything the kernels need for one (cascade, decimation) pair.
 struct FilterPlan {
     int K = 0, D = 1, LT = 32, NK = 32, S = 0;
+    bool rerun = false;           // full-rate form: the rerun kernel (iir_rerun.cuh), no output stage, no R table
     bool y32 = false;             // float-staged kernels (plain CF32 output, preferred realisation)
     bool par = false;             // kernels run the parallel (partial-fraction) realisation, else the cascade
     const char* form_note = "";   // why the cascade was chosen, when it was

@@ -34,13 +34,13 @@ static void step(const FilterPlan& P, double* v, double x, double* out)
 
 extern "C" {
 
-// info[0]=par, [1]=window, [2]=chained, [3]=decay, [4]=par_err, [5]=hn1, [6]=run length, [7]=kept per run, [8]=y32
+// info[0]=par, [1]=window, [2]=chained, [3]=decay, [4]=par_err, [5]=hn1, [6]=run length, [7]=kept per run, [8]=y32, [9]=rerun
 int emul_plan_info(int K, const double* sos, int D, int force_cascade, int want_y32, double* info)
 {
     FilterPlan P; const char* msg = "";
     if (!make_filter_plan(K, (const double(*)[6])sos, D, force_cascade != 0, want_y32 != 0, &P, &msg)) return -1;
     info[0] = P.par; info[1] = P.window; info[2] = P.chained; info[3] = (double)P.decay_samples;
-    info[4] = P.par_err; info[5] = P.hn1; info[6] = P.LT; info[7] = P.NK; info[8] = P.y32;
+    info[4] = P.par_err; info[5] = P.hn1; info[6] = P.LT; info[7] = P.NK; info[8] = P.y32; info[9] = P.rerun;
     return 0;
 }
 
@@ -68,6 +68,16 @@ int emul_run(int K, const double* sos, int D, int force_cascade, int want_y32, d
             step(P, v, x[r * LT + t] + bias, &y);
             if (t % D == 0) ys[t / D] = y;
         }
+        if (P.rerun) {
+            // iir_rerun.cuh: the run again from its true entry state (offset by the steady state of the bias)
+            double w[kMaxS];
+            for (int i = 0; i < S; i++) w[i] = sb[i] + s0[i];
+            for (int t = 0; t < LT; t++) {
+                double y;
+                step(P, w, x[r * LT + t] + bias, &y);
+                if (t % D == 0) out[r * NK + t / D] = fma(y, gain, out_bias);
+            }
+        } else
         for (int m = 0; m < NK; m++) {
             double y = ys[m];
             for (int c = 0; c < S; c++) y = fma(P.tables.R[m][c], s0[c], y);

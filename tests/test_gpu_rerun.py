@@ -1,0 +1,165 @@
+"""Parity of kernel (b)'s full-rate form (csrc/iir_rerun.cuh: the input tile stays in shared memory and each run is
+filtered a second time from its true entry state) with the CPU oracle: every input kind, every output format,
+the S1G and HiF field orders, chunked submits, batches with ragged lengths, unaligned output buffers.
+D = 1 is what the reference's own Soapy filters run at (CaribouliteStream.cpp:85-91,282-367: order 6, no
+decimation).  Tolerance as in test_gpu_iir.py.  Runs through the C ABI."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5
+
+
+def rel_rms(a, b):
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    return np.sqrt(np.mean((a - b) ** 2, axis=0)) / np.sqrt(np.mean(b ** 2, axis=0))
+
+
+def _dev(torch, a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to("cuda:0")
+
+
+def _cs16(po, w, channel=0):
+    _, cs16, _, _ = po.smi_read(w.view(np.uint8), w.size, channel)
+    return cs16[: w.size]
+
+
+@pytest.mark.parametrize("order,fc", [(1, 100e3), (2, 100e3), (3, 50e3), (4, 250e3), (6, 10e3), (6, 50e3), (8, 400e3)])
+@pytest.mark.parametrize("kind", ["words", "cs16", "cf32"])
+def test_full_rate_every_input_kind(cb, po, torch_cuda, order, fc, kind):
+    torch = torch_cuda
+    n = (1 << 18) + 64 * 13 + 7            # whole tiles, a partial tile and a tail
+    sos = po.butter_lowpass_sos(order, 4e6, fc)
+    w = po.gen_words(n, seed=order)
+    cs16 = _cs16(po, w)
+    x = po.cs16_to_cf32(cs16)
+    ref = po.filter_cf32_f32(sos, x)
+    out = torch.zeros((n, 2), dtype=torch.float32, device="cuda:0")
+    with cb.Context(sos=sos, decimation=1, parity=cb.PARITY_F32) as ctx:
+        fi = ctx.filter_info()
+        assert fi.run_len == 64 and fi.decimation == 1          # the rerun plan (tests/test_host_plan.py)
+        if kind == "words":
+            pad = np.zeros((n + 3) & ~3, np.uint32)
+            pad[:n] = w
+            ctx.filter_submit(cb.IN_WORDS, _dev(torch, pad.view(np.int32)), n, out)
+        elif kind == "cs16":
+            ctx.filter_submit(cb.IN_CS16, _dev(torch, cs16), n, out)      # scaled by 1/4096 like the words (parity F32)
+        else:
+            ctx.filter_submit(cb.IN_CF32, _dev(torch, x), n, out)
+        ret, res = ctx.wait()
+        assert res.n_filtered == n
+    assert np.all(rel_rms(out.cpu().numpy(), ref) <= TOL)
+
+
+def test_full_rate_hif_field_order(cb, po, torch_cuda):
+    """HiF words carry I in bits 13:1 (caribou_smi.c:371-373): its own kernel instantiation."""
+    torch = torch_cuda
+    n = 1 << 18
+    sos = po.butter_lowpass_sos(6, 4e6, 25e3)
+    w = po.gen_words(n, seed=3)
+    ref = po.filter_cf32_f32(sos, po.cs16_to_cf32(_cs16(po, w, channel=po.CH_HIF)))
+    out = torch.zeros((n, 2), dtype=torch.float32, device="cuda:0")
+    with cb.Context(sos=sos, decimation=1, parity=cb.PARITY_F32, channel=cb.CH_HIF) as ctx:
+        ctx.rx_submit(_dev(torch, w.view(np.int32)), n * 4, out)
+        ret, res = ctx.wait()
+        assert ret == n
+    assert np.all(rel_rms(out.cpu().numpy(), ref) <= TOL)
+
+
+def test_full_rate_chunked_equals_one_shot_and_state_matches_reference(cb, po, torch_cuda):
+    torch = torch_cuda
+    n = 1 << 18
+    sos = po.butter_lowpass_sos(6, 4e6, 10e3)
+    w = po.gen_words(n, seed=5)
+    ci, cq = po.Cascade(sos), po.Cascade(sos)
+    ref = po.filter_cf32_f32(sos, po.cs16_to_cf32(_cs16(po, w)), ci, cq)
+    d_w = _dev(torch, w.view(np.int32))
+    one = torch.zeros((n, 2), dtype=torch.float32, device="cuda:0")
+    parts = torch.zeros((n, 2), dtype=torch.float32, device="cuda:0")
+    cuts = [0, 4096, 4096 + 1000 * 4, 100000, 100000 + 4 * 77, n]
+    with cb.Context(sos=sos, decimation=1, parity=cb.PARITY_F32) as ctx:
+        ctx.filter_submit(cb.IN_WORDS, d_w, n, one)
+        ctx.wait()
+        st_one = ctx.get_state()
+    with cb.Context(sos=sos, decimation=1, parity=cb.PARITY_F32) as ctx:
+        for a, b in zip(cuts[:-1], cuts[1:]):
+            ctx.filter_submit(cb.IN_WORDS, d_w[a:b], b - a, parts[a:b])
+        ctx.wait()
+        st_parts = ctx.get_state()
+    assert np.all(rel_rms(one.cpu().numpy(), ref) <= TOL)
+    assert np.all(rel_rms(parts.cpu().numpy(), ref) <= TOL)
+    assert np.all(rel_rms(parts.cpu().numpy(), one.cpu().numpy()) <= 1e-6)
+    ref_state = np.concatenate([ci.state, cq.state])
+    np.testing.assert_allclose(st_one, ref_state, rtol=1e-9, atol=0)
+    np.testing.assert_allclose(st_parts, ref_state, rtol=1e-9, atol=0)
+
+
+def test_full_rate_batch_of_ragged_streams(cb, po, torch_cuda):
+    torch = torch_cuda
+    ns, n = 5, 5 * 2048 + 64 * 3 + 40
+    sos = po.butter_lowpass_sos(4, 4e6, 250e3)
+    ws = [po.gen_words(n, seed=10 + s) for s in range(ns)]
+    d_w = _dev(torch, np.stack(ws).view(np.int32))
+    out = torch.zeros((ns, n, 2), dtype=torch.float32, device="cuda:0")
+    with cb.Context(sos=sos, decimation=1, parity=cb.PARITY_F32, n_streams=ns) as ctx:
+        ctx.rx_submit(d_w, n * 4, out, stride_bytes=n * 4, filt_stride=n)
+        ret, res = ctx.wait()
+        assert ret == n
+        states = [ctx.get_state(s) for s in range(ns)]
+    for s in range(ns):
+        ci, cq = po.Cascade(sos), po.Cascade(sos)
+        ref = po.filter_cf32_f32(sos, po.cs16_to_cf32(_cs16(po, ws[s])), ci, cq)
+        assert np.all(rel_rms(out[s].cpu().numpy(), ref) <= TOL)
+        np.testing.assert_allclose(states[s], np.concatenate([ci.state, cq.state]), rtol=1e-9)
+
+
+@pytest.mark.parametrize("fmt", ["CF32", "CS16", "CF64", "CS8"])
+def test_full_rate_formats_and_unaligned_output(cb, po, torch_cuda, fmt):
+    """The Soapy formats at full rate (reference ordering for CS16 / CS8, CaribouliteStream.cpp:291-298,349-367) against
+    the oracle, and a buffer the 32-byte stores cannot be used on gives the same bits through scalar stores."""
+    torch = torch_cuda
+    n = 1 << 17
+    sos = po.butter_lowpass_sos(6, 4e6, 50e3)
+    w = po.gen_words(n, seed=7)
+    cs16 = _cs16(po, w)
+    dt = {"CF32": torch.float32, "CS16": torch.int16, "CF64": torch.float64, "CS8": torch.int8}[fmt]
+    parity = cb.PARITY_F32 if fmt in ("CF32", "CF64") else cb.PARITY_Q16
+    if parity == cb.PARITY_Q16:
+        q = po.filter_cs16_q16(sos, cs16)
+        ref = q if fmt == "CS16" else po.cs16_to_cs8(q)
+    else:
+        ref = po.filter_cf32_f32(sos, po.cs16_to_cf32(cs16))
+    big = torch.zeros((n + 1, 2), dtype=dt, device="cuda:0")
+    results = []
+    for out in (big[:n], big[1:]):
+        big.zero_()
+        torch.cuda.synchronize()
+        with cb.Context(sos=sos, decimation=1, parity=parity, out_format=getattr(cb, "FMT_" + fmt)) as ctx:
+            ctx.filter_submit(cb.IN_WORDS, _dev(torch, w.view(np.int32)), n, out)
+            ret, res = ctx.wait()
+            assert res.n_filtered == n
+        results.append(out.clone())
+    assert torch.equal(results[0], results[1])
+    got = results[0].cpu().numpy()
+    if parity == cb.PARITY_Q16:
+        diff = np.abs(got.astype(np.float64) - ref.astype(np.float64))
+        assert diff.max() <= 1.0001 and np.mean(diff > 0) < 1e-4      # an LSB may flip when y is within ~1e-10 of an integer
+    else:
+        assert np.all(rel_rms(got, ref) <= TOL)
+
+
+def test_full_rate_repeat_is_bit_identical(cb, po, torch_cuda):
+    torch = torch_cuda
+    n = 1 << 20
+    sos = po.butter_lowpass_sos(4, 4e6, 250e3)
+    d_w = _dev(torch, po.gen_words(n, seed=11).view(np.int32))
+    outs = []
+    for _ in range(2):
+        out = torch.zeros((n, 2), dtype=torch.float32, device="cuda:0")
+        with cb.Context(sos=sos, decimation=1, parity=cb.PARITY_F32) as ctx:
+            ctx.filter_submit(cb.IN_WORDS, d_w, n, out)
+            ctx.wait()
+        outs.append(out)
+    assert torch.equal(outs[0], outs[1])

@@ -30,10 +30,10 @@ def emul(tmp_path_factory):
 
 
 def plan_info(L, sos, D, y32, force_cascade=0):
-    info = np.zeros(9)
+    info = np.zeros(10)
     assert L.emul_plan_info(len(sos), sos.ctypes.data, D, force_cascade, y32, info.ctypes.data) == 0
     return dict(par=int(info[0]), window=int(info[1]), chained=int(info[2]), decay=int(info[3]), par_err=info[4],
-                hn1=info[5], run_len=int(info[6]), kept=int(info[7]), y32=int(info[8]))
+                hn1=info[5], run_len=int(info[6]), kept=int(info[7]), y32=int(info[8]), rerun=int(info[9]))
 
 
 def test_run_lengths_follow_the_shared_memory_budget(emul, po):
@@ -45,8 +45,15 @@ def test_run_lengths_follow_the_shared_memory_budget(emul, po):
             for y32 in (0, 1):
                 p = plan_info(emul, sos, D, y32)
                 assert p["run_len"] % 32 == 0 and p["run_len"] % D == 0
-                assert p["kept"] == p["run_len"] // D and p["kept"] <= 32 and p["kept"] % 4 == 0
-                assert p["par"] == 1 and p["y32"] == y32          # Butterworth poles are distinct: parallel form
+                assert p["kept"] == p["run_len"] // D and p["kept"] % 4 == 0
+                assert p["par"] == 1                              # Butterworth poles are distinct: parallel form
+                if p["rerun"]:
+                    # full-rate streams (csrc/iir_rerun.cuh): the input tile is what stays in shared memory, there is
+                    # no stage of kept outputs to bound the run and no float staging
+                    assert D == 1 and p["y32"] == 0 and p["run_len"] == 64
+                else:
+                    assert p["kept"] <= 32 and p["y32"] == y32
+    assert plan_info(emul, po.butter_lowpass_sos(4, 4e6, 250e3), 1, 1, force_cascade=1)["rerun"] == 0   # cascade form: staged kernel
     sos4 = po.butter_lowpass_sos(4, 4e6, 250e3)
     assert plan_info(emul, sos4, 8, 1)["run_len"] == 160          # the C4 configuration (profiles/r1_sweeps.txt, sweep 18)
     assert plan_info(emul, sos4, 16, 1)["run_len"] == 320
