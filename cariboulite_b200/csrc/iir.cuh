@@ -145,11 +145,12 @@ __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
 #ifndef CBL_RR_WARPS3
 #define CBL_RR_WARPS3 12
 #endif
-#ifndef CBL_RR_NBUF
-#define CBL_RR_NBUF 2
+#ifndef CBL_RR_P3U
+#define CBL_RR_P3U 1             // chunks of four outputs per iteration of the rerun kernel's phase-3 loop
 #endif
 constexpr int kRerunMaxD = CBL_RR_MAXD;
 constexpr int kRerunLT   = CBL_RR_LT;
+constexpr int kRerunP3Unroll = CBL_RR_P3U;
 static_assert(kRerunMaxD <= 2, "rerun kernels exist for D = 1 and D = 2");
 inline bool iir_is_rerun(int D, bool par) { return par && D <= kRerunMaxD; }
 #ifndef CBL_IIR_STAGES

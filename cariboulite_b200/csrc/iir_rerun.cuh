@@ -10,11 +10,16 @@
 // outputs straight into 32-byte stores.  FP64 work per complex sample at D = 1: 4K + 8K + 2 instead of
 // 8K + 4K + 2 plus the per-tile work of 32-sample runs; shared memory per warp: two input tiles.
 //
-//   iteration i of a warp:   phase 1-2 of tile i (ring slot i % NBUF)
-//                            look-back + phase 3 of tile i-1 (the slot before)     <- one tile late, as before
-//                            that slot is free: the TMA boxes of tile i + NBUF - 1 are requested into it
-// With two slots the request is consumed right away by the next iteration's phase 1 and the other warps of the
-// SMSP cover its latency; with three it has a whole iteration of slack at the price of fewer warps per SM.
+//   iteration i of a warp:   phase 1-2 of tile i (ring slot i & 1)
+//                            ticket for tile i+1 (its round trip hides behind phase 3)
+//                            look-back + phase 3 of tile i-1 (the other slot)      <- one tile late, as before
+//                            that slot is free: the TMA boxes of tile i+1 are requested into it
+// The request is consumed right away by the next iteration's phase 1; the other warps of the SMSP cover its
+// latency (a third slot buys a whole iteration of slack but costs a quarter of the warps: slower, sweep 22).
+// Tickets are taken half an iteration ahead, not two iterations as in the staged kernel: an iteration is long
+// here, and the further ahead tiles are handed out the further the warps that own neighbouring tiles drift
+// apart - with narrow filters, whose look-back reads several predecessors, a fifth of the time went into
+// waiting for aggregates (sweep 23).
 #pragma once
 #include "iir_kernel.cuh"
 
@@ -27,7 +32,7 @@ struct RerunCfg {
     static constexpr int NK    = LT / D;
     static constexpr int SPS   = (IN == IN_CF32) ? 16 : 32;   // samples per 128-byte row step
     static constexpr int NSTEP = LT / SPS;                    // 4 KiB boxes per tile
-    static constexpr int NBUF  = CBL_RR_NBUF;                 // input tiles a warp holds: 2, or 3 to request a tile a whole iteration ahead
+    static constexpr int NBUF  = 2;                           // input tiles a warp holds
     static constexpr int HALF_BYTES    = NSTEP * 4096;        // one tile
     static constexpr int RING_BYTES    = NBUF * HALF_BYTES;
     static constexpr int SCRATCH_BYTES = 2 * S * 8 * 2;
@@ -38,7 +43,6 @@ struct RerunCfg {
     static constexpr int WPC = SMEM_WARPS < REG_WARPS ? SMEM_WARPS : REG_WARPS;
     static_assert(WPC >= 1, "a warp's buffers do not fit shared memory");
     static_assert(LT % 32 == 0 && (D == 1 || D == 2), "phase 3 works in groups of 8 or 16 samples: whole chunks of 4 kept outputs");
-    static_assert(NBUF == 2 || NBUF == 3, "two or three input tiles per warp");
     static constexpr int SMEM_BYTES = WPC * WARP_BYTES + WPC * NBUF * NSTEP * 8 + 1024;
 };
 
@@ -163,16 +167,14 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     };
 
     uint32_t slot = 0, par = 0;    // ring slot of the tile in phases 1-2 and the parity its barriers complete with
-    uint32_t tile = 0xFFFFFFFFu, next = 0xFFFFFFFFu;
+    uint32_t tile = 0xFFFFFFFFu;
     uint32_t* const ticket = P.ticket + __ldg(P.ticket + 32 + lane);      // words 32..63 of the ticket block stay zero
     if (lane == 0) {
         tile = take_ticket(ticket);
-        next = take_ticket(ticket);
     }
     tile = __shfl_sync(0xffffffffu, tile, 0);
     uint32_t stream = tile / tps, tis = tile - stream * tps;
     if (lane == 0 && tile < P.total_tiles) issue_tile(stream, tis, 0u);
-    if (C::NBUF == 3 && lane == 0 && next < P.total_tiles) issue_tile(next / tps, next % tps, 1u);
 
     bool owe = false;
     uint32_t ptile = 0, pstream = 0, ptis = 0;
@@ -186,12 +188,9 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         const bool have = tile < P.total_tiles;
         const uint32_t half = slot;
         const uint32_t prev = slot == 0 ? (uint32_t)C::NBUF - 1u : slot - 1u;     // the owed tile's slot
-        uint32_t next2 = 0xFFFFFFFFu, nstream = 0, ntis = 0;
+        uint32_t next = 0xFFFFFFFFu;       // meaningful in lane 0
         double f[2][S];
         if (have) {
-            if (lane == 0) next2 = take_ticket(ticket);
-            nstream = next / tps;
-            ntis = next - nstream * tps;
 
             // ---- phase 1: the run from the steady state, end state only
             double va[K][2], vb[K][2];
@@ -204,19 +203,24 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             for (int step = 0; step < C::NSTEP; step++) {
                 mbar_wait(bar_u32 + 8 * (half * C::NSTEP + step), par);
                 const uint32_t box = ring_u32 + half * C::HALF_BYTES + step * 4096;
-                uint4 q[8];
+                // the 128-byte row in two groups of four pieces: the loops of a tile iteration have to share the
+                // 32 KiB instruction cache of the SM with eleven other warps in other phases
+#pragma unroll 1
+                for (int co = 0; co < 8; co += 4) {
+                    uint4 q[4];
 #pragma unroll
-                for (int ci = 0; ci < 8; ci++) q[ci] = row_piece(box, ci);
+                    for (int ci = 0; ci < 4; ci++) q[ci] = row_piece(box, co + ci);
 #pragma unroll
-                for (int ci = 0; ci < 8; ci++) {
-                    const uint32_t wv[4] = {q[ci].x, q[ci].y, q[ci].z, q[ci].w};
+                    for (int ci = 0; ci < 4; ci++) {
+                        const uint32_t wv[4] = {q[ci].x, q[ci].y, q[ci].z, q[ci].w};
 #pragma unroll
-                    for (int e = 0; e < (IN == IN_CF32 ? 2 : 4); e++) {
-                        double xa, xb;
-                        if (INJECT) inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
-                        else sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
-                        filter_step<K, PAR, false>(T, va, xa);
-                        filter_step<K, PAR, false>(T, vb, xb);
+                        for (int e = 0; e < (IN == IN_CF32 ? 2 : 4); e++) {
+                            double xa, xb;
+                            if (INJECT) inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
+                            else sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
+                            filter_step<K, PAR, false>(T, va, xa);
+                            filter_step<K, PAR, false>(T, vb, xb);
+                        }
                     }
                 }
             }
@@ -257,6 +261,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                     }
                 }
             }
+            if (lane == 0) next = take_ticket(ticket);      // looked at after phase 3
             if (lane == 31 && !P.chained) {
                 double* agg = P.desc_agg + (size_t)tile * (2 * S);
 #pragma unroll
@@ -279,16 +284,26 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                     sin_c = __longlong_as_double((long long)pre);
                     if (!P.chained) {
                         const int depth = (int)ptis < P.window ? (int)ptis : P.window;
-                        for (int j = 2; j <= depth; j++) {
+                        // two tiles' aggregates are requested together (one L2 round trip for both)
+                        for (int j = 2; j <= depth; j += 2) {
+                            const bool two = j + 1 <= depth;
                             const double* a = P.desc_agg + (size_t)(ptile - j) * (2 * S) + crail * S;
+                            const double* a2 = a - (two ? 2 * S : 0);
                             const double* mp = P.mtile_pow + (size_t)(j - 1) * (S * S) + crow * S;
-                            unsigned long long dv[S];
+                            unsigned long long dv[S], dw[S];
 #pragma unroll
-                            for (int col = 0; col < S; col++) dv[col] = ld_desc(a + col);
+                            for (int col = 0; col < S; col++) { dv[col] = ld_desc(a + col); dw[col] = ld_desc(a2 + col); }
 #pragma unroll
                             for (int col = 0; col < S; col++) {
                                 while (dv[col] == kDescEmpty) { __nanosleep(32); dv[col] = ld_desc(a + col); }
                                 sin_c = fma(__ldg(mp + col), __longlong_as_double((long long)dv[col]), sin_c);
+                            }
+                            if (two) {
+#pragma unroll
+                                for (int col = 0; col < S; col++) {
+                                    while (dw[col] == kDescEmpty) { __nanosleep(32); dw[col] = ld_desc(a2 + col); }
+                                    sin_c = fma(__ldg(mp + S * S + col), __longlong_as_double((long long)dw[col]), sin_c);
+                                }
                             }
                         }
                         if ((int)ptis <= P.window) {     // the window reaches the start of the stream
@@ -361,50 +376,53 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                     vb[k][0] = T.sbias[2 * k] + s0[1][2 * k];     vb[k][1] = T.sbias[2 * k + 1] + s0[1][2 * k + 1];
                 }
                 uint64_t o = (uint64_t)pstream * P.out_stride + (uint64_t)run * C::NK;
-                const uint32_t ohalf = prev;
-                constexpr int PER = (IN == IN_CF32) ? 2 : 4;      // samples per 16 bytes
-#pragma unroll 1
-                for (int step = 0; step < C::NSTEP; step++) {
-                    const uint32_t box = ring_u32 + ohalf * C::HALF_BYTES + step * 4096;
-                    // the row in two groups of four pieces: the group body is unrolled (kept positions are static)
-#pragma unroll 1
-                    for (int co = 0; co < 2; co++) {
-                        uint4 q[4];
+                constexpr int PER = (IN == IN_CF32) ? 2 : 4;      // samples per 16-byte piece
+                constexpr int PP  = 4 * D / PER;                  // pieces that hold four kept outputs = one store
+                const uint32_t tile_u32 = ring_u32 + prev * C::HALF_BYTES;
+                // one chunk of four kept outputs per iteration, not unrolled (one copy of the format switch in
+                // store_out4); the next chunk's pieces are read while this one is filtered
+                auto chunk_pieces = [&](int ch, uint4 (&q)[PP]) {
+                    const int p0 = ch * PP;                       // piece within the run: box p0 / 8, piece p0 % 8
 #pragma unroll
-                        for (int ci = 0; ci < 4; ci++) q[ci] = row_piece(box, co * 4 + ci);
-                        double yi[4], yq[4];
+                    for (int i = 0; i < PP; i++) q[i] = row_piece(tile_u32 + (uint32_t)(p0 >> 3) * 4096u, (p0 & 7) + i);
+                };
+                uint4 qn[PP];
+                chunk_pieces(0, qn);
+#pragma unroll (kRerunP3Unroll)
+                for (int ch = 0; ch < C::NK / 4; ch++) {
+                    uint4 q[PP];
 #pragma unroll
-                        for (int ci = 0; ci < 4; ci++) {
-                            const uint32_t wv[4] = {q[ci].x, q[ci].y, q[ci].z, q[ci].w};
+                    for (int i = 0; i < PP; i++) q[i] = qn[i];
+                    if (ch + 1 < C::NK / 4) chunk_pieces(ch + 1, qn);
+                    double yi[4], yq[4];
 #pragma unroll
-                            for (int e = 0; e < PER; e++) {
-                                const int j = ci * PER + e;          // sample within the group (group starts on a multiple of D)
-                                double xa, xb;
-                                if (INJECT) inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
-                                else sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
-                                if (j % D == 0) {
-                                    const int m = (j / D) & 3;
-                                    yi[m] = fma(filter_step<K, PAR, true>(T, va, xa), T.gain, T.out_bias);
-                                    yq[m] = fma(filter_step<K, PAR, true>(T, vb, xb), T.gain, T.out_bias);
-                                    if (m == 3) { store_out4(P, o, yi, yq); o += 4; }
-                                } else {
-                                    filter_step<K, PAR, false>(T, va, xa);
-                                    filter_step<K, PAR, false>(T, vb, xb);
-                                }
+                    for (int ci = 0; ci < PP; ci++) {
+                        const uint32_t wv[4] = {q[ci].x, q[ci].y, q[ci].z, q[ci].w};
+#pragma unroll
+                        for (int e = 0; e < PER; e++) {
+                            const int j = ci * PER + e;          // sample within the chunk (chunks start on multiples of D)
+                            double xa, xb;
+                            if (INJECT) inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
+                            else sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
+                            if (j % D == 0) {
+                                yi[j / D] = fma(filter_step<K, PAR, true>(T, va, xa), T.gain, T.out_bias);
+                                yq[j / D] = fma(filter_step<K, PAR, true>(T, vb, xb), T.gain, T.out_bias);
+                            } else {
+                                filter_step<K, PAR, false>(T, va, xa);
+                                filter_step<K, PAR, false>(T, vb, xb);
                             }
                         }
                     }
+                    store_out4(P, o, yi, yq);
+                    o += 4;
                 }
             }
             __syncwarp();   // the owed tile's ring slot and the scratch are free again
         }
         if (!have) break;
-        // the slot the owed tile just left takes the tile NBUF - 1 tickets ahead
-        if (C::NBUF == 2) {
-            if (lane == 0 && next < P.total_tiles) issue_tile(nstream, ntis, prev);
-        } else {
-            if (lane == 0 && next2 < P.total_tiles) issue_tile(next2 / tps, next2 % tps, prev);
-        }
+        // the slot the owed tile just left takes this warp's next tile
+        const uint32_t nstream = next / tps, ntis = next - nstream * tps;
+        if (lane == 0 && next < P.total_tiles) issue_tile(nstream, ntis, prev);
         owe = true;
         ptile = tile; pstream = stream; ptis = tis;
 #pragma unroll
@@ -415,7 +433,6 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         tile = __shfl_sync(0xffffffffu, next, 0);
         stream = __shfl_sync(0xffffffffu, nstream, 0);
         tis = __shfl_sync(0xffffffffu, ntis, 0);
-        next = next2;
     }
 }
 

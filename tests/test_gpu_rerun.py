@@ -163,3 +163,26 @@ def test_full_rate_repeat_is_bit_identical(cb, po, torch_cuda):
             ctx.wait()
         outs.append(out)
     assert torch.equal(outs[0], outs[1])
+
+
+@pytest.mark.parametrize("order,fc", [(4, 250e3), (6, 10e3), (6, 25e3), (6, 50e3)])
+def test_full_rate_reordering_error_in_fp64(cb, po, torch_cuda, order, fc):
+    """The reordering error of the full-rate form, stated as north_star asks: CF64 output against the oracle's
+    sequential FP64 DF-II cascade.  Inside a run the samples are filtered in the reference's order from the run's
+    true entry state; what differs is that state (warp scan + look-back) and the parallel-form realisation.
+    Numbers in DESIGN.md; the bound asserted here is 1e-9 of RMS."""
+    torch = torch_cuda
+    n = 1 << 20
+    sos = po.butter_lowpass_sos(order, 4e6, fc)
+    w = po.gen_words(n)
+    x = _cs16(po, w).astype(np.float64) / 4096.0
+    ref = np.stack([po.Cascade(sos).run_f64(np.ascontiguousarray(x[:, r])) for r in range(2)], axis=1)
+    out = torch.zeros((n, 2), dtype=torch.float64, device="cuda:0")
+    with cb.Context(sos=sos, decimation=1, parity=cb.PARITY_F32, out_format=cb.FMT_CF64) as ctx:
+        ctx.filter_submit(cb.IN_WORDS, _dev(torch, w.view(np.int32)), n, out)
+        ctx.wait()
+    got = out.cpu().numpy()
+    err = rel_rms(got, ref)
+    mx = np.max(np.abs(got - ref)) / np.sqrt(np.mean(ref ** 2))
+    print("\nfull-rate reordering error order %d fc %g: rel-rms %s, max/rms %.3g" % (order, fc, err, mx))
+    assert np.all(err <= 1e-9), err
