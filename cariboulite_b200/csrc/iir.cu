@@ -13,7 +13,7 @@ int launch_iir(int K, int D, int in_kind, bool par, bool y32, const CUtensorMap&
                const IirTables& t, int num_sms, cudaStream_t st)
 {
     iir_launch_fn fn = nullptr;
-    if (iir_is_rerun(D, par)) {
+    if (iir_is_rerun(K, D, par)) {
         switch (K) {
             case 1: fn = iir_rerun_k1(D, in_kind); break;
             case 2: fn = iir_rerun_k2(D, in_kind); break;

@@ -133,8 +133,10 @@ __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
 // Full-rate and lightly decimated streams of the parallel realisation take the rerun kernel (iir_rerun.cuh): the
 // input tile stays in shared memory and is filtered a second time from the true entry state, so the run length is
 // set by the input (two tiles of LT * 128 bytes per warp), not by a stage of kept outputs.
-#ifndef CBL_RR_MAXD
-#define CBL_RR_MAXD 1            // largest decimation that takes the rerun kernel (0: never; at most 2)
+// Which streams: every full-rate one, and decimate-by-2 from three sections on (sweeps 22 and 25: at D = 2 the
+// staged kernel still wins for K <= 2, at D >= 4 everywhere).
+#ifndef CBL_RR_ENABLE
+#define CBL_RR_ENABLE 1          // 0: staged kernel everywhere (A/B builds)
 #endif
 #ifndef CBL_RR_LT
 #define CBL_RR_LT 64
@@ -148,11 +150,12 @@ __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
 #ifndef CBL_RR_P3U
 #define CBL_RR_P3U 1             // chunks of four outputs per iteration of the rerun kernel's phase-3 loop
 #endif
-constexpr int kRerunMaxD = CBL_RR_MAXD;
 constexpr int kRerunLT   = CBL_RR_LT;
 constexpr int kRerunP3Unroll = CBL_RR_P3U;
-static_assert(kRerunMaxD <= 2, "rerun kernels exist for D = 1 and D = 2");
-inline bool iir_is_rerun(int D, bool par) { return par && D <= kRerunMaxD; }
+__host__ __device__ constexpr bool iir_is_rerun(int K, int D, bool par)
+{
+    return CBL_RR_ENABLE != 0 && par && (D == 1 || (D == 2 && K >= 3));
+}
 #ifndef CBL_IIR_STAGES
 #define CBL_IIR_STAGES 2
 #endif

@@ -757,7 +757,7 @@ typedef int (*iir_launch_fn)(const CUtensorMap&, const IirParams&, const IirTabl
 template <int K, int D, int IN, bool PAR, bool Y32>
 iir_launch_fn staged_launch()
 {
-    if constexpr (PAR && D <= kRerunMaxD) return nullptr;
+    if constexpr (iir_is_rerun(K, D, PAR)) return nullptr;
     else return &launch_iir_t<K, D, IN, PAR, Y32>;
 }
 

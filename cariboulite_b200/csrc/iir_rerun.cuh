@@ -1,4 +1,5 @@
-// Kernel (b), full-rate and lightly decimated form (D <= kRerunMaxD, parallel realisation): the "rerun" kernel.
+// Kernel (b), full-rate and lightly decimated form (iir_is_rerun(): D = 1, and D = 2 from three sections on; parallel
+// realisation): the "rerun" kernel.
 //
 // The staged kernel (iir_kernel.cuh) keeps the zero-state outputs of a run in shared memory and corrects each
 // kept one with R[m] . s0 later.  That pays when few outputs are kept; at D = 1 every sample is kept, the stage
@@ -453,21 +454,22 @@ int launch_rerun_t(const CUtensorMap& tmap, const IirParams& p, const IirTables&
     return (int)cudaGetLastError();
 }
 
+template <int KK, int D>
+iir_launch_fn rerun_pick_kind(int in_kind)
+{
+    if constexpr (iir_is_rerun(KK, D, true)) {
+        if (in_kind == IN_WORDS) return &launch_rerun_t<KK, D, IN_WORDS>;
+        if (in_kind == IN_WORDS_HIF) return &launch_rerun_t<KK, D, IN_WORDS_HIF>;
+        if (in_kind == IN_CS16) return &launch_rerun_t<KK, D, IN_CS16>;
+        if (in_kind == IN_CF32) return &launch_rerun_t<KK, D, IN_CF32>;
+    }
+    return nullptr;
+}
+
 template <int KK>
 iir_launch_fn rerun_pick_launch(int D, int in_kind)
 {
-#define CBL_RR_CASE(DD)                                                                  \
-    if (D == DD && DD <= kRerunMaxD) {                                                   \
-        constexpr int DE = DD <= kRerunMaxD ? DD : 1;                                    \
-        if (in_kind == IN_WORDS) return &launch_rerun_t<KK, DE, IN_WORDS>;               \
-        if (in_kind == IN_WORDS_HIF) return &launch_rerun_t<KK, DE, IN_WORDS_HIF>;       \
-        if (in_kind == IN_CS16) return &launch_rerun_t<KK, DE, IN_CS16>;                 \
-        if (in_kind == IN_CF32) return &launch_rerun_t<KK, DE, IN_CF32>;                 \
-    }
-    CBL_RR_CASE(1)
-    CBL_RR_CASE(2)
-#undef CBL_RR_CASE
-    return nullptr;
+    return D == 1 ? rerun_pick_kind<KK, 1>(in_kind) : (D == 2 ? rerun_pick_kind<KK, 2>(in_kind) : nullptr);
 }
 
 }  // namespace cbl

@@ -415,7 +415,7 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, 
     if (!P->par) { for (int i = 0; i < kMaxS; i++) P->sstar[i] = 0; P->hn1 = 1; }
     // the float-staged kernels exist for the preferred realisation only; they afford longer runs
     // (the rerun kernel of full-rate streams stages nothing: its run length comes from the input tile)
-    P->rerun = iir_is_rerun(D, P->par);
+    P->rerun = iir_is_rerun(K, D, P->par);
     P->y32 = !P->rerun && want_y32 && iir_has_y32(K, P->par);
     P->LT = P->rerun ? kRerunLT : iir_run_len(K, D, P->y32);
     P->NK = P->LT / D;

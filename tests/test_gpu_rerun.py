@@ -186,3 +186,28 @@ def test_full_rate_reordering_error_in_fp64(cb, po, torch_cuda, order, fc):
     mx = np.max(np.abs(got - ref)) / np.sqrt(np.mean(ref ** 2))
     print("\nfull-rate reordering error order %d fc %g: rel-rms %s, max/rms %.3g" % (order, fc, err, mx))
     assert np.all(err <= 1e-9), err
+
+
+@pytest.mark.parametrize("order,fc", [(5, 100e3), (6, 10e3), (6, 50e3), (8, 400e3)])
+@pytest.mark.parametrize("kind", ["words", "cf32"])
+def test_decimate_by_two_from_three_sections_on(cb, po, torch_cuda, order, fc, kind):
+    """D = 2 takes the rerun kernel when the cascade has three or more sections (csrc/iir.cuh iir_is_rerun)."""
+    torch = torch_cuda
+    n, D = (1 << 18) + 64 * 5 + 6, 2
+    sos = po.butter_lowpass_sos(order, 4e6, fc)
+    w = po.gen_words(n, seed=20 + order)
+    x = po.cs16_to_cf32(_cs16(po, w))
+    ci, cq = po.Cascade(sos), po.Cascade(sos)
+    ref = po.filter_cf32_f32(sos, x, ci, cq)[::D]
+    out = torch.zeros((n // D, 2), dtype=torch.float32, device="cuda:0")
+    with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32) as ctx:
+        assert ctx.filter_info().run_len == 64
+        if kind == "words":
+            ctx.filter_submit(cb.IN_WORDS, _dev(torch, w.view(np.int32)), n, out)
+        else:
+            ctx.filter_submit(cb.IN_CF32, _dev(torch, x), n, out)
+        ret, res = ctx.wait()
+        assert res.n_filtered == n // D
+        st = ctx.get_state()
+    assert np.all(rel_rms(out.cpu().numpy(), ref) <= TOL)
+    np.testing.assert_allclose(st, np.concatenate([ci.state, cq.state]), rtol=1e-9, atol=0)

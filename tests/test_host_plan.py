@@ -50,7 +50,7 @@ def test_run_lengths_follow_the_shared_memory_budget(emul, po):
                 if p["rerun"]:
                     # full-rate streams (csrc/iir_rerun.cuh): the input tile is what stays in shared memory, there is
                     # no stage of kept outputs to bound the run and no float staging
-                    assert D == 1 and p["y32"] == 0 and p["run_len"] == 64
+                    assert (D == 1 or (D == 2 and len(sos) >= 3)) and p["y32"] == 0 and p["run_len"] == 64
                 else:
                     assert p["kept"] <= 32 and p["y32"] == y32
     assert plan_info(emul, po.butter_lowpass_sos(4, 4e6, 250e3), 1, 1, force_cascade=1)["rerun"] == 0   # cascade form: staged kernel
