@@ -429,7 +429,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
         // L2 round trip hides behind the scan.
         const int comp = lane < 2 * S ? lane : 0;
         unsigned long long pre = kDescEmpty;
-        if (owe && ptis != 0 && lane < 2 * S)
+        if (owe && ptis != 0)
             pre = ld_desc((P.chained ? P.desc_incl : P.desc_agg) + (size_t)(ptile - 1) * (2 * S) + comp);
 
         if (have) {
@@ -476,7 +476,11 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             const uint32_t ystage = ystage0 + (buf ^ 1u) * C::YSTAGE_BYTES;
             // state entering the tile, component `lane` (< 2S) per lane
             const int crail = comp / S, crow = comp % S;
-            if (lane < 2 * S) {
+            // Every lane walks the look-back (lanes >= 2S repeat component 0: same addresses, no extra traffic) and
+            // only the store is predicated: with the walk under `if (lane < 2S)` and more than one trip through its
+            // loop, the two groups of lanes stayed apart all the way through phase 3 - every instruction issued
+            // twice, at 16 threads (ncu, order 6 at fc = 10 kHz: profiles/r1_sweeps.txt, sweep 26).
+            {
                 double sin_c = 0.0;
                 if (ptis == 0) {
                     sin_c = P.state_in[(size_t)pstream * (2 * S) + (crail ^ swap) * S + crow];
@@ -507,7 +511,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                         }
                     }
                 }
-                sts64(scratch + lane * 8, sin_c);
+                if (lane < 2 * S) sts64(scratch + lane * 8, sin_c);
             }
             __syncwarp();
             double sin[2][S];
