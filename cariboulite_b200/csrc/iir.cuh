@@ -147,6 +147,9 @@ __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
 #ifndef CBL_RR_WARPS3
 #define CBL_RR_WARPS3 12
 #endif
+#ifndef CBL_RR_WARPS4
+#define CBL_RR_WARPS4 12
+#endif
 #ifndef CBL_RR_P3U
 #define CBL_RR_P3U 1             // chunks of four outputs per iteration of the rerun kernel's phase-3 loop
 #endif

@@ -39,8 +39,9 @@ struct RerunCfg {
     static constexpr int SCRATCH_BYTES = 2 * S * 8 * 2;
     static constexpr int WARP_BYTES = RING_BYTES + SCRATCH_BYTES;
     static constexpr int SMEM_WARPS = (232448 - 1024) / (WARP_BYTES + NBUF * NSTEP * 8);
-    // registers (cuobjdump -res-usage): ~144 (K <= 2), ~180 (K = 3), ~235 (K = 4); 12 warps allow 168, 8 allow 255
-    static constexpr int REG_WARPS  = (K <= 2) ? CBL_RR_WARPS : (K == 3 ? CBL_RR_WARPS3 : 8);
+    // registers (cuobjdump -res-usage): 113-118 (K <= 2), 156 (K = 3), 200 (K = 4) unconstrained; 12 warps allow 168,
+    // which K = 4 also fits without spilling (sweep 27: 4.85 -> 4.31 ms); CF32 input is limited to 7 warps by shared memory
+    static constexpr int REG_WARPS  = (K <= 2) ? CBL_RR_WARPS : (K == 3 ? CBL_RR_WARPS3 : CBL_RR_WARPS4);
     static constexpr int WPC = SMEM_WARPS < REG_WARPS ? SMEM_WARPS : REG_WARPS;
     static_assert(WPC >= 1, "a warp's buffers do not fit shared memory");
     static_assert(LT % 32 == 0 && (D == 1 || D == 2), "phase 3 works in groups of 8 or 16 samples: whole chunks of 4 kept outputs");
