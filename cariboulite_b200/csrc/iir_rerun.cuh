@@ -392,6 +392,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 #pragma unroll
                     for (int i = 0; i < PP; i++) q[i] = row_piece(tile_u32 + (uint32_t)(p0 >> 3) * 4096u, (p0 & 7) + i);
                 };
+                const bool fast_f32 = P.out_mode == OUT_F32 && P.out_vec != 0;
                 uint4 qn[PP];
                 chunk_pieces(0, qn);
 #pragma unroll (kRerunP3Unroll)
@@ -419,7 +420,13 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                             }
                         }
                     }
-                    store_out4(P, o, yi, yq);
+                    if (fast_f32) {      // plain CF32 into an aligned buffer: one test instead of the format switch
+                        stg_cf32x4(reinterpret_cast<float2*>(P.out) + o, make_float2((float)yi[0], (float)yq[0]),
+                                   make_float2((float)yi[1], (float)yq[1]), make_float2((float)yi[2], (float)yq[2]),
+                                   make_float2((float)yi[3], (float)yq[3]));
+                    } else {
+                        store_out4(P, o, yi, yq);
+                    }
                     o += 4;
                 }
             }
