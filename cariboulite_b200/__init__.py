@@ -54,6 +54,20 @@ class UnpackOut(C.Structure):
                 ("sync_idx", C.c_void_p), ("sync_cap", C.c_size_t)]
 
 
+class StreamResult(C.Structure):
+    _fields_ = [("n_samples", C.c_int64), ("n_filtered", C.c_int64), ("first_bad_chunk", C.c_int32),
+                ("n_misaligned_chunks", C.c_int32)]
+
+
+def MEM_IO(mem_in, mem_out):
+    """CARIBOU_CUDA_MEM_IO: different memory kinds for the input bytes and the output arrays of unpack_submit."""
+    return 0x100 | (mem_in & 0xF) | ((mem_out & 0xF) << 4)
+
+
+SHARD_ID_BYTES = 128
+SHARD_ALLGATHER, SHARD_CHAIN = 0, 1
+
+
 class Result(C.Structure):
     _fields_ = [("n_samples", C.c_int64), ("n_samples_b", C.c_int64), ("n_filtered", C.c_int64),
                 ("n_invalid", C.c_uint64), ("n_sync", C.c_uint64), ("first_bad_chunk", C.c_int32),
@@ -124,6 +138,18 @@ def lib():
         "caribou_cuda_rxstream_mtu": (sz, [vp]),
         "caribou_cuda_rxstream_read": (i, [vp, vp, sz, C.c_long]),
         "caribou_cuda_pump": (i64, [vp, i, i, i, sz, i64]),
+        "caribou_cuda_stream_results": (i, [vp, vp]),
+        "caribou_cuda_radio_read_cf32": (i, [vp, i, vp, vp, sz]),
+        "caribou_cuda_shard_unique_id": (i, [vp]),
+        "caribou_cuda_shard_init": (i, [vp, i, i, vp]),
+        "caribou_cuda_shard_attach_comm": (i, [vp, i, i, vp]),
+        "caribou_cuda_shard_set_mode": (i, [vp, i]),
+        "caribou_cuda_shard_submit": (i, [vp, i, vp, sz, sz, vp, sz]),
+        "caribou_cuda_shard_begin": (i, [vp, i, vp, sz, sz, vp, sz]),
+        "caribou_cuda_shard_gather_buffer": (vp, [vp, C.POINTER(sz)]),
+        "caribou_cuda_shard_finish": (i, [vp]),
+        "caribou_cuda_shard_exchange_local": (i, [C.POINTER(vp), i]),
+        "caribou_cuda_shard_profile": (i, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)
@@ -150,6 +176,11 @@ EXPORTED_SYMBOLS = [
     "caribou_cuda_ring_reset", "caribou_cuda_ring_size", "caribou_cuda_ring_capacity", "caribou_cuda_ring_dropped",
     "caribou_cuda_async_open", "caribou_cuda_async_activate", "caribou_cuda_async_read", "caribou_cuda_async_idle",
     "caribou_cuda_async_ring", "caribou_cuda_async_close",
+    "caribou_cuda_stream_results", "caribou_cuda_radio_read_cf32",
+    "caribou_cuda_shard_unique_id", "caribou_cuda_shard_init", "caribou_cuda_shard_attach_comm",
+    "caribou_cuda_shard_set_mode", "caribou_cuda_shard_submit", "caribou_cuda_shard_begin",
+    "caribou_cuda_shard_gather_buffer", "caribou_cuda_shard_finish", "caribou_cuda_shard_exchange_local",
+    "caribou_cuda_shard_profile",
 ]
 
 
@@ -268,6 +299,40 @@ class Context:
             raise CaribouCudaError(last_error())
         return ret, r
 
+    def stream_results(self):
+        """Per-capture results of the last rx_submit (waits for the context)."""
+        arr = (StreamResult * self.n_streams)()
+        self._check(lib().caribou_cuda_stream_results(self.h, C.cast(arr, C.c_void_p)))
+        return list(arr)
+
+    # -- multi-GPU time sharding, hand-off on the device (SURVEY 8e row 2)
+    def shard_init(self, rank, world, unique_id=None):
+        """unique_id: the 128 bytes of shard_unique_id() from rank 0 (ncclCommInitRank inside the library), or None:
+        no communicator - move the end vectors yourself between shard_begin and shard_finish."""
+        buf = None
+        if unique_id is not None:
+            assert len(unique_id) == SHARD_ID_BYTES
+            buf = C.create_string_buffer(bytes(unique_id), SHARD_ID_BYTES)
+        return self._check(lib().caribou_cuda_shard_init(self.h, rank, world, C.cast(buf, C.c_void_p) if buf is not None else None))
+
+    def shard_set_mode(self, mode):
+        return self._check(lib().caribou_cuda_shard_set_mode(self.h, mode))
+
+    def shard_submit(self, in_kind, x, n_samples, out, in_stride=0, out_stride=0):
+        return self._check(lib().caribou_cuda_shard_submit(self.h, in_kind, _ptr(x), n_samples, in_stride, _ptr(out), out_stride))
+
+    def shard_begin(self, in_kind, x, n_samples, out, in_stride=0, out_stride=0):
+        return self._check(lib().caribou_cuda_shard_begin(self.h, in_kind, _ptr(x), n_samples, in_stride, _ptr(out), out_stride))
+
+    def shard_finish(self):
+        return self._check(lib().caribou_cuda_shard_finish(self.h))
+
+    def shard_profile(self):
+        """(pass-1 ms, hand-off + fix-up ms) of the last sharded call; needs set_profiling(True)."""
+        a, b = C.c_float(0), C.c_float(0)
+        self._check(lib().caribou_cuda_shard_profile(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     # -- kernel (a)
     def unpack_submit(self, raw, nbytes=None, stride_bytes=0, cs16=None, meta=None, cf32=None, cs16_b=None,
                       meta_b=None, cf32_b=None, invalid_idx=None, sync_idx=None, mem=None):
@@ -350,6 +415,33 @@ class Context:
         if mem is None:
             mem = MEM_HOST if isinstance(samples, np.ndarray) else MEM_DEVICE
         return self._check(lib().caribou_cuda_tx_pack_submit(self.h, in_format, _ptr(samples), n, mem, _ptr(words)))
+
+
+def shard_unique_id():
+    """ncclGetUniqueId through the library (rank 0 calls it and ships the bytes to the other ranks)."""
+    buf = C.create_string_buffer(SHARD_ID_BYTES)
+    if lib().caribou_cuda_shard_unique_id(C.cast(buf, C.c_void_p)) != OK:
+        raise CaribouCudaError(last_error())
+    return buf.raw
+
+
+def shard_exchange_local(contexts):
+    """The hand-off between `world` contexts of this process (between shard_begin and shard_finish of all of them)."""
+    arr = (C.c_void_p * len(contexts))(*[c.h for c in contexts])
+    if lib().caribou_cuda_shard_exchange_local(arr, len(contexts)) != OK:
+        raise CaribouCudaError(last_error())
+
+
+def tone_tables():
+    """The 800-entry tone tables of the synthetic SMI word generator: one period of
+    round(3000 cos(2 pi 5e3 n / 4e6) + 800 cos(2 pi 1e6 n / 4e6)) for the I rail and the same with sin for the
+    Q rail (5 kHz repeats every 800 samples at fs = 4 MHz, 1 MHz every 4).  caribou_cuda_synth_words takes them
+    from the host so that the device generator needs no transcendentals; tests/test_abi.py checks them against
+    the CPU generator's own tables."""
+    n = np.arange(800, dtype=np.float64)
+    ti = np.round(3000.0 * np.cos(2 * np.pi * n / 800.0) + 800.0 * np.cos(2 * np.pi * n / 4.0))
+    tq = np.round(3000.0 * np.sin(2 * np.pi * n / 800.0) + 800.0 * np.sin(2 * np.pi * n / 4.0))
+    return ti.astype(np.int16), tq.astype(np.int16)
 
 
 def build(force=False):

@@ -41,6 +41,21 @@ void DevBuf::release()
     if (p) cudaFree(p);
     p = nullptr; cap = 0;
 }
+bool HostBuf::reserve(size_t n)
+{
+    if (n <= cap) return true;
+    if (p) cudaFreeHost(p);
+    p = nullptr; cap = 0;
+    const size_t want = (n + 65535) & ~size_t(65535);
+    if (!cuda_ok(cudaMallocHost(&p, want), "cudaMallocHost")) return false;
+    cap = want;
+    return true;
+}
+void HostBuf::release()
+{
+    if (p) cudaFreeHost(p);
+    p = nullptr; cap = 0;
+}
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda needed)
 typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -113,16 +128,19 @@ static double scale_of(const caribou_cuda_ctx* c, int in_kind)
 }
 // The kernels filter the raw sample values and fold the input scale into the output gain (exact: a power
 // of two).  If the input kind of a stream changes mid-life, its state is rescaled to the new raw units.
-static int ensure_scale(caribou_cuda_ctx* c, int in_kind)
+int ensure_scale(caribou_cuda_ctx* c, int in_kind)
 {
     const double sc = scale_of(c, in_kind);
     if (sc == c->in_scale) return CARIBOU_CUDA_OK;
+    if (resolve_queue(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     const size_t n = (size_t)c->cfg.n_streams * 2 * c->plan.S;
     std::vector<double> st(n);
+    // copies ordered on the context's (non-blocking) stream, then waited for: the host vector is pageable
+    CBL_CHECK(cudaMemcpyAsync(st.data(), c->d_state, n * 8, cudaMemcpyDeviceToHost, c->stream));
     CBL_CHECK(cudaStreamSynchronize(c->stream));
-    CBL_CHECK(cudaMemcpy(st.data(), c->d_state, n * 8, cudaMemcpyDeviceToHost));
     for (double& v : st) v *= c->in_scale / sc;
-    CBL_CHECK(cudaMemcpy(c->d_state, st.data(), n * 8, cudaMemcpyHostToDevice));
+    CBL_CHECK(cudaMemcpyAsync(c->d_state, st.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
     c->in_scale = sc;
     return CARIBOU_CUDA_OK;
 }
@@ -137,13 +155,13 @@ static void prof_mark(caribou_cuda_ctx* c, int which)
 }
 
 // ------------------------------------------------------------------ the IIR launch sequence
-// Filters n samples per stream that sit in device memory.  `state_in_dev` is the state each stream starts
-// from (kernel coordinates); when commit is set the end state is written back to ctx->d_state.
-// max_tiles > 0 limits the launch to the first max_tiles tiles of every stream (multi-GPU fix-up).
-static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t in_stride,
-                   void* d_out, size_t out_stride, const int32_t* gate, bool commit, uint32_t max_tiles)
+// Filters n samples per stream that sit in device memory (declaration and contract: ctx.h).
+int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t in_stride,
+            void* d_out, size_t out_stride, const int32_t* gate, uint32_t gate_stride, bool commit, uint32_t max_tiles,
+            double* state)
 {
     const FilterPlan& P = c->plan;
+    if (!state) state = c->d_state;
     const uint32_t ns = c->win_cnt;                               // streams of this launch (a window of the batch)
     const size_t st_off = (size_t)c->win0 * 2 * P.S;             // their filter states
     const int LT = P.LT;
@@ -189,11 +207,12 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
         p.desc_agg = c->desc_agg.as<double>();
         p.desc_incl = c->desc_incl.as<double>();
         p.ticket = c->d_ticket;
-        p.state_in = c->d_state + st_off;
+        p.state_in = state + st_off;
         p.state_out = c->d_state_next + st_off;
         p.out = d_out;
         p.out_stride = out_stride;
         p.gate = gate;
+        p.gate_stride = gate_stride;
         // (0x413 << 21) | sign bit of the 13-bit field at bits 13:1;  (0x414 << 21) | sign bit of the int16
         p.inj_mul = 1u << 31;
         p.inj_xor = in_kind == IN_WORDS ? 0x82602000u : 0x82808000u;
@@ -228,7 +247,7 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
         if (e != 0) { cuda_ok((cudaError_t)e, "iir_scan_kernel launch"); return CARIBOU_CUDA_ERR; }
         c->launches++;
         if (p.write_state) {
-            launch_commit_state(c->d_state + st_off, c->d_state_next + st_off, (size_t)ns * 2 * P.S, gate, c->stream);
+            launch_commit_state(state + st_off, c->d_state_next + st_off, ns, (size_t)2 * P.S, gate, gate_stride, c->stream);
             c->launches++;
         }
     }
@@ -242,8 +261,9 @@ static int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n,
         t.in_kind = in_kind; t.layout = layout; t.out_mode = c->out_mode; t.K = P.K; t.D = P.D; t.par = P.par ? 1 : 0;
         for (int k = 0; k < P.K; k++) { t.a1[k] = T.a1[k]; t.a2[k] = T.a2[k]; t.c1[k] = T.c1[k]; t.c2[k] = T.c2[k]; }
         t.gain = T.gain;
-        t.state = c->d_state + st_off;
+        t.state = state + st_off;
         t.gate = gate;
+        t.gate_stride = gate_stride;
         launch_iir_tail(t, c->stream);
         c->launches++;
     }
@@ -278,7 +298,7 @@ static SubGeom sub_geom(const caribou_cuda_ctx* c, const void* d_bytes, size_t n
     return g;
 }
 
-static int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes)
+int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes, bool with_gates)
 {
     // d_bytes points at the first stream of the current window (c->win0, c->win_cnt)
     const uint32_t ns_all = (uint32_t)c->cfg.n_streams, ns = c->win_cnt, w0 = c->win0;
@@ -289,6 +309,7 @@ static int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nby
     // first_bad <- INT_MAX (0x7f7f7f7f is large enough) for the window; counters <- 0 at the first window
     CBL_CHECK(cudaMemsetAsync(c->d_first_bad + (size_t)w0 * 2, 0x7f, (size_t)ns * 2 * 4, c->stream));
     if (w0 == 0) CBL_CHECK(cudaMemsetAsync(c->d_counters, 0, sizeof(Counters), c->stream));
+    if (with_gates) CBL_CHECK(cudaMemsetAsync(c->d_sflags + 2 * (size_t)ns_all + w0, 0, (size_t)ns * 4, c->stream));
     for (int s = 0; s < nsub; s++) {
         const SubGeom g = sub_geom(c, d_bytes, nbytes, s);
         OffsetsParams p;
@@ -303,6 +324,11 @@ static int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nby
         p.first_bad_stride = 2;
         p.n_misaligned = &c->d_counters->n_misaligned;
         p.any_misaligned = &c->d_counters->any_misaligned;
+        p.gate = with_gates ? c->d_sflags + w0 : nullptr;
+        p.gate_seq = with_gates ? c->d_sflags + ns_all + w0 : nullptr;
+        p.nmis = with_gates ? c->d_sflags + 2 * (size_t)ns_all + w0 : nullptr;
+        p.seq = (int32_t)c->queue.size();
+        p.lost = c->d_sflags + 3 * (size_t)ns_all;
         launch_find_offsets(p, c->stream);
         if (g.n_chunks) c->launches++;
     }
@@ -311,10 +337,12 @@ static int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nby
 }
 
 // unpack kernel for every stream of the batch; all pointers are device pointers
+// (streams [c->win0, c->win0 + c->win_cnt) of the batch; d_bytes and the outputs point at stream 0)
 static int run_unpack(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes,
                       const caribou_cuda_unpack_out& o, uint32_t max_chunks, size_t out_stride_samples)
 {
     const uint32_t ns = (uint32_t)c->cfg.n_streams;
+    const uint32_t st0 = c->win0, st1 = c->win0 + c->win_cnt;
     const int nsub = n_subs_of(c);
     const uint64_t n_raw_words = (nbytes + 3) / 4;
     const uint32_t n_tiles = (uint32_t)((n_raw_words + kUnpackTileWords - 1) / kUnpackTileWords);
@@ -322,13 +350,17 @@ static int run_unpack(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, s
     const bool want_flags = true;
     if (n_raw_words > (1ull << 31)) { set_error("unpack: at most 2^31 words per stream and submit"); return CARIBOU_CUDA_ERR; }
     // per-tile counts, their scan, work list (+ its length); running totals per stream launch
+    if (n_raw_words * ns > (1ull << 32) && (o.invalid_idx || o.sync_idx)) {
+        set_error("unpack: index lists are 32-bit - at most 2^32 words per batch when they are requested");
+        return CARIBOU_CUDA_ERR;
+    }
     if (!c->desc_inv.reserve((size_t)n_tiles * 20 + 16) || !c->desc_syn.reserve(((size_t)ns + 1) * 16)) return CARIBOU_CUDA_ERR;
     // running (n_invalid, n_sync) after each stream's launch: slot s is read by launch s, slot s + 1 written by it
     uint64_t* run_totals = c->desc_syn.as<uint64_t>();
     CBL_CHECK(cudaMemsetAsync(run_totals, 0, 16, c->stream));
     const bool prof = c->profiling && !c->has_filter;
     if (prof) prof_mark(c, 0);
-    for (uint32_t st = 0; st < ns; st++) {
+    for (uint32_t st = st0; st < st1; st++) {
         UnpackParams p;
         memset(&p, 0, sizeof(p));
         const uint8_t* sb = reinterpret_cast<const uint8_t*>(d_bytes) + (size_t)st * stride_bytes;
@@ -363,22 +395,23 @@ static int run_unpack(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, s
         p.tile_offsets = p.tile_counts + n_tiles;
         p.work = reinterpret_cast<uint32_t*>(p.tile_offsets + n_tiles);
         p.n_work = p.work + n_tiles;
-        p.totals_in = run_totals + 2 * (size_t)st;
-        p.totals_out = run_totals + 2 * (size_t)st + 2;
+        p.totals_in = run_totals + 2 * (size_t)(st - st0);
+        p.totals_out = run_totals + 2 * (size_t)(st - st0) + 2;
         p.n_tiles = n_tiles;
         CBL_CHECK(cudaMemsetAsync(c->desc_inv.p, 0, (size_t)n_tiles * 8, c->stream));
         c->launches += (uint64_t)launch_unpack(p, c->num_sms, c->stream);
     }
     if (prof) prof_mark(c, 1);
-    CBL_CHECK(cudaMemcpyAsync(c->d_counters->totals, run_totals + 2 * (size_t)ns, 16, cudaMemcpyDeviceToDevice, c->stream));
+    CBL_CHECK(cudaMemcpyAsync(c->d_counters->totals, run_totals + 2 * (size_t)(st1 - st0), 16, cudaMemcpyDeviceToDevice, c->stream));
     CBL_CHECK(cudaGetLastError());
     return CARIBOU_CUDA_OK;
 }
 
-static int mirror_counters(caribou_cuda_ctx* c)
+int mirror_counters(caribou_cuda_ctx* c)
 {
     CBL_CHECK(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     CBL_CHECK(cudaMemcpyAsync(c->h_first_bad, c->d_first_bad, (size_t)c->cfg.n_streams * 2 * 4, cudaMemcpyDeviceToHost, c->stream));
+    CBL_CHECK(cudaMemcpyAsync(c->h_sflags, c->d_sflags, ((size_t)c->cfg.n_streams * 3 + 4) * 4, cudaMemcpyDeviceToHost, c->stream));
     return CARIBOU_CUDA_OK;
 }
 
@@ -436,7 +469,13 @@ caribou_cuda_ctx* caribou_cuda_create(const caribou_cuda_config* cfg_in)
         !cuda_ok(cudaMalloc(&c->d_counters, sizeof(Counters)), "cudaMalloc") ||
         !cuda_ok(cudaMalloc(&c->d_first_bad, ns * 2 * 4), "cudaMalloc") ||
         !cuda_ok(cudaMallocHost(&c->h_counters, sizeof(Counters)), "cudaMallocHost") ||
-        !cuda_ok(cudaMallocHost(&c->h_first_bad, ns * 2 * 4), "cudaMallocHost")) return fail();
+        !cuda_ok(cudaMallocHost(&c->h_first_bad, ns * 2 * 4), "cudaMallocHost") ||
+        !cuda_ok(cudaMalloc(&c->d_sflags, (ns * 3 + 4) * 4), "cudaMalloc") ||
+        !cuda_ok(cudaMallocHost(&c->h_sflags, (ns * 3 + 4) * 4), "cudaMallocHost")) return fail();
+    cudaMemset(c->d_sflags, 0, (ns * 3 + 4) * 4);
+    cudaMemset(c->d_sflags + ns, 0x7f, ns * 4);
+    memset(c->h_sflags, 0, (ns * 3 + 4) * 4);
+    c->sres.resize(ns);
     cudaMemset(c->d_ticket, 0, 256);
     cudaMemset(c->d_counters, 0, sizeof(Counters));
     cudaMemset(c->d_first_bad, 0x7f, ns * 2 * 4);
@@ -451,8 +490,7 @@ caribou_cuda_ctx* caribou_cuda_create(const caribou_cuda_config* cfg_in)
         if (!cuda_ok(cudaMalloc(&c->d_plane, P.plane.size() * 8), "cudaMalloc") ||
             !cuda_ok(cudaMalloc(&c->d_mtile_pow, P.mtile_pow.size() * 8), "cudaMalloc") ||
             !cuda_ok(cudaMalloc(&c->d_state, ns * 2 * P.S * 8), "cudaMalloc") ||
-            !cuda_ok(cudaMalloc(&c->d_state_next, ns * 2 * P.S * 8), "cudaMalloc") ||
-            !cuda_ok(cudaMalloc(&c->d_state_backup, ns * 2 * P.S * 8), "cudaMalloc")) return fail();
+            !cuda_ok(cudaMalloc(&c->d_state_next, ns * 2 * P.S * 8), "cudaMalloc")) return fail();
         cudaMemcpy(c->d_plane, P.plane.data(), P.plane.size() * 8, cudaMemcpyHostToDevice);
         cudaMemcpy(c->d_mtile_pow, P.mtile_pow.data(), P.mtile_pow.size() * 8, cudaMemcpyHostToDevice);
         cudaMemset(c->d_state, 0, ns * 2 * P.S * 8);
@@ -468,6 +506,7 @@ void caribou_cuda_destroy(caribou_cuda_ctx* c)
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->shard) { shard_release(c->shard); c->shard = nullptr; }
     DevBuf* bufs[] = {&c->desc_agg, &c->desc_incl, &c->offs, &c->desc_inv, &c->desc_syn, &c->stage_in,
                       &c->stage_cs16[0], &c->stage_cs16[1], &c->stage_meta[0], &c->stage_meta[1], &c->stage_cf32[0],
                       &c->stage_cf32[1], &c->stage_filt, &c->stage_inv, &c->stage_syn, &c->scratch_cs16};
@@ -476,7 +515,6 @@ void caribou_cuda_destroy(caribou_cuda_ctx* c)
     if (c->d_mtile_pow) cudaFree(c->d_mtile_pow);
     if (c->d_state) cudaFree(c->d_state);
     if (c->d_state_next) cudaFree(c->d_state_next);
-    if (c->d_state_backup) cudaFree(c->d_state_backup);
     for (cudaEvent_t e : c->pipe_ev) if (e) cudaEventDestroy(e);
     if (c->h2d_stream) cudaStreamDestroy(c->h2d_stream);
     if (c->d2h_stream) cudaStreamDestroy(c->d2h_stream);
@@ -486,6 +524,9 @@ void caribou_cuda_destroy(caribou_cuda_ctx* c)
     if (c->d_tone) cudaFree(c->d_tone);
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->h_first_bad) cudaFreeHost(c->h_first_bad);
+    if (c->d_sflags) cudaFree(c->d_sflags);
+    if (c->h_sflags) cudaFreeHost(c->h_sflags);
+    c->h_bounce.release();
     for (cudaEvent_t e : c->prof_ev) if (e) cudaEventDestroy(e);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -541,7 +582,7 @@ int caribou_cuda_butter_lowpass(int order, double fs, double fc, double* sos)
 static int unpack_device(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes,
                          const caribou_cuda_unpack_out& o, size_t out_stride_samples)
 {
-    const int mc = run_find_offsets(c, d_bytes, nbytes, stride_bytes);
+    const int mc = run_find_offsets(c, d_bytes, nbytes, stride_bytes, false);
     if (mc < 0) return mc;
     return run_unpack(c, d_bytes, nbytes, stride_bytes, o, (uint32_t)mc, out_stride_samples);
 }
@@ -554,29 +595,41 @@ int caribou_cuda_unpack_submit(caribou_cuda_ctx* c, const void* bytes, size_t nb
     const size_t ns = (size_t)c->cfg.n_streams;
     if (ns > 1 && stream_stride_bytes < nbytes) { set_error("stream stride smaller than the stream"); return CARIBOU_CUDA_ERR; }
     if (ns == 1) stream_stride_bytes = (nbytes + 15) & ~size_t(15);
-    c->pending.active = false;
+    if (resolve_queue(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     c->last_is_unpack = true;
+    c->last_is_shard = false;
+    c->sres_valid = false;
     c->last_nbytes = nbytes;
     c->last_n_filtered = 0;
     const int nsub = n_subs_of(c);
     // per-sub-stream output capacity in samples
     size_t sub_samples[2];
     for (int s = 0; s < nsub; s++) sub_samples[s] = (size_t)(sub_geom(c, bytes, nbytes, s).sv.nbytes / 4);
-    if (mem == CARIBOU_CUDA_MEM_DEVICE) {
+    // one kind for everything, or CARIBOU_CUDA_MEM_IO(in, out)
+    const int in_mem = (mem & 0x100) ? (mem & 0xF) : mem, out_mem = (mem & 0x100) ? ((mem >> 4) & 0xF) : mem;
+    if (in_mem < 0 || in_mem > 2 || out_mem < 0 || out_mem > 2) { set_error("bad memory kind"); return CARIBOU_CUDA_ERR; }
+    if (in_mem == CARIBOU_CUDA_MEM_DEVICE && out_mem == CARIBOU_CUDA_MEM_DEVICE) {
         if (ns > 1 && (stream_stride_bytes % 16)) { set_error("stream stride must be a multiple of 16 bytes"); return CARIBOU_CUDA_ERR; }
         const size_t ostride = (sub_samples[0] + 3) & ~size_t(3);
         if (unpack_device(c, bytes, nbytes, stream_stride_bytes, *out, ns > 1 ? ostride : 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
         return mirror_counters(c);
     }
-    // host memory: stage through device buffers (single stream only)
+    // host memory: stage through device buffers (single stream only).  The input and the outputs may be of
+    // different kinds (CARIBOU_CUDA_MEM_IO): the shims read(2) into a page-locked segment buffer and deliver
+    // into the caller's pageable arrays.
     if (ns != 1) { set_error("host-memory unpack supports n_streams == 1"); return CARIBOU_CUDA_ERR; }
-    if (!c->stage_in.reserve(nbytes + 64)) return CARIBOU_CUDA_ERR;
-    CBL_CHECK(cudaMemcpyAsync(c->stage_in.p, bytes, nbytes, cudaMemcpyHostToDevice, c->stream));
-    const int mc = run_find_offsets(c, c->stage_in.p, nbytes, stream_stride_bytes);
+    const void* d_src = bytes;
+    if (in_mem != CARIBOU_CUDA_MEM_DEVICE) {
+        if (!c->stage_in.reserve(nbytes + 64)) return CARIBOU_CUDA_ERR;
+        CBL_CHECK(cudaMemcpyAsync(c->stage_in.p, bytes, nbytes, cudaMemcpyHostToDevice, c->stream));
+        d_src = c->stage_in.p;
+    }
+    if (out_mem == CARIBOU_CUDA_MEM_DEVICE) {        // host bytes, device arrays: nothing comes back but the counters
+        if (unpack_device(c, d_src, nbytes, stream_stride_bytes, *out, 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        return mirror_counters(c);
+    }
+    const int mc = run_find_offsets(c, d_src, nbytes, stream_stride_bytes, false);
     if (mc < 0) return mc;
-    if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
-    CBL_CHECK(cudaStreamSynchronize(c->stream));   // need the alignment verdict to know which slots get written
-    const bool clean = c->h_counters->any_misaligned == 0;
     caribou_cuda_unpack_out d = *out;
     void* hcs16[2] = {out->cs16, out->cs16_b};
     void* hmeta[2] = {out->meta, out->meta_b};
@@ -591,15 +644,87 @@ int caribou_cuda_unpack_submit(caribou_cuda_ctx* c, const void* bytes, size_t nb
         if (hcs16[s]) { if (!c->stage_cs16[s].reserve(n * 4 + 64)) return CARIBOU_CUDA_ERR; *dcs16[s] = c->stage_cs16[s].p; }
         if (hmeta[s]) { if (!c->stage_meta[s].reserve(n + 64)) return CARIBOU_CUDA_ERR; *dmeta[s] = c->stage_meta[s].p; }
         if (hcf32[s]) { if (!c->stage_cf32[s].reserve(n * 8 + 64)) return CARIBOU_CUDA_ERR; *dcf32[s] = c->stage_cf32[s].p; }
-        if (!clean) {   // some slots stay untouched: start from the caller's buffer contents
+    }
+    if (out->invalid_idx && out->invalid_cap) { if (!c->stage_inv.reserve(out->invalid_cap * 4)) return CARIBOU_CUDA_ERR; d.invalid_idx = c->stage_inv.as<uint32_t>(); }
+    if (out->sync_idx && out->sync_cap) { if (!c->stage_syn.reserve(out->sync_cap * 4)) return CARIBOU_CUDA_ERR; d.sync_idx = c->stage_syn.as<uint32_t>(); }
+
+    if (out_mem == CARIBOU_CUDA_MEM_HOST) {
+        // ---- pageable outputs: everything is queued behind the alignment search without waiting for its verdict.
+        // The results come down into a page-locked bounce buffer together with the per-chunk offsets; after the
+        // one synchronisation the host copies them into the caller's arrays - all of them for an aligned capture,
+        // for a misaligned one exactly the slots the reference writes (the others keep the caller's bytes).
+        size_t off_cs16[2], off_meta[2], off_cf32[2], total = 0;
+        auto carve = [&](size_t bytes_) { const size_t o = total; total += (bytes_ + 63) & ~size_t(63); return o; };
+        for (int s = 0; s < nsub; s++) {
+            const size_t n = sub_samples[s];
+            off_cs16[s] = carve(hcs16[s] ? n * 4 : 0);
+            off_meta[s] = carve(hmeta[s] ? n : 0);
+            off_cf32[s] = carve(hcf32[s] ? n * 8 : 0);
+        }
+        const size_t n_offs = (size_t)nsub * std::max(mc, 1);
+        const size_t off_offs = carve(n_offs * 4);
+        if (!c->h_bounce.reserve(total)) return CARIBOU_CUDA_ERR;
+        uint8_t* hb = c->h_bounce.as<uint8_t>();
+        if (run_unpack(c, d_src, nbytes, stream_stride_bytes, d, (uint32_t)mc, 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        if (mc > 0) CBL_CHECK(cudaMemcpyAsync(hb + off_offs, c->offs.p, n_offs * 4, cudaMemcpyDeviceToHost, c->stream));
+        for (int s = 0; s < nsub; s++) {
+            const size_t n = sub_samples[s];
+            if (hcs16[s] && n) CBL_CHECK(cudaMemcpyAsync(hb + off_cs16[s], *dcs16[s], n * 4, cudaMemcpyDeviceToHost, c->stream));
+            if (hmeta[s] && n) CBL_CHECK(cudaMemcpyAsync(hb + off_meta[s], *dmeta[s], n, cudaMemcpyDeviceToHost, c->stream));
+            if (hcf32[s] && n) CBL_CHECK(cudaMemcpyAsync(hb + off_cf32[s], *dcf32[s], n * 8, cudaMemcpyDeviceToHost, c->stream));
+        }
+        CBL_CHECK(cudaStreamSynchronize(c->stream));
+        const bool clean = c->h_counters->any_misaligned == 0;
+        const int32_t* h_offs = reinterpret_cast<const int32_t*>(hb + off_offs);
+        const size_t cb = c->cfg.chunk_bytes, spc = cb / 4;
+        for (int s = 0; s < nsub; s++) {
+            const size_t n = sub_samples[s];
+            if (clean) {
+                if (hcs16[s]) memcpy(hcs16[s], hb + off_cs16[s], n * 4);
+                if (hmeta[s]) memcpy(hmeta[s], hb + off_meta[s], n);
+                if (hcf32[s]) memcpy(hcf32[s], hb + off_cf32[s], n * 8);
+                continue;
+            }
+            const SubGeom g = sub_geom(c, bytes, nbytes, s);
+            const int32_t fb = c->h_first_bad[s];
+            for (uint32_t ch = 0; ch < g.n_chunks; ch++) {
+                if ((int64_t)ch >= (int64_t)fb) break;                        // caribou_smi.c:665-668: nothing after a lost sync
+                const uint64_t cstart = (uint64_t)ch * cb, rem = g.sv.nbytes - cstart;
+                const size_t len = (size_t)std::min<uint64_t>(rem, cb), nfull = len / 4;
+                const int32_t offs = h_offs[(size_t)s * mc + ch];
+                const size_t shorten = offs > 0 ? (size_t)offs / 4 + 1 : 0;     // caribou_smi.c:323
+                const size_t nvalid = nfull > shorten ? nfull - shorten : 0;
+                const size_t extra = (shorten > 0 && nvalid >= 2) ? 1 : 0;      // the extrapolated sample (:382-389), no meta
+                const size_t j0 = (size_t)ch * spc;
+                if (hcs16[s]) memcpy((uint8_t*)hcs16[s] + j0 * 4, hb + off_cs16[s] + j0 * 4, (nvalid + extra) * 4);
+                if (hmeta[s]) memcpy((uint8_t*)hmeta[s] + j0, hb + off_meta[s] + j0, nvalid);
+                if (hcf32[s]) memcpy((uint8_t*)hcf32[s] + j0 * 8, hb + off_cf32[s] + j0 * 8, (nvalid + extra) * 8);
+            }
+        }
+        const size_t ni = (size_t)std::min<uint64_t>(c->h_counters->totals[0], out->invalid_cap);
+        const size_t nsy = (size_t)std::min<uint64_t>(c->h_counters->totals[1], out->sync_cap);
+        if (out->invalid_idx && ni) CBL_CHECK(cudaMemcpyAsync(out->invalid_idx, d.invalid_idx, ni * 4, cudaMemcpyDeviceToHost, c->stream));
+        if (out->sync_idx && nsy) CBL_CHECK(cudaMemcpyAsync(out->sync_idx, d.sync_idx, nsy * 4, cudaMemcpyDeviceToHost, c->stream));
+        if ((out->invalid_idx && ni) || (out->sync_idx && nsy)) CBL_CHECK(cudaStreamSynchronize(c->stream));
+        return CARIBOU_CUDA_OK;
+    }
+
+    // ---- page-locked outputs: asynchronous copies straight into the caller's buffers.  Which slots get written is
+    // only known after the alignment search, so its verdict is waited for; a misaligned capture starts from the
+    // caller's buffer contents so that untouched slots come back unchanged.
+    if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
+    const bool clean = c->h_counters->any_misaligned == 0;
+    if (!clean) {
+        for (int s = 0; s < nsub; s++) {
+            const size_t n = sub_samples[s];
             if (hcs16[s]) CBL_CHECK(cudaMemcpyAsync(*dcs16[s], hcs16[s], n * 4, cudaMemcpyHostToDevice, c->stream));
             if (hmeta[s]) CBL_CHECK(cudaMemcpyAsync(*dmeta[s], hmeta[s], n, cudaMemcpyHostToDevice, c->stream));
             if (hcf32[s]) CBL_CHECK(cudaMemcpyAsync(*dcf32[s], hcf32[s], n * 8, cudaMemcpyHostToDevice, c->stream));
         }
     }
-    if (out->invalid_idx && out->invalid_cap) { if (!c->stage_inv.reserve(out->invalid_cap * 4)) return CARIBOU_CUDA_ERR; d.invalid_idx = c->stage_inv.as<uint32_t>(); }
-    if (out->sync_idx && out->sync_cap) { if (!c->stage_syn.reserve(out->sync_cap * 4)) return CARIBOU_CUDA_ERR; d.sync_idx = c->stage_syn.as<uint32_t>(); }
-    if (run_unpack(c, c->stage_in.p, nbytes, stream_stride_bytes, d, (uint32_t)mc, 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (run_unpack(c, d_src, nbytes, stream_stride_bytes, d, (uint32_t)mc, 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     for (int s = 0; s < nsub; s++) {
         const size_t n = sub_samples[s];
@@ -607,12 +732,13 @@ int caribou_cuda_unpack_submit(caribou_cuda_ctx* c, const void* bytes, size_t nb
         if (hmeta[s]) CBL_CHECK(cudaMemcpyAsync(hmeta[s], *dmeta[s], n, cudaMemcpyDeviceToHost, c->stream));
         if (hcf32[s]) CBL_CHECK(cudaMemcpyAsync(hcf32[s], *dcf32[s], n * 8, cudaMemcpyDeviceToHost, c->stream));
     }
-    if (mem == CARIBOU_CUDA_MEM_HOST || out->invalid_idx || out->sync_idx) {
+    if (out->invalid_idx || out->sync_idx) {
         CBL_CHECK(cudaStreamSynchronize(c->stream));
         const size_t ni = (size_t)std::min<uint64_t>(c->h_counters->totals[0], out->invalid_cap);
         const size_t nsy = (size_t)std::min<uint64_t>(c->h_counters->totals[1], out->sync_cap);
-        if (out->invalid_idx && ni) CBL_CHECK(cudaMemcpy(out->invalid_idx, d.invalid_idx, ni * 4, cudaMemcpyDeviceToHost));
-        if (out->sync_idx && nsy) CBL_CHECK(cudaMemcpy(out->sync_idx, d.sync_idx, nsy * 4, cudaMemcpyDeviceToHost));
+        if (out->invalid_idx && ni) CBL_CHECK(cudaMemcpyAsync(out->invalid_idx, d.invalid_idx, ni * 4, cudaMemcpyDeviceToHost, c->stream));
+        if (out->sync_idx && nsy) CBL_CHECK(cudaMemcpyAsync(out->sync_idx, d.sync_idx, nsy * 4, cudaMemcpyDeviceToHost, c->stream));
+        CBL_CHECK(cudaStreamSynchronize(c->stream));
     }
     return CARIBOU_CUDA_OK;
 }
@@ -625,6 +751,31 @@ static int check_filter_args(caribou_cuda_ctx* c, size_t n)
     return CARIBOU_CUDA_OK;
 }
 
+}  // extern "C"
+
+namespace cbl {
+// single-stream filter pass on device memory, skipped on the device when *gate != 0 (compat.cu: a read that lost
+// word sync delivers nothing and must not advance the Stream's filters)
+int filter_device(caribou_cuda_ctx* c, int in_kind, const void* in, size_t n, void* out, const int32_t* gate)
+{
+    if (!c || !in || !out || c->cfg.n_streams != 1) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    CBL_CHECK(cudaSetDevice(c->device));
+    if (check_filter_args(c, n) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (resolve_queue(c) != CARIBOU_CUDA_OK || ensure_scale(c, in_kind) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    c->last_is_unpack = false;
+    c->last_is_shard = false;
+    c->sres_valid = false;
+    c->last_ret = (int64_t)n;
+    c->last_n_filtered = (int64_t)(n / c->plan.D);
+    if (n == 0) return CARIBOU_CUDA_OK;
+    if (run_iir(c, in_kind, in, n, (n + 3) & ~size_t(3), out, n / c->plan.D, gate, 0, true, 0, nullptr) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    c->pos += n;
+    return CARIBOU_CUDA_OK;
+}
+}  // namespace cbl
+
+extern "C" {
+
 int caribou_cuda_filter_submit(caribou_cuda_ctx* c, int in_kind, const void* in, size_t n, size_t in_stride,
                                int mem, void* out, size_t out_stride)
 {
@@ -635,21 +786,23 @@ int caribou_cuda_filter_submit(caribou_cuda_ctx* c, int in_kind, const void* in,
     const size_t ns = (size_t)c->cfg.n_streams;
     const size_t es = in_elem_bytes(in_kind);
     const size_t nout = n / c->plan.D;
-    c->pending.active = false;
+    if (resolve_queue(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     c->last_is_unpack = false;
+    c->last_is_shard = false;
+    c->sres_valid = false;
     c->last_ret = (int64_t)n;
     c->last_n_filtered = (int64_t)nout;
     if (n == 0) return CARIBOU_CUDA_OK;
     if (ns == 1) { in_stride = (n + 3) & ~size_t(3); out_stride = nout; }
     if (mem == CARIBOU_CUDA_MEM_DEVICE) {
-        if (run_iir(c, in_kind, in, n, in_stride, out, out_stride, nullptr, true, 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        if (run_iir(c, in_kind, in, n, in_stride, out, out_stride, nullptr, 0, true, 0, nullptr) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
         c->pos += n;
         return CARIBOU_CUDA_OK;
     }
     if (ns != 1) { set_error("host-memory filter supports n_streams == 1"); return CARIBOU_CUDA_ERR; }
     if (!c->stage_in.reserve(n * es + 64) || !c->stage_filt.reserve(nout * c->out_elem + 64)) return CARIBOU_CUDA_ERR;
     CBL_CHECK(cudaMemcpyAsync(c->stage_in.p, in, n * es, cudaMemcpyHostToDevice, c->stream));
-    if (run_iir(c, in_kind, c->stage_in.p, n, in_stride, c->stage_filt.p, out_stride, nullptr, true, 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (run_iir(c, in_kind, c->stage_in.p, n, in_stride, c->stage_filt.p, out_stride, nullptr, 0, true, 0, nullptr) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     CBL_CHECK(cudaMemcpyAsync(out, c->stage_filt.p, nout * c->out_elem, cudaMemcpyDeviceToHost, c->stream));
     c->pos += n;
     if (mem == CARIBOU_CUDA_MEM_HOST) CBL_CHECK(cudaStreamSynchronize(c->stream));
@@ -663,14 +816,15 @@ int caribou_cuda_filter_fixup(caribou_cuda_ctx* c, int in_kind, const void* in, 
     if (mem != CARIBOU_CUDA_MEM_DEVICE) { set_error("fix-up works on device memory"); return CARIBOU_CUDA_ERR; }
     CBL_CHECK(cudaSetDevice(c->device));
     if (check_filter_args(c, n) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (resolve_queue(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     if (ensure_scale(c, in_kind) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     const FilterPlan& P = c->plan;
     const size_t ns = (size_t)c->cfg.n_streams;
     if (ns == 1) { in_stride = (n + 3) & ~size_t(3); out_stride = n / P.D; }
     // the shard was filtered from zero state and left f in d_state; its true end state is M_shard s_in + f
     std::vector<double> f(ns * 2 * P.S), ker(ns * 2 * P.S), m((size_t)P.S * P.S);
+    CBL_CHECK(cudaMemcpyAsync(f.data(), c->d_state, f.size() * 8, cudaMemcpyDeviceToHost, c->stream));
     CBL_CHECK(cudaStreamSynchronize(c->stream));
-    CBL_CHECK(cudaMemcpy(f.data(), c->d_state, f.size() * 8, cudaMemcpyDeviceToHost));
     for (size_t s = 0; s < ns; s++) state_to_kernel(P, state_in + s * 2 * P.S, ker.data() + s * 2 * P.S);
     for (double& v : ker) v /= c->in_scale;
     plan_power_kernel(P, n, m.data());     // A^n in kernel coordinates
@@ -683,7 +837,8 @@ int caribou_cuda_filter_fixup(caribou_cuda_ctx* c, int in_kind, const void* in, 
                 end[s * 2 * P.S + r * P.S + i] = (double)acc;
             }
     // re-run the leading tiles from the true incoming state
-    CBL_CHECK(cudaMemcpy(c->d_state, ker.data(), ker.size() * 8, cudaMemcpyHostToDevice));
+    CBL_CHECK(cudaMemcpyAsync(c->d_state, ker.data(), ker.size() * 8, cudaMemcpyHostToDevice, c->stream));
+    CBL_CHECK(cudaStreamSynchronize(c->stream));       // `ker` is pageable: the copy has landed before it is reused
     const size_t fix = caribou_cuda_fixup_samples(c, n);
     const uint32_t tile_samples = 32u * (uint32_t)P.LT;
     uint32_t max_tiles = (uint32_t)((fix + tile_samples - 1) / tile_samples);
@@ -691,11 +846,11 @@ int caribou_cuda_filter_fixup(caribou_cuda_ctx* c, int in_kind, const void* in, 
     if (max_tiles == 0 || max_tiles >= tiles_ps) {
         // no useful contraction (or a short shard): filter the whole shard again from the true state;
         // the kernels then leave the true end state in d_state themselves
-        if (run_iir(c, in_kind, in, n, in_stride, out, out_stride, nullptr, true, 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        if (run_iir(c, in_kind, in, n, in_stride, out, out_stride, nullptr, 0, true, 0, nullptr) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
         CBL_CHECK(cudaStreamSynchronize(c->stream));
         return CARIBOU_CUDA_OK;
     }
-    if (run_iir(c, in_kind, in, n, in_stride, out, out_stride, nullptr, false, max_tiles) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (run_iir(c, in_kind, in, n, in_stride, out, out_stride, nullptr, 0, false, max_tiles, nullptr) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     CBL_CHECK(cudaMemcpyAsync(c->d_state, end.data(), end.size() * 8, cudaMemcpyHostToDevice, c->stream));
     CBL_CHECK(cudaStreamSynchronize(c->stream));
     return CARIBOU_CUDA_OK;
@@ -716,8 +871,12 @@ int caribou_cuda_shard_matrix(caribou_cuda_ctx* c, uint64_t n_samples, double* m
 }
 
 // ------------------------------------------------------------------ fused rx path
-static int rx_fallback(caribou_cuda_ctx* c);
-
+// Every capture of a batch is an independent read.  The fused kernel is launched optimistically for all of
+// them; the alignment search that runs just before it raises a per-capture gate (sticky until the queue is
+// resolved) for a capture with a misaligned or un-alignable chunk, and the fused kernel, the state commit and
+// the tail kernel skip exactly those captures.  Submits are queued; caribou_cuda_wait (or the next call that
+// needs a quiet context) redoes the gated captures - and only those - on the slow path for every queued
+// submit from the one that raised the gate on, in order, so their filter state advances as it would have.
 int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes, size_t stride_bytes, int mem,
                            const caribou_cuda_unpack_out* uo, void* filt_out, size_t filt_stride)
 {
@@ -727,27 +886,34 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
     const size_t n = nbytes / 4;
     if (check_filter_args(c, n) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     if (ensure_scale(c, IN_WORDS) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (c->queue.size() >= kMaxQueuedRx && resolve_queue(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     const FilterPlan& P = c->plan;
     const size_t ns = (size_t)c->cfg.n_streams;
     const size_t nout = n / P.D;
     if (ns == 1) { stride_bytes = (nbytes + 15) & ~size_t(15); filt_stride = nout; }
     if (stride_bytes % 16) { set_error("stream stride must be a multiple of 16 bytes"); return CARIBOU_CUDA_ERR; }
     c->last_is_unpack = false;
+    c->last_is_shard = false;
+    c->sres_valid = false;
     c->last_nbytes = nbytes;
     c->last_ret = (int64_t)n;
     c->last_n_filtered = (int64_t)nout;
-    c->pending.active = false;
     if (n == 0) return CARIBOU_CUDA_OK;
 
     const void* d_bytes = bytes;
     void* d_out = filt_out;
-    c->pipelined_last = false;
+    const int32_t* gates = c->d_sflags;
+    PendingRx q;
+    q.seq = (int32_t)c->queue.size();
+    q.bytes = bytes; q.nbytes = nbytes; q.stride = stride_bytes; q.mem = mem;
+    q.filt_out = filt_out; q.filt_stride = filt_stride;
     if (mem != CARIBOU_CUDA_MEM_DEVICE) {
         if (uo) { set_error("rx_submit with unpack outputs needs device memory"); return CARIBOU_CUDA_ERR; }
         if (ns > 1 && (stride_bytes < nbytes || filt_stride < nout)) { set_error("stream stride smaller than the stream"); return CARIBOU_CUDA_ERR; }
         if (!c->stage_in.reserve(ns * stride_bytes + 64) || !c->stage_filt.reserve(ns * filt_stride * c->out_elem + 64)) return CARIBOU_CUDA_ERR;
         d_bytes = c->stage_in.p;
         d_out = c->stage_filt.p;
+        q.d_bytes = d_bytes; q.d_out = d_out;
         if (mem == CARIBOU_CUDA_MEM_HOST_PINNED && ns >= 4) {
             // ---- pipelined: the batch goes through in groups of streams; group g+1 is on its way up while
             // group g is being filtered and group g-1 is on its way down (both copy engines and the SMs busy)
@@ -762,7 +928,6 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
             }
             cudaEvent_t ev_start = c->pipe_ev[2 * kGroups], ev_done = c->pipe_ev[2 * kGroups + 1];
             // the staging buffers may still be in use by the previous submit on the main stream
-            CBL_CHECK(cudaMemcpyAsync(c->d_state_backup, c->d_state, ns * 2 * P.S * 8, cudaMemcpyDeviceToDevice, c->stream));
             CBL_CHECK(cudaEventRecord(ev_start, c->stream));
             CBL_CHECK(cudaStreamWaitEvent(c->h2d_stream, ev_start, 0));
             CBL_CHECK(cudaStreamWaitEvent(c->d2h_stream, ev_start, 0));
@@ -778,10 +943,10 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
                 CBL_CHECK(cudaEventRecord(c->pipe_ev[2 * g], c->h2d_stream));
                 CBL_CHECK(cudaStreamWaitEvent(c->stream, c->pipe_ev[2 * g], 0));
                 c->win0 = (uint32_t)s0; c->win_cnt = (uint32_t)cnt;
-                const int mcg = run_find_offsets(c, db + s0 * stride_bytes, nbytes, stride_bytes);
+                const int mcg = run_find_offsets(c, db + s0 * stride_bytes, nbytes, stride_bytes, true);
                 if (mcg < 0) { rc = mcg; break; }
                 rc = run_iir(c, IN_WORDS, db + s0 * stride_bytes, n, stride_bytes / 4, dob + s0 * filt_stride * c->out_elem, filt_stride,
-                             &c->d_counters->any_misaligned, true, 0);
+                             gates + s0, 1, true, 0, nullptr);
                 if (rc != CARIBOU_CUDA_OK) break;
                 CBL_CHECK(cudaEventRecord(c->pipe_ev[2 * g + 1], c->stream));
                 CBL_CHECK(cudaStreamWaitEvent(c->d2h_stream, c->pipe_ev[2 * g + 1], 0));
@@ -793,11 +958,7 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
             CBL_CHECK(cudaEventRecord(ev_done, c->d2h_stream));
             CBL_CHECK(cudaStreamWaitEvent(c->stream, ev_done, 0));      // waiting for the context now covers the copies
             if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
-            c->pipelined_last = true;
-            c->pending.active = true;
-            c->pending.bytes = bytes; c->pending.nbytes = nbytes; c->pending.stride = stride_bytes; c->pending.mem = mem;
-            c->pending.filt_out = filt_out; c->pending.filt_stride = filt_stride;
-            c->pending.d_bytes = d_bytes; c->pending.d_out = d_out;
+            c->queue.push_back(q);
             c->pos += n;
             return CARIBOU_CUDA_OK;
         }
@@ -805,88 +966,149 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
         const size_t in_span = (ns - 1) * stride_bytes + nbytes;
         CBL_CHECK(cudaMemcpyAsync(c->stage_in.p, bytes, in_span, cudaMemcpyHostToDevice, c->stream));
     }
-    const int mc = run_find_offsets(c, d_bytes, nbytes, stride_bytes);
+    q.d_bytes = d_bytes; q.d_out = d_out;
+    const int mc = run_find_offsets(c, d_bytes, nbytes, stride_bytes, true);
     if (mc < 0) return mc;
-    // optimistic fused launch, a no-op on the device if any chunk turned out misaligned
-    if (run_iir(c, IN_WORDS, d_bytes, n, stride_bytes / 4, d_out, filt_stride, &c->d_counters->any_misaligned, true, 0) != CARIBOU_CUDA_OK)
+    // optimistic fused launch: captures whose gate the search just raised are skipped on the device
+    if (run_iir(c, IN_WORDS, d_bytes, n, stride_bytes / 4, d_out, filt_stride, gates, 1, true, 0, nullptr) != CARIBOU_CUDA_OK)
         return CARIBOU_CUDA_ERR;
     if (uo) {
-        if (mem != CARIBOU_CUDA_MEM_DEVICE) { set_error("rx_submit with unpack outputs needs device memory"); return CARIBOU_CUDA_ERR; }
         const size_t ostride = ns > 1 ? ((n + 3) & ~size_t(3)) : 0;
         if (run_unpack(c, d_bytes, nbytes, stride_bytes, *uo, (uint32_t)mc, ostride) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     }
     if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     if (mem != CARIBOU_CUDA_MEM_DEVICE)
         CBL_CHECK(cudaMemcpyAsync(filt_out, d_out, ((ns - 1) * filt_stride + nout) * c->out_elem, cudaMemcpyDeviceToHost, c->stream));
-    c->pending.active = true;
-    c->pending.bytes = bytes; c->pending.nbytes = nbytes; c->pending.stride = stride_bytes; c->pending.mem = mem;
-    c->pending.filt_out = filt_out; c->pending.filt_stride = filt_stride;
-    c->pending.d_bytes = d_bytes; c->pending.d_out = d_out;
+    c->queue.push_back(q);
     c->pos += n;
-    if (mem == CARIBOU_CUDA_MEM_HOST) return caribou_cuda_wait(c, nullptr) < 0 ? CARIBOU_CUDA_ERR : CARIBOU_CUDA_OK;
+    if (mem == CARIBOU_CUDA_MEM_HOST) return resolve_queue(c);
     return CARIBOU_CUDA_OK;
 }
 
-// Misaligned capture: the fused launch did nothing.  Decode into a zero-filled CS16 scratch with the
-// reference's chunk semantics, then filter the delivered samples.
-static int rx_fallback(caribou_cuda_ctx* c)
+}  // extern "C"
+
+namespace cbl {
+
+// One capture (stream s) of one queued submit on the slow path: decode into a zero-filled CS16 scratch with the
+// reference's chunk semantics, then filter what the reference's read loop would have delivered.  Synchronous.
+static int rx_replay_stream(caribou_cuda_ctx* c, const PendingRx& q, size_t s, caribou_cuda_stream_result* r)
 {
-    PendingRx& q = c->pending;
     const FilterPlan& P = c->plan;
     const size_t ns = (size_t)c->cfg.n_streams;
     const size_t n = q.nbytes / 4;
     const size_t sstride = (n + 3) & ~size_t(3);
-    if (!c->scratch_cs16.reserve(ns * sstride * 4 + 64)) return CARIBOU_CUDA_ERR;
-    // a pipelined submit gates group by group: groups seen before the first misaligned chunk have already been
-    // filtered and have advanced their states - everything is redone from the states the submit started with
-    if (c->pipelined_last) CBL_CHECK(cudaMemcpyAsync(c->d_state, c->d_state_backup, ns * 2 * P.S * 8, cudaMemcpyDeviceToDevice, c->stream));
-    CBL_CHECK(cudaMemsetAsync(c->scratch_cs16.p, 0, ns * sstride * 4, c->stream));
+    if (!c->scratch_cs16.reserve(sstride * 4 + 64)) return CARIBOU_CUDA_ERR;
+    const uint8_t* d_bytes = reinterpret_cast<const uint8_t*>(q.d_bytes);
+    uint8_t* d_out = reinterpret_cast<uint8_t*>(q.d_out);
+    if (q.mem != CARIBOU_CUDA_MEM_DEVICE) {
+        // later submits have reused the staging buffers: fetch this capture again
+        if (!c->stage_in.reserve(ns * q.stride + 64) || !c->stage_filt.reserve(ns * q.filt_stride * c->out_elem + 64)) return CARIBOU_CUDA_ERR;
+        d_bytes = c->stage_in.as<uint8_t>();
+        d_out = c->stage_filt.as<uint8_t>();
+        CBL_CHECK(cudaMemcpyAsync(c->stage_in.as<uint8_t>() + s * q.stride, reinterpret_cast<const uint8_t*>(q.bytes) + s * q.stride,
+                                  q.nbytes, cudaMemcpyHostToDevice, c->stream));
+    }
+    CBL_CHECK(cudaMemsetAsync(c->scratch_cs16.p, 0, sstride * 4, c->stream));
+    CBL_CHECK(cudaMemsetAsync(c->d_counters, 0, sizeof(Counters), c->stream));
+    c->win0 = (uint32_t)s; c->win_cnt = 1;
+    auto done = [&](int rc) { c->win0 = 0; c->win_cnt = (uint32_t)ns; return rc; };
     caribou_cuda_unpack_out o;
     memset(&o, 0, sizeof(o));
-    o.cs16 = c->scratch_cs16.p;
-    const int mc = run_find_offsets(c, q.d_bytes, q.nbytes, q.stride);
-    if (mc < 0) return mc;
-    if (run_unpack(c, q.d_bytes, q.nbytes, q.stride, o, (uint32_t)mc, ns > 1 ? sstride : 0) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
-    if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    // run_unpack addresses stream s of the batch at out + s * out_stride: hand it a base that lands on the scratch
+    o.cs16 = c->scratch_cs16.as<uint32_t>() - s * sstride;
+    const int mc = run_find_offsets(c, d_bytes + s * q.stride, q.nbytes, q.stride, false);
+    if (mc < 0) return done(mc);
+    if (run_unpack(c, d_bytes, q.nbytes, q.stride, o, (uint32_t)mc, sstride) != CARIBOU_CUDA_OK) return done(CARIBOU_CUDA_ERR);
+    if (mirror_counters(c) != CARIBOU_CUDA_OK) return done(CARIBOU_CUDA_ERR);
     CBL_CHECK(cudaStreamSynchronize(c->stream));
-    // samples delivered before a lost sync (all streams must agree for a batched filter launch)
+    // samples delivered before a lost sync (caribou_smi.c:664-677)
     int64_t deliver = (int64_t)n;
     bool lost = false;
-    for (size_t s = 0; s < ns; s++) {
-        const int32_t fb = c->h_first_bad[s * 2];
-        const uint64_t cb = c->cfg.chunk_bytes;
-        if (fb != INT_MAX && (uint64_t)fb < (q.nbytes + cb - 1) / cb) {
-            lost = true;
-            deliver = std::min<int64_t>(deliver, (int64_t)fb * (int64_t)(cb / 4));
-        }
+    const int32_t fb = c->h_first_bad[s * 2];
+    const uint64_t cb = c->cfg.chunk_bytes;
+    if (fb != INT_MAX && (uint64_t)fb < (q.nbytes + cb - 1) / cb) {
+        lost = true;
+        deliver = (int64_t)fb * (int64_t)(cb / 4);
     }
     deliver -= deliver % P.D;
     if (deliver > 0) {
-        if (run_iir(c, IN_CS16, c->scratch_cs16.p, (size_t)deliver, sstride, q.d_out, q.filt_stride, nullptr, true, 0) != CARIBOU_CUDA_OK)
-            return CARIBOU_CUDA_ERR;
+        if (run_iir(c, IN_CS16, c->scratch_cs16.p, (size_t)deliver, sstride, d_out + s * q.filt_stride * c->out_elem, q.filt_stride,
+                    nullptr, 0, true, 0, nullptr) != CARIBOU_CUDA_OK)
+            return done(CARIBOU_CUDA_ERR);
         if (q.mem != CARIBOU_CUDA_MEM_DEVICE)
-            CBL_CHECK(cudaMemcpyAsync(q.filt_out, q.d_out, ((ns - 1) * q.filt_stride + (size_t)deliver / P.D) * c->out_elem, cudaMemcpyDeviceToHost, c->stream));
+            CBL_CHECK(cudaMemcpyAsync(reinterpret_cast<uint8_t*>(q.filt_out) + s * q.filt_stride * c->out_elem,
+                                      d_out + s * q.filt_stride * c->out_elem, (size_t)deliver / P.D * c->out_elem,
+                                      cudaMemcpyDeviceToHost, c->stream));
     }
     CBL_CHECK(cudaStreamSynchronize(c->stream));
-    c->pos -= n;
-    c->pos += (uint64_t)deliver;
-    c->last_ret = lost ? CARIBOU_CUDA_ERR_SYNC : deliver;
-    c->last_n_filtered = deliver / P.D;
+    if (r) {
+        r->n_samples = lost ? CARIBOU_CUDA_ERR_SYNC : deliver;
+        r->n_filtered = deliver / P.D;
+        r->first_bad_chunk = lost ? fb : -1;
+        r->n_misaligned_chunks = c->h_counters->n_misaligned;
+    }
+    return done(CARIBOU_CUDA_OK);
+}
+
+int resolve_queue(caribou_cuda_ctx* c)
+{
+    if (c->queue.empty()) return CARIBOU_CUDA_OK;
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
+    const size_t ns = (size_t)c->cfg.n_streams;
+    const PendingRx last = c->queue.back();
+    const size_t n = last.nbytes / 4;
+    // results of the last submit as the fused path left them (a gated capture is overwritten by its replay)
+    std::vector<int32_t> gate(c->h_sflags, c->h_sflags + ns), gseq(c->h_sflags + ns, c->h_sflags + 2 * ns);
+    Counters cnt = *c->h_counters;
+    bool any = false;
+    for (size_t s = 0; s < ns; s++) {
+        c->sres[s].n_samples = (int64_t)n;
+        c->sres[s].n_filtered = (int64_t)(n / c->plan.D);
+        c->sres[s].first_bad_chunk = -1;
+        c->sres[s].n_misaligned_chunks = c->h_sflags[2 * ns + s];
+        any = any || gate[s] != 0;
+    }
+    std::vector<PendingRx> queue;
+    queue.swap(c->queue);              // run_find_offsets stamps submits with the queue length: empty from here on
+    if (any) {
+        for (size_t s = 0; s < ns; s++) {
+            if (!gate[s]) continue;
+            for (const PendingRx& q : queue) {
+                if (q.seq < gseq[s]) continue;
+                if (rx_replay_stream(c, q, s, q.seq == last.seq ? &c->sres[s] : nullptr) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+            }
+        }
+        CBL_CHECK(cudaMemsetAsync(c->d_sflags, 0, ns * 4, c->stream));
+        CBL_CHECK(cudaMemsetAsync(c->d_sflags + ns, 0x7f, ns * 4, c->stream));
+        CBL_CHECK(cudaStreamSynchronize(c->stream));
+        memset(c->h_sflags, 0, ns * 4);
+        // the batch-level counters describe the last submit as a whole again
+        *c->h_counters = cnt;
+    }
+    int64_t ret = (int64_t)n, nf = (int64_t)(n / c->plan.D);
+    for (size_t s = 0; s < ns; s++) {
+        if (c->sres[s].n_samples == CARIBOU_CUDA_ERR_SYNC) ret = CARIBOU_CUDA_ERR_SYNC;
+        else if (ret >= 0) ret = std::min(ret, c->sres[s].n_samples);
+        nf = std::min(nf, c->sres[s].n_filtered);
+    }
+    c->last_ret = ret;
+    c->last_n_filtered = nf;
+    c->sres_valid = true;
     return CARIBOU_CUDA_OK;
 }
+
+}  // namespace cbl
+
+extern "C" {
 
 int64_t caribou_cuda_wait(caribou_cuda_ctx* c, caribou_cuda_result* res)
 {
     if (!c) { set_error("null context"); return CARIBOU_CUDA_ERR; }
     if (!cuda_ok(cudaSetDevice(c->device), "cudaSetDevice") || !cuda_ok(cudaStreamSynchronize(c->stream), "cudaStreamSynchronize"))
         return CARIBOU_CUDA_ERR;
-    if (c->pending.active) {
-        c->pending.active = false;
-        if (c->h_counters->any_misaligned != 0) {
-            if (rx_fallback(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
-        }
-    }
+    if (resolve_queue(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     int64_t ret = c->last_ret, ret_b = 0;
+    if (c->last_is_shard && c->h_counters->any_misaligned != 0) ret = CARIBOU_CUDA_ERR_SYNC;   // shards are aligned chunks or nothing
     if (c->last_is_unpack) {
         const int nsub = n_subs_of(c);
         int64_t r[2] = {0, 0};
@@ -907,14 +1129,34 @@ int64_t caribou_cuda_wait(caribou_cuda_ctx* c, caribou_cuda_result* res)
         res->n_filtered = c->last_n_filtered;
         res->n_invalid = c->h_counters->totals[0];
         res->n_sync = c->h_counters->totals[1];
-        int32_t fb = INT_MAX;
-        for (int i = 0; i < c->cfg.n_streams * 2; i++) fb = std::min(fb, c->h_first_bad[i]);
-        const uint64_t cb = c->cfg.chunk_bytes;
-        res->first_bad_chunk = (fb != INT_MAX && (uint64_t)fb < (c->last_nbytes + cb - 1) / cb) ? fb : -1;
+        res->first_bad_chunk = -1;
         res->n_misaligned_chunks = c->h_counters->n_misaligned;
+        if (c->sres_valid) {
+            int32_t nm = 0;
+            for (const caribou_cuda_stream_result& r : c->sres) {
+                if (r.first_bad_chunk >= 0 && (res->first_bad_chunk < 0 || r.first_bad_chunk < res->first_bad_chunk)) res->first_bad_chunk = r.first_bad_chunk;
+                nm += r.n_misaligned_chunks;
+            }
+            res->n_misaligned_chunks = nm;
+        } else {
+            int32_t fb = INT_MAX;
+            for (int i = 0; i < c->cfg.n_streams * 2; i++) fb = std::min(fb, c->h_first_bad[i]);
+            const uint64_t cb = c->cfg.chunk_bytes;
+            res->first_bad_chunk = (fb != INT_MAX && (uint64_t)fb < (c->last_nbytes + cb - 1) / cb) ? fb : -1;
+        }
     }
     return ret;
 }
+
+int caribou_cuda_stream_results(caribou_cuda_ctx* c, caribou_cuda_stream_result* out)
+{
+    if (!c || !out) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    if (caribou_cuda_wait(c, nullptr) == CARIBOU_CUDA_ERR) return CARIBOU_CUDA_ERR;
+    if (!c->sres_valid) { set_error("per-capture results exist after caribou_cuda_rx_submit only"); return CARIBOU_CUDA_ERR; }
+    for (int s = 0; s < c->cfg.n_streams; s++) out[s] = c->sres[s];
+    return CARIBOU_CUDA_OK;
+}
+
 
 int caribou_cuda_filter_info(caribou_cuda_ctx* c, caribou_cuda_filter_info_t* info)
 {
@@ -938,7 +1180,8 @@ int caribou_cuda_get_state(caribou_cuda_ctx* c, int stream, double* state)
     if (caribou_cuda_wait(c, nullptr) == CARIBOU_CUDA_ERR) return CARIBOU_CUDA_ERR;
     const FilterPlan& P = c->plan;
     double ker[2 * kMaxS];
-    CBL_CHECK(cudaMemcpy(ker, c->d_state + (size_t)stream * 2 * P.S, (size_t)2 * P.S * 8, cudaMemcpyDeviceToHost));
+    CBL_CHECK(cudaMemcpyAsync(ker, c->d_state + (size_t)stream * 2 * P.S, (size_t)2 * P.S * 8, cudaMemcpyDeviceToHost, c->stream));
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
     state_to_ref(P, ker, state);
     for (int i = 0; i < 2 * P.S; i++) state[i] *= c->in_scale;
     return CARIBOU_CUDA_OK;
@@ -952,7 +1195,9 @@ int caribou_cuda_set_state(caribou_cuda_ctx* c, int stream, const double* state)
     double ker[2 * kMaxS];
     state_to_kernel(P, state, ker);
     for (int i = 0; i < 2 * P.S; i++) ker[i] /= c->in_scale;
-    CBL_CHECK(cudaMemcpy(c->d_state + (size_t)stream * 2 * P.S, ker, (size_t)2 * P.S * 8, cudaMemcpyHostToDevice));
+    // ordered on the context's stream (the kernels that read the state run there), waited for because `ker` is a local
+    CBL_CHECK(cudaMemcpyAsync(c->d_state + (size_t)stream * 2 * P.S, ker, (size_t)2 * P.S * 8, cudaMemcpyHostToDevice, c->stream));
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
     return CARIBOU_CUDA_OK;
 }
 
@@ -961,8 +1206,14 @@ int caribou_cuda_reset(caribou_cuda_ctx* c)
     if (!c) { set_error("null context"); return CARIBOU_CUDA_ERR; }
     CBL_CHECK(cudaSetDevice(c->device));
     CBL_CHECK(cudaStreamSynchronize(c->stream));
-    c->pending.active = false;
-    if (c->has_filter) CBL_CHECK(cudaMemset(c->d_state, 0, (size_t)c->cfg.n_streams * 2 * c->plan.S * 8));
+    // whatever was queued is dropped with the state it would have advanced
+    const size_t ns = (size_t)c->cfg.n_streams;
+    c->queue.clear();
+    CBL_CHECK(cudaMemsetAsync(c->d_sflags, 0, ns * 4, c->stream));
+    CBL_CHECK(cudaMemsetAsync(c->d_sflags + ns, 0x7f, ns * 4, c->stream));
+    if (c->has_filter) CBL_CHECK(cudaMemsetAsync(c->d_state, 0, ns * 2 * c->plan.S * 8, c->stream));
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
+    memset(c->h_sflags, 0, ns * 3 * 4);
     c->pos = 0;
     return CARIBOU_CUDA_OK;
 }
@@ -980,8 +1231,10 @@ int caribou_cuda_tx_pack_submit(caribou_cuda_ctx* c, int in_format, const void* 
         default: set_error("unknown sample format"); return CARIBOU_CUDA_ERR;
     }
     CBL_CHECK(cudaSetDevice(c->device));
-    c->pending.active = false;
+    if (resolve_queue(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     c->last_is_unpack = false;
+    c->last_is_shard = false;
+    c->sres_valid = false;
     c->last_n_filtered = 0;
     c->last_ret = (int64_t)n;
     if (n == 0) return CARIBOU_CUDA_OK;
@@ -1023,7 +1276,7 @@ int caribou_cuda_synth_words(caribou_cuda_ctx* c, void* dev_words, uint64_t n0, 
     if (!c->d_tone) CBL_CHECK(cudaMalloc(&c->d_tone, 1600 * sizeof(int16_t)));
     CBL_CHECK(cudaMemcpyAsync(c->d_tone, tone_i, 800 * 2, cudaMemcpyHostToDevice, c->stream));
     CBL_CHECK(cudaMemcpyAsync(c->d_tone + 800, tone_q, 800 * 2, cudaMemcpyHostToDevice, c->stream));
-    launch_synth(reinterpret_cast<uint32_t*>(dev_words), n0, n, hif_layout, seed, c->d_tone, c->d_tone + 800, c->stream);
+    launch_synth(reinterpret_cast<uint32_t*>(dev_words), n0, n, hif_layout, seed, c->d_tone, c->d_tone + 800, c->num_sms, c->stream);
     c->launches++;
     CBL_CHECK(cudaGetLastError());
     return CARIBOU_CUDA_OK;

@@ -29,6 +29,15 @@ struct DevBuf {
     template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+// page-locked host buffer that only ever grows (contents are not kept)
+struct HostBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    bool reserve(size_t n);
+    void release();
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
 // small block of flags/counters mirrored to pinned host memory after every submit
 struct Counters {
     int32_t  first_bad[2];        // per sub-stream, min over streams is not needed: stream 0.. handled per launch
@@ -37,12 +46,34 @@ struct Counters {
     uint64_t totals[2];           // n_invalid, n_sync
 };
 
-struct PendingRx {                // what caribou_cuda_rx_submit has to redo if a chunk was misaligned
-    bool active = false;
+struct PendingRx {                // one queued caribou_cuda_rx_submit: what has to be redone for a capture that
+    int32_t seq = 0;              // turned out misaligned (position in the queue since the last resolve)
     const void* bytes = nullptr; size_t nbytes = 0; size_t stride = 0; int mem = 0;
     void* filt_out = nullptr; size_t filt_stride = 0;
     const void* d_bytes = nullptr; void* d_out = nullptr;
 };
+constexpr size_t kMaxQueuedRx = 64;   // rx submits queued without a wait; the next one resolves the queue first
+
+struct Shard;                     // multi-GPU time sharding (shard.cu)
+void shard_release(Shard* s);
+
+// ---- launch sequences shared by api.cu, compat.cu and shard.cu
+// Filters n samples per stream (device memory) of the streams in the context's window.  `state` is the buffer
+// the streams start from and, with commit, end in (kernel coordinates; nullptr: the context's own d_state);
+// max_tiles > 0 limits the launch to the first max_tiles tiles of every stream (fix-up pass, no commit).
+// Tiles of stream s are skipped when gate[s * gate_stride] != 0.
+int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t in_stride, void* d_out,
+            size_t out_stride, const int32_t* gate, uint32_t gate_stride, bool commit, uint32_t max_tiles,
+            double* state);
+// alignment search of the window's streams; returns the chunk count (>= 0) or an error code.
+// with_gates: also raise the sticky per-stream gates the fused launches look at
+int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes, bool with_gates);
+int mirror_counters(caribou_cuda_ctx* c);
+int ensure_scale(caribou_cuda_ctx* c, int in_kind);
+// blocks until every queued rx submit has been carried out (misaligned captures redone on the slow path)
+int resolve_queue(caribou_cuda_ctx* c);
+// caribou_cuda_filter_submit on device memory with an optional gate (a no-op on the device when *gate != 0)
+int filter_device(caribou_cuda_ctx* c, int in_kind, const void* in, size_t n, void* out, const int32_t* gate);
 
 }  // namespace cbl
 
@@ -79,17 +110,22 @@ struct caribou_cuda_ctx {
     cbl::Counters* h_counters = nullptr;   // pinned
     int32_t* d_first_bad = nullptr;   // [n_streams][2]
     int32_t* h_first_bad = nullptr;   // pinned mirror
+    // per-stream verdicts of the fused path: [0..ns) sticky gate, [ns..2ns) first submit that raised it,
+    // [2ns..3ns) misaligned chunks of the last submit; [3ns] sticky "a chunk had no alignment" flag the shims
+    // clear before a read and gate the filter with (a read that lost sync delivers nothing, CaribouliteStream.cpp:266-276)
+    int32_t* d_sflags = nullptr;
+    int32_t* h_sflags = nullptr;      // pinned mirror
 
     // staging for host memory
     cbl::DevBuf stage_in, stage_cs16[2], stage_meta[2], stage_cf32[2], stage_filt, stage_inv, stage_syn, scratch_cs16;
+
+    cbl::HostBuf h_bounce;            // page-locked bounce buffer of the pageable-output unpack path
 
     // window of streams the launch helpers work on (pipelined host-buffer submits walk the batch group by group)
     uint32_t win0 = 0, win_cnt = 0;
     // copy engines' streams and events of the pipelined host-buffer path (created on first use)
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
     std::vector<cudaEvent_t> pipe_ev;
-    double* d_state_backup = nullptr;   // filter state before a pipelined submit (restored if it has to be redone)
-    bool pipelined_last = false;
 
     // synth
     int16_t* d_tone = nullptr;
@@ -97,7 +133,12 @@ struct caribou_cuda_ctx {
     // last submit, for caribou_cuda_wait
     int64_t last_ret = 0;
     bool last_is_unpack = false;
+    bool last_is_shard = false;       // the last submit was a sharded call: wait reports -3 for a misaligned shard
     size_t last_nbytes = 0;
     int64_t last_n_filtered = 0;
-    cbl::PendingRx pending;
+    std::vector<cbl::PendingRx> queue;                 // rx submits since the last resolve
+    std::vector<caribou_cuda_stream_result> sres;      // per-capture results of the last rx submit
+    bool sres_valid = false;
+
+    cbl::Shard* shard = nullptr;                       // multi-GPU time sharding (shard.cu)
 };

@@ -41,7 +41,7 @@ __global__ void iir_tail_kernel(const __grid_constant__ IirTailParams P)
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t stream = t >> 1, rail = t & 1u;          // rail 0 = I, 1 = Q
     if (stream >= P.n_streams) return;
-    if (P.gate != nullptr && *P.gate != 0) return;
+    if (P.gate != nullptr && P.gate[(size_t)stream * P.gate_stride] != 0) return;
     constexpr int S = 2 * K;
     double v[K][2];
     double* sp = P.state + (size_t)stream * (2 * S) + rail * S;
@@ -127,16 +127,22 @@ void launch_iir_tail(const IirTailParams& p, cudaStream_t st)
     }
 }
 
-__global__ void commit_state_kernel(double* state, const double* next, size_t n, const int32_t* gate)
+__global__ void commit_state_kernel(double* state, const double* next, size_t n, size_t per_stream, const int32_t* gate,
+                                    uint32_t gate_stride)
 {
-    if (gate != nullptr && *gate != 0) return;
-    for (size_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) state[i] = next[i];
+    for (size_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        if (gate != nullptr && gate[(i / per_stream) * gate_stride] != 0) continue;
+        state[i] = next[i];
+    }
 }
 
-void launch_commit_state(double* state, const double* state_next, size_t n, const int32_t* gate, cudaStream_t st)
+void launch_commit_state(double* state, const double* state_next, size_t n_streams, size_t per_stream, const int32_t* gate,
+                         uint32_t gate_stride, cudaStream_t st)
 {
+    const size_t n = n_streams * per_stream;
     if (n == 0) return;
-    commit_state_kernel<<<(unsigned)((n + 255) / 256 > 64 ? 64 : (n + 255) / 256), 256, 0, st>>>(state, state_next, n, gate);
+    commit_state_kernel<<<(unsigned)((n + 255) / 256 > 64 ? 64 : (n + 255) / 256), 256, 0, st>>>(state, state_next, n, per_stream,
+                                                                                                 gate, gate_stride);
 }
 
 }  // namespace cbl

@@ -37,6 +37,7 @@ namespace cbl {
 constexpr int kMaxK  = 4;
 constexpr int kMaxS  = 2 * kMaxK;      // state dimension per rail
 constexpr int kMaxNK = 32;             // kept outputs per run
+constexpr int kMaxDevices = 64;        // device ordinals the per-device launch set-up keeps a slot for
 
 enum { IN_WORDS = 0, IN_CS16 = 1, IN_CF32 = 2,
        IN_WORDS_HIF = 3 };   // internal: SMI words with the HiF field order (I = lo13), its own kernel instantiation
@@ -86,7 +87,8 @@ struct IirParams {
     double*   state_out;        // [n_streams][2S]
     void*     out;              // kept outputs, NK per run, streams out_stride elements apart
     uint64_t  out_stride;
-    const int32_t* gate;        // optional: the launch is a no-op when *gate != 0 (misaligned capture)
+    const int32_t* gate;        // optional: tiles of stream s are skipped when gate[s * gate_stride] != 0 (a capture that
+    uint32_t  gate_stride;      // lost word alignment is redone on the slow path); stride 0 = one flag for the launch
     // mantissa injection (iir_kernel.cuh inject_f64): sign-flip | exponent << 1 word, and the multiplier 2^31
     uint32_t  inj_xor, inj_mul;
     int       scan_rounds;      // Kogge-Stone rounds of the warp scan that can still contribute (<= 5)
@@ -102,7 +104,8 @@ struct IirTailParams {
     double a1[kMaxK], a2[kMaxK], c1[kMaxK], c2[kMaxK];
     double gain;
     double* state;                          // [n_streams][2S] kernel coordinates, updated in place
-    const int32_t* gate;                    // optional: no-op when *gate != 0
+    const int32_t* gate;                    // optional: stream s is skipped when gate[s * gate_stride] != 0
+    uint32_t gate_stride;
 };
 
 // Run length LT (samples one thread filters sequentially) for a cascade of K sections and a decimation factor D.
@@ -180,7 +183,8 @@ inline bool iir_has_y32(int K, bool par) { (void)K; return par; }
 int launch_iir(int K, int D, int in_kind, bool par, bool y32, const CUtensorMap& tmap, const IirParams& p,
                const IirTables& t, int num_sms, cudaStream_t st);
 void launch_iir_tail(const IirTailParams& p, cudaStream_t st);
-// state <- state_next (n doubles) unless *gate != 0
-void launch_commit_state(double* state, const double* state_next, size_t n, const int32_t* gate, cudaStream_t st);
+// state <- state_next (n_streams x per_stream doubles), except for streams with gate[s * gate_stride] != 0
+void launch_commit_state(double* state, const double* state_next, size_t n_streams, size_t per_stream, const int32_t* gate,
+                         uint32_t gate_stride, cudaStream_t st);
 
 }  // namespace cbl

@@ -288,8 +288,6 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     }
     __syncwarp();
 
-    if (P.gate != nullptr && __ldg(P.gate) != 0) return;
-
     constexpr int swap = 0;     // rail A is I, rail B is Q for every input kind (the HiF layout is its own instantiation)
     const uint32_t tps = P.tiles_per_stream;
 
@@ -341,6 +339,9 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
 
     for (;;) {
         const bool have = tile < P.total_tiles;
+        // a stream whose capture lost word alignment is left to the slow path (api.cu): its tiles still drain the
+        // ring (the boxes were requested before anybody could know) but are neither filtered nor stored
+        const bool live = have && (P.gate == nullptr || __ldg(P.gate + (size_t)stream * P.gate_stride) == 0);
         uint32_t next2 = 0xFFFFFFFFu, nstream = 0, ntis = 0;
         double f[2][S];
         double va[K][2], vb[K][2];
@@ -369,7 +370,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                 constexpr int GS = U * PER;                      // samples per group
                 const uint32_t ylane = ystage + lane * 8;
 #pragma unroll 1
-                for (int co = 0; co < 8 / U; co++) {
+                for (int co = 0; co < (live ? 8 / U : 0); co++) {
                     const int gbase = step * C::SPS + co * GS;   // first sample of the group within the run
                     uint4 q[U];
 #pragma unroll
@@ -432,7 +433,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
         if (owe && ptis != 0)
             pre = ld_desc((P.chained ? P.desc_incl : P.desc_agg) + (size_t)(ptile - 1) * (2 * S) + comp);
 
-        if (have) {
+        if (live) {
             // ---- phase 2: warp scan of run end states: E_t = sum_{j<=t} M^(t-j) f_j
 #pragma unroll
             for (int k = 0; k < K; k++) {
@@ -717,13 +718,15 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             __syncwarp();   // this half of the output stage and the scratch are free again
         }
         if (!have) break;
-        owe = true;
+        owe = live;
         ptile = tile; pstream = stream; ptis = tis;
+        if (live) {
 #pragma unroll
-        for (int r = 0; r < 2; r++)
+            for (int r = 0; r < 2; r++)
 #pragma unroll
-            for (int c = 0; c < S; c++) pf[r][c] = f[r][c];
-        buf ^= 1u;
+                for (int c = 0; c < S; c++) pf[r][c] = f[r][c];
+            buf ^= 1u;
+        }
         // lane 0's view of the ticket pipeline becomes everybody's current tile
         tile = __shfl_sync(0xffffffffu, next, 0);
         stream = __shfl_sync(0xffffffffu, nstream, 0);
@@ -739,15 +742,22 @@ int launch_iir_t(const CUtensorMap& tmap, const IirParams& p, const IirTables& t
 {
     using C = IirCfg<K, D, IN, PAR, Y32>;
     auto kern = iir_scan_kernel<K, D, IN, PAR, Y32>;
-    static int occ = 0;
-    if (occ == 0) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+    // the shared-memory opt-in is a per-device attribute of the function: one slot per device ordinal (the
+    // writes are idempotent, so two host threads racing on a slot only repeat the query)
+    static int occ_dev[kMaxDevices] = {0};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= kMaxDevices) return (int)cudaErrorInvalidDevice;
+    if (occ_dev[dev] == 0) {
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
         if (e != cudaSuccess) return (int)e;
         int n = 0;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, C::WPC * 32, C::SMEM_BYTES);
         if (e != cudaSuccess) return (int)e;
-        occ = n > 0 ? n : 1;
+        occ_dev[dev] = n > 0 ? n : 1;
     }
+    const int occ = occ_dev[dev];
     const uint64_t want = ((uint64_t)p.total_tiles + C::WPC - 1) / C::WPC;
     const uint64_t cap = (uint64_t)occ * (uint64_t)num_sms;
     const int grid = (int)(want < cap ? want : cap);

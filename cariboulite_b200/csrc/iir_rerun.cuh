@@ -147,8 +147,6 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     }
     __syncwarp();
 
-    if (P.gate != nullptr && __ldg(P.gate) != 0) return;
-
     const uint32_t tps = P.tiles_per_stream;
 
     const uint32_t inj_xor = P.inj_xor, inj_mul = P.inj_mul;
@@ -188,6 +186,8 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 
     for (;;) {
         const bool have = tile < P.total_tiles;
+        // gated stream (its capture lost word alignment, api.cu): the tile drains its boxes and is otherwise skipped
+        const bool live = have && (P.gate == nullptr || __ldg(P.gate + (size_t)stream * P.gate_stride) == 0);
         const uint32_t half = slot;
         const uint32_t prev = slot == 0 ? (uint32_t)C::NBUF - 1u : slot - 1u;     // the owed tile's slot
         uint32_t next = 0xFFFFFFFFu;       // meaningful in lane 0
@@ -208,7 +208,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 // the 128-byte row in two groups of four pieces: the loops of a tile iteration have to share the
                 // 32 KiB instruction cache of the SM with eleven other warps in other phases
 #pragma unroll 1
-                for (int co = 0; co < 8; co += 4) {
+                for (int co = 0; co < (live ? 8 : 0); co += 4) {
                     uint4 q[4];
 #pragma unroll
                     for (int ci = 0; ci < 4; ci++) q[ci] = row_piece(box, co + ci);
@@ -243,7 +243,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             // ---- phase 2: warp scan of run end states: E_t = sum_{j<=t} M^(t-j) f_j
 #pragma unroll
             for (int j = 0; j < 5; j++) {
-                if (j < P.scan_rounds) {
+                if (j < P.scan_rounds && live) {
                     const int d = 1 << j;
                     double g[2][S];
 #pragma unroll
@@ -264,7 +264,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 }
             }
             if (lane == 0) next = take_ticket(ticket);      // looked at after phase 3
-            if (lane == 31 && !P.chained) {
+            if (lane == 31 && !P.chained && live) {
                 double* agg = P.desc_agg + (size_t)tile * (2 * S);
 #pragma unroll
                 for (int r = 0; r < 2; r++)
@@ -436,7 +436,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         // the slot the owed tile just left takes this warp's next tile
         const uint32_t nstream = next / tps, ntis = next - nstream * tps;
         if (lane == 0 && next < P.total_tiles) issue_tile(nstream, ntis, prev);
-        owe = true;
+        owe = live;
         ptile = tile; pstream = stream; ptis = tis;
 #pragma unroll
         for (int r = 0; r < 2; r++)
@@ -454,11 +454,15 @@ int launch_rerun_t(const CUtensorMap& tmap, const IirParams& p, const IirTables&
 {
     using C = RerunCfg<K, D, IN>;
     auto kern = iir_rerun_kernel<K, D, IN>;
-    static bool ready = false;
-    if (!ready) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+    static bool ready_dev[kMaxDevices] = {false};      // per device: the shared-memory opt-in is a per-device attribute
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= kMaxDevices) return (int)cudaErrorInvalidDevice;
+    if (!ready_dev[dev]) {
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
         if (e != cudaSuccess) return (int)e;
-        ready = true;
+        ready_dev[dev] = true;
     }
     const uint64_t want = ((uint64_t)p.total_tiles + C::WPC - 1) / C::WPC;
     const int grid = (int)(want < (uint64_t)num_sms ? want : (uint64_t)num_sms);

@@ -1,11 +1,15 @@
 // Kernel (a) of libcaribou_cuda: per-chunk alignment search and the fused
-// unpack / demux / sync-check / sign-extend / CS16 / CF32 kernel with ordered
-// warp-ballot compaction of flagged words.
+// unpack / demux / sync-check / sign-extend / CS16 / CF32 kernel, plus the ordered
+// compaction of flagged words.
 //
 // What it computes is fixed by the reference (LC/caribou_smi/caribou_smi.c:235-393); how it
-// is computed is not: one thread owns 8 consecutive raw words (two 128-bit loads), emits one
-// 128-bit CS16 store, two 128-bit CF32 stores and one 32-bit meta store per 4 samples, and the
-// ascending index lists come from a single-pass chained scan over tiles (decoupled look-back).
+// is computed is not.  A tile is 4096 consecutive raw words; a plain tile (whole words, every
+// chunk it touches aligned) is decoded with four coalesced 128-bit loads in flight per thread,
+// one 128-bit CS16 store, one 32-bit meta store and two 128-bit CF32 stores per 4 samples;
+// everything else takes the per-sample path with the reference's integer arithmetic.
+// Flagged words are counted per tile by the decode kernel (warp ballots, one atomic per warp
+// that saw any); a one-CTA scan turns the counts into list offsets and a work list, and only
+// the flagged tiles are read again to emit their indices in ascending order.
 #include "unpack.cuh"
 #include <limits.h>
 
@@ -69,9 +73,21 @@ __global__ void __launch_bounds__(kFindThreads) find_offsets_kernel(OffsetsParam
     }
     if (threadIdx.x == 0) {
         p.offs[(size_t)blockIdx.y * p.offs_stride + c] = result;
-        if (result < 0) atomicMin(p.first_bad + (size_t)blockIdx.y * p.first_bad_stride, (int)c);
-        if (result > 0) atomicAdd(p.n_misaligned, 1);
-        if (result != 0) *p.any_misaligned = 1;
+        if (result < 0) {
+            atomicMin(p.first_bad + (size_t)blockIdx.y * p.first_bad_stride, (int)c);
+            if (p.lost) *p.lost = 1;
+        }
+        if (result > 0) {
+            atomicAdd(p.n_misaligned, 1);
+            if (p.nmis) atomicAdd(p.nmis + blockIdx.y, 1);
+        }
+        if (result != 0) {
+            *p.any_misaligned = 1;
+            if (p.gate) {
+                p.gate[blockIdx.y] = 1;
+                atomicMin(p.gate_seq + blockIdx.y, p.seq);
+            }
+        }
     }
 }
 
@@ -472,10 +488,10 @@ __global__ void synth_kernel(uint32_t* out, uint64_t n0, uint64_t n, int hif_lay
 }
 
 void launch_synth(uint32_t* out, uint64_t n0, uint64_t n, int hif_layout, uint64_t seed,
-                  const int16_t* tone_i, const int16_t* tone_q, cudaStream_t st)
+                  const int16_t* tone_i, const int16_t* tone_q, int num_sms, cudaStream_t st)
 {
     if (n == 0) return;
-    synth_kernel<<<148 * 8, 256, 0, st>>>(out, n0, n, hif_layout, seed, tone_i, tone_q);
+    synth_kernel<<<(num_sms > 0 ? num_sms : 148) * 8, 256, 0, st>>>(out, n0, n, hif_layout, seed, tone_i, tone_q);
 }
 
 }  // namespace cbl

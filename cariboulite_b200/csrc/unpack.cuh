@@ -16,6 +16,12 @@ struct OffsetsParams {
     uint32_t first_bad_stride;
     int32_t* n_misaligned;  // out: += chunks with offs > 0
     int32_t* any_misaligned;// out: set to 1 if any chunk has offs != 0 (shared by all subs/streams)
+    // per-stream verdicts for the fused path (all optional, indexed by the stream of the launch):
+    int32_t* gate;          // out: set to 1 when a chunk of the stream has offs != 0 - sticky, the fused kernels skip the stream
+    int32_t* gate_seq;      // out: min over the submits that set the gate of `seq`
+    int32_t* nmis;          // out: += chunks of the stream with offs > 0
+    int32_t  seq;           // sequence number of this submit since the context last resolved its queue
+    int32_t* lost;          // optional out: set to 1 when a chunk has no alignment at all (sticky: the caller clears it)
 };
 
 struct UnpackParams {
@@ -55,6 +61,6 @@ void launch_find_offsets(const OffsetsParams& p, cudaStream_t st);
 // returns the number of kernels launched (decode, flag scan, flag index emission)
 int launch_unpack(const UnpackParams& p, int num_sms, cudaStream_t st);
 void launch_synth(uint32_t* out, uint64_t n0, uint64_t n, int hif_layout, uint64_t seed,
-                  const int16_t* tone_i, const int16_t* tone_q, cudaStream_t st);
+                  const int16_t* tone_i, const int16_t* tone_q, int num_sms, cudaStream_t st);
 
 }  // namespace cbl

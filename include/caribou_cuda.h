@@ -39,6 +39,9 @@ typedef enum { CARIBOU_CUDA_MEM_DEVICE = 0,        /* pointers are device memory
                CARIBOU_CUDA_MEM_HOST_PINNED = 1,   /* page-locked host memory: async copies */
                CARIBOU_CUDA_MEM_HOST = 2           /* pageable host memory: staged, synchronous */
 } caribou_cuda_mem;
+/* caribou_cuda_unpack_submit only: input bytes of kind `in`, output arrays of kind `out` (the shims read(2) into a
+ * page-locked buffer and deliver into the caller's pageable arrays) */
+#define CARIBOU_CUDA_MEM_IO(in, out)  (0x100 | ((in) & 0xF) | (((out) & 0xF) << 4))
 
 /* Sample formats of SoapyCariboulite's setupStream (LC/soapy_api/CaribouliteStreamFunctions.cpp:11-19). */
 typedef enum { CARIBOU_CUDA_FMT_CF32 = 0, CARIBOU_CUDA_FMT_CS16 = 1,
@@ -56,6 +59,9 @@ typedef enum { CARIBOU_CUDA_IN_WORDS = 0,   /* raw 32-bit SMI words (fused unpac
                CARIBOU_CUDA_IN_CS16 = 1,    /* packed (int16 i, int16 q)           */
                CARIBOU_CUDA_IN_CF32 = 2     /* packed (float i, float q)            */
 } caribou_cuda_input;
+
+/* Realisation of the cascade inside the scan kernels (caribou_cuda_config.kernel_form). */
+typedef enum { CARIBOU_CUDA_FORM_AUTO = 0, CARIBOU_CUDA_FORM_CASCADE = 1, CARIBOU_CUDA_FORM_PARALLEL = 2 } caribou_cuda_form;
 
 typedef struct caribou_cuda_ctx caribou_cuda_ctx;
 
@@ -79,8 +85,6 @@ typedef struct {
                                          cascade when the poles allow it; CASCADE keeps the reference's stage-by-stage
                                          arithmetic order inside every run */
 } caribou_cuda_config;
-
-typedef enum { CARIBOU_CUDA_FORM_AUTO = 0, CARIBOU_CUDA_FORM_CASCADE = 1, CARIBOU_CUDA_FORM_PARALLEL = 2 } caribou_cuda_form;
 
 /* What the scan kernel does with the configured cascade (for tests, DESIGN.md numbers and the curious). */
 typedef struct {
@@ -116,12 +120,23 @@ typedef struct {
 typedef struct {
     int64_t  n_samples;      /* samples delivered (per sub-stream in dual-channel mode: S1G) */
     int64_t  n_samples_b;    /* HiF sub-stream */
-    int64_t  n_filtered;     /* filtered/decimated samples written per stream */
+    int64_t  n_filtered;     /* filtered/decimated samples written per stream (batch: the minimum over the streams) */
     uint64_t n_invalid;      /* exact, even when the index list is capped */
     uint64_t n_sync;
     int32_t  first_bad_chunk;    /* first chunk with no alignment, -1 if none */
     int32_t  n_misaligned_chunks;/* chunks with offs > 0 */
 } caribou_cuda_result;
+
+/* One capture of a batch (caribou_cuda_rx_submit with n_streams > 1): the captures are independent reads, so each
+ * has its own return value exactly as caribou_smi_read would give it (LC/caribou_smi/caribou_smi.c:632-682). */
+typedef struct {
+    int64_t  n_samples;          /* samples consumed by the filter, or CARIBOU_CUDA_ERR_SYNC (-3) when a chunk of THIS
+                                    capture had no alignment (caribou_smi.c:665-668) */
+    int64_t  n_filtered;         /* filtered/decimated samples written for this capture (on -3: those of the chunks
+                                    before the un-alignable one) */
+    int32_t  first_bad_chunk;    /* -1 if none */
+    int32_t  n_misaligned_chunks;/* chunks of this capture with offs > 0 */
+} caribou_cuda_stream_result;
 
 /* ---------------------------------------------------------------- lifecycle */
 /* Replaces caribou_smi_init's buffer/stream set-up (LC/caribou_smi/caribou_smi.c:513-581) and the
@@ -133,6 +148,11 @@ void*       caribou_cuda_get_stream(caribou_cuda_ctx* ctx); /* cudaStream_t the 
 /* Block until everything submitted on the context has finished; fills *res (may be NULL) with the
  * counters of the last submit.  Returns the last submit's sample count or error code. */
 int64_t     caribou_cuda_wait(caribou_cuda_ctx* ctx, caribou_cuda_result* res);
+/* Per-capture results of the last caribou_cuda_rx_submit (call after caribou_cuda_wait): fills out[0..n_streams).
+ * A capture that lost word alignment does not disturb the others: they stay on the fused kernel, the affected
+ * capture alone is redone through unpack -> CS16 -> filter with the reference's chunk semantics.  Several
+ * submits may be queued before one wait; a misaligned capture is then redone for all of them, in order. */
+int         caribou_cuda_stream_results(caribou_cuda_ctx* ctx, caribou_cuda_stream_result* out);
 /* Number of kernels this context has launched so far (bench.py's gpu_launches). */
 uint64_t    caribou_cuda_launch_count(const caribou_cuda_ctx* ctx);
 
@@ -199,6 +219,43 @@ int    caribou_cuda_filter_fixup(caribou_cuda_ctx* ctx, int in_kind, const void*
                                  size_t in_stride_elems, int mem, void* out, size_t out_stride_elems,
                                  const double* state_in /* 4*n_sos doubles per stream, host */);
 
+/* Device-side hand-off (BASELINE.json configs[4]): one long stream, time-chunked over the GPUs of
+ * a box.  Rank g of `world` owns samples [g n, (g+1) n) of every call; state and decimation phase carry over from
+ * call to call exactly as on one GPU (the reference's behaviour to match: filter objects that are never reset,
+ * LC/soapy_api/CaribouliteStream.hpp:124-131, fed MTU after MTU by LC/caribou_smi/caribou_smi.c:643-679).
+ *
+ *   caribou_cuda_shard_submit =  pass 1   fused kernel over the shard from ZERO state -> outputs + end vector f_g
+ *                                hand-off ncclAllGather of the 4K doubles per stream on the context's stream (or the
+ *                                         ncclSend/ncclRecv chain, mode 1), then a one-CTA kernel composes
+ *                                         s_in(g) = sum_{j<g} M^(g-1-j) f_j + M^g carry   and the new carry, M = A^n
+ *                                fix-up   the leading tiles (caribou_cuda_fixup_samples) re-run from s_in(g), read
+ *                                         from device memory
+ * Nothing on that path touches the host: no stream synchronisation, no host copy.  caribou_cuda_wait returns
+ * n_samples (or -3 if a chunk of the shard lost word alignment: shards must consist of aligned chunks).
+ *
+ * NCCL is bound at run time (dlopen of libnccl.so.2, so that a process that already carries an NCCL - PyTorch's -
+ * shares it): caribou_cuda_shard_unique_id wraps ncclGetUniqueId (rank 0 calls it and ships the 128 bytes to the
+ * other ranks by any means), caribou_cuda_shard_init wraps ncclCommInitRank; caribou_cuda_shard_attach_comm borrows an
+ * ncclComm_t the caller owns.  With id == NULL no communicator is created and the caller moves the end vectors
+ * itself between caribou_cuda_shard_begin and caribou_cuda_shard_finish (caribou_cuda_shard_gather_buffer: device
+ * memory, [world][n_streams * 4 * n_sos] doubles, slot `rank` written by begin, all slots read by finish), or lets
+ * caribou_cuda_shard_exchange_local do it for `world` contexts of ONE process (one per GPU, peer copies). */
+#define CARIBOU_CUDA_SHARD_ID_BYTES 128
+int    caribou_cuda_shard_unique_id(void* id /* CARIBOU_CUDA_SHARD_ID_BYTES */);
+int    caribou_cuda_shard_init(caribou_cuda_ctx* ctx, int rank, int world, const void* id);
+int    caribou_cuda_shard_attach_comm(caribou_cuda_ctx* ctx, int rank, int world, void* nccl_comm);
+int    caribou_cuda_shard_set_mode(caribou_cuda_ctx* ctx, int mode);   /* 0: all-gather (default), 1: send/recv chain */
+int    caribou_cuda_shard_submit(caribou_cuda_ctx* ctx, int in_kind, const void* in, size_t n_samples,
+                                 size_t in_stride_elems, void* out, size_t out_stride_elems);
+int    caribou_cuda_shard_begin(caribou_cuda_ctx* ctx, int in_kind, const void* in, size_t n_samples,
+                                size_t in_stride_elems, void* out, size_t out_stride_elems);
+void*  caribou_cuda_shard_gather_buffer(caribou_cuda_ctx* ctx, size_t* bytes_per_rank);
+int    caribou_cuda_shard_finish(caribou_cuda_ctx* ctx);
+int    caribou_cuda_shard_exchange_local(caribou_cuda_ctx* const* ctxs, int world);
+/* Device times of the last sharded call when profiling is enabled (caribou_cuda_set_profiling): pass 1, and
+ * hand-off + fix-up, in milliseconds.  Synchronises the context. */
+int    caribou_cuda_shard_profile(caribou_cuda_ctx* ctx, float* pass_ms, float* handoff_ms);
+
 /* ---------------------------------------------------------------- host-side filter design
  * Iir::Butterworth::LowPass<order>::setup(fs, fc) (LC/iir/iir/Butterworth.cpp:49-68,107-117,
  * PoleFilter.cpp:47-90, Cascade.cpp:94-118).  Writes (order+1)/2 rows of (b0,b1,b2,a0,a1,a2);
@@ -230,6 +287,14 @@ int caribou_cuda_smi_read(caribou_cuda_smi* dev, int channel,
                           caribou_cuda_sample_meta* metadata, size_t length_samples);
 /* size_t caribou_smi_get_native_batch_samples(caribou_smi_st*)     LC/caribou_smi/caribou_smi.c:765-769 */
 size_t caribou_cuda_smi_get_native_batch_samples(caribou_cuda_smi* dev);
+
+/* int CaribouLiteRadio::ReadSamples(std::complex<float>* samples, size_t num_to_read, uint8_t* meta)
+ *                                                LC/CaribouLite.hpp:188-189, LC/CaribouLiteRadioCpp.cpp:72-95
+ * CF32 (= native / 4096.0f) and the sync metadata of one read in one call and one device synchronisation; `samples`
+ * is num_to_read (float re, float im) pairs, `meta` may be NULL.  The radio's persistent _read_samples /
+ * _read_metadata buffers live on the device.  Returns what cariboulite_radio_read_samples returns; nothing is
+ * written for a result <= 0. */
+int caribou_cuda_radio_read_cf32(caribou_cuda_smi* dev, int channel, float* samples, uint8_t* meta, size_t num_to_read);
 
 /* SoapySDR::Stream's RX half (LC/soapy_api/CaribouliteStream.hpp:64-137): format switch, MTU clamp,
  * three never-reset order-6 Butterworth filter pairs, Q16 ordering. */

@@ -6,7 +6,9 @@
 
 One continuous stream of G * calls * 2^log2 words, device-generated in place, time-chunked over the G ranks;
 fused unpack -> order-6 Butterworth (fc = 10 kHz, the narrowest reference filter) -> decimate by 8 with the
-IIR state handed from GPU to GPU.  Rank 0 gathers every rank's output and compares the WHOLE stream with the
+IIR state handed from GPU to GPU ON THE DEVICE: caribou_cuda_shard_submit (ncclAllGather or the ncclSend/ncclRecv
+chain on the context's stream, composition kernel, fix-up from device memory; the communicator is created inside
+the library from a unique id that rank 0 ships through torch.distributed).  Rank 0 gathers every rank's output and compares the WHOLE stream with the
 sequential CPU oracle (tolerance: 1e-5 of signal RMS per rail, north_star); it also prints the time of the
 hand-off.  Prints one JSON line.  tests/test_gpu_multi.py runs it when the box has >= 2 GPUs."""
 import argparse
@@ -32,7 +34,6 @@ def main():
     import torch
     import torch.distributed as dist
     import cariboulite_b200 as cb
-    from cariboulite_b200 import shard
     from oracle import pyoracle as po
 
     rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
@@ -41,22 +42,27 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     n, D = 1 << a.log2_words, 8
     sos = cb.butter_lowpass(a.order, 4e6, a.fc)
-    ti, tq = po.tone_tables()
+    ti, tq = cb.tone_tables()
     ctx = cb.Context(device=local, sos=sos, decimation=D, parity=cb.PARITY_F32, out_format=cb.FMT_CF32)
-    ss = shard.ShardedStream(ctx, mode=a.mode, device=dev)
+    ids = [cb.shard_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(ids, src=0)
+    ctx.shard_init(rank, world, ids[0])
+    ctx.shard_set_mode(cb.SHARD_CHAIN if a.mode == "chain" else cb.SHARD_ALLGATHER)
+    ctx.set_profiling(True)
     d_w = torch.empty(n, dtype=torch.int32, device=dev)
     d_out = torch.zeros((a.calls, n // D, 2), dtype=torch.float32, device=dev)
-    t_hand = []
+    t_hand, t_dev = [], []
     for call in range(a.calls):
         n0 = (call * world + rank) * n
         ctx.synth_words(d_w, n, n0=n0, tone_i=ti, tone_q=tq)
         torch.cuda.synchronize(dev)
         dist.barrier()
         t0 = time.perf_counter()
-        ss.process(cb.IN_WORDS, d_w, n, d_out[call])
-        ctx.wait()
+        ctx.shard_submit(cb.IN_WORDS, d_w, n, d_out[call])
+        assert ctx.wait()[0] == n
         torch.cuda.synchronize(dev)
         t_hand.append(time.perf_counter() - t0)
+        t_dev.append(ctx.shard_profile())
     # gather on rank 0: [world][calls][n/D][2]
     allout = [torch.empty_like(d_out) for _ in range(world)] if rank == 0 else None
     dist.gather(d_out, allout, dst=0)
@@ -83,7 +89,9 @@ def main():
         ok = bool(np.all(e <= 1e-5) and wmax <= 1e-5)
         print(json.dumps({"world": world, "mode": a.mode, "words_per_rank_per_call": n, "calls": a.calls, "ok": ok,
                           "err": err, "fixup_samples": int(ctx.fixup_samples(n)),
-                          "process_ms_per_call": [round(t * 1e3, 3) for t in t_hand]}), flush=True)
+                          "process_ms_per_call": [round(t * 1e3, 3) for t in t_hand],
+                          "pass_ms": [round(t[0], 4) for t in t_dev], "handoff_fixup_ms": [round(t[1], 4) for t in t_dev]}),
+              flush=True)
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.broadcast(flag, src=0)
     ctx.close()

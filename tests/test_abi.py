@@ -74,3 +74,39 @@ def test_compute_fails_loudly_without_a_gpu(cb):
     assert "no CUDA device" in str(e.value) or "CUDA" in str(e.value)
     lib = cb.lib()
     assert lib.caribou_cuda_smi_open(0, 0, 0) is None or True   # must not crash; a device is needed later
+
+
+def test_tone_tables_of_the_package_are_the_generators(cb, po):
+    """bench.py and the multi-GPU scripts take the synthetic generator's tone tables from the package (the B200 arm
+    never imports the oracle); they must be the tables the CPU generator uses."""
+    a, b = cb.tone_tables()
+    c, d = po.tone_tables()
+    np.testing.assert_array_equal(a, c)
+    np.testing.assert_array_equal(b, d)
+
+
+def test_stream_result_layout_and_mem_io(cb, tmp_path):
+    src = tmp_path / "layout2.c"
+    src.write_text('''
+#include <stdio.h>
+#include <stddef.h>
+#include "caribou_cuda.h"
+int main(void) {
+  printf("%zu %zu %d %d\\n", sizeof(caribou_cuda_stream_result), offsetof(caribou_cuda_stream_result, first_bad_chunk),
+         CARIBOU_CUDA_MEM_IO(CARIBOU_CUDA_MEM_HOST_PINNED, CARIBOU_CUDA_MEM_HOST), CARIBOU_CUDA_SHARD_ID_BYTES);
+  return 0; }''')
+    exe = tmp_path / "layout2"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    v = [int(x) for x in subprocess.check_output([str(exe)], text=True).split()]
+    assert v == [C.sizeof(cb.StreamResult), cb.StreamResult.first_bad_chunk.offset,
+                 cb.MEM_IO(cb.MEM_HOST_PINNED, cb.MEM_HOST), cb.SHARD_ID_BYTES]
+
+
+def test_sharding_needs_a_context_and_fails_loudly(cb):
+    """No GPU: the sharding entry points reject a null context instead of crashing; the NCCL binding is lazy, so
+    the library loads where libnccl is absent."""
+    L = cb.lib()
+    assert L.caribou_cuda_shard_init(None, 0, 1, None) == cb.ERR
+    assert L.caribou_cuda_shard_submit(None, 0, None, 0, 0, None, 0) == cb.ERR
+    assert L.caribou_cuda_shard_finish(None) == cb.ERR
+    assert L.caribou_cuda_stream_results(None, None) == cb.ERR

@@ -86,6 +86,33 @@ def test_q16_reference_ordering(cb, po, torch_cuda, fmt):
     assert np.all(rel_rms(got, ref) <= TOL)
 
 
+@pytest.mark.parametrize("fmt", ["CS16", "CF32", "CF64", "CS8"])
+@pytest.mark.parametrize("name,D", [("ref50k", 8), ("c3", 4)])
+def test_q16_reference_ordering_with_decimation(cb, po, torch_cuda, fmt, name, D):
+    """The staged kernel's OUT_Q16_* epilogues: reference ordering (truncate to int16 after the filter) with the
+    decimation fused into the store, against filter_cs16_q16(...)[::D] of the oracle."""
+    torch = torch_cuda
+    n = 1 << 18
+    sos = po.butter_lowpass_sos(*FILTERS[name])
+    cs16 = _words_to_cs16(po, po.gen_words(n))
+    q = po.filter_cs16_q16(sos, cs16)[::D]
+    code = {"CS16": cb.FMT_CS16, "CF32": cb.FMT_CF32, "CF64": cb.FMT_CF64, "CS8": cb.FMT_CS8}[fmt]
+    ref = {"CS16": q, "CF32": po.cs16_to_cf32(q), "CF64": po.cs16_to_cf64(q), "CS8": po.cs16_to_cs8(q)}[fmt]
+    for kind, x in ((cb.IN_CS16, _dev(torch, cs16)), (cb.IN_WORDS, _dev(torch, po.gen_words(n).view(np.int32)))):
+        out = torch.zeros((n // D, 2), dtype=getattr(torch, np.dtype(cb.FMT_DTYPE[code]).name), device="cuda:0")
+        with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_Q16, out_format=code) as ctx:
+            ctx.filter_submit(kind, x, n, out)
+            ret, res = ctx.wait()
+            assert ret == n and res.n_filtered == n // D
+        got = out.cpu().numpy()
+        diff = np.abs(got.astype(np.float64) - ref.astype(np.float64))
+        lsb = {"CS16": 1, "CF32": 1 / 4096, "CF64": 1 / 4096, "CS8": 1}[fmt]
+        assert diff.max() <= lsb * 1.0001, kind
+        assert np.mean(diff > 0) < 1e-4, kind
+        if fmt != "CS8":
+            assert np.all(rel_rms(got, ref) <= TOL), kind
+
+
 def test_state_carries_across_calls_and_matches_reference(cb, po, torch_cuda):
     """Chunking never changes results; get_state returns the reference's DF-II (v1,v2) values."""
     torch = torch_cuda

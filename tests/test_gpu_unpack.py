@@ -99,9 +99,9 @@ def test_ragged_lengths(cb, po, torch_cuda, n):
         _check_single(cb, po, torch_cuda, raw[:-1], 0, 4096)   # byte count not a multiple of 4
 
 
-@pytest.mark.parametrize("B", [1, 8, 4096])
+@pytest.mark.parametrize("B", [1, 8, 4096, 131072])
 def test_dual_channel_demux(cb, po, torch_cuda, B):
-    n = 1 << 17
+    n = 1 << 17 if B < 131072 else 1 << 20        # B = 131072: MTU-interleaved, SURVEY 8a A9's secondary case
     a = po.gen_words(n // 2, channel=0)
     b = po.gen_words(n // 2, channel=1)
     w = np.empty(n, np.uint32)
@@ -136,3 +136,51 @@ def test_host_memory_path(cb, po, torch_cuda):
     assert ret == eret
     np.testing.assert_array_equal(cs16, ecs)
     np.testing.assert_array_equal(meta, emeta)
+
+
+@pytest.mark.parametrize("drop", [0, 2, 5])
+@pytest.mark.parametrize("pinned_in", [False, True])
+def test_host_memory_bounce_path_leaves_untouched_slots(cb, po, torch_cuda, drop, pinned_in):
+    """Pageable outputs: one synchronisation, the caller's arrays receive exactly the slots the reference writes
+    (sentinels elsewhere), also with the input in page-locked memory (CARIBOU_CUDA_MEM_IO, what the shims use)."""
+    torch = torch_cuda
+    w = po.gen_words(100000)
+    w[40000] ^= 0x80000000
+    raw = np.ascontiguousarray(w.view(np.uint8)[drop:])
+    n = raw.size // 4 + 2
+    cs16 = np.full((n, 2), SENT16, np.int16)
+    meta = np.full(n, 0x5A, np.uint8)
+    cf32 = np.full((n, 2), -7.0, np.float32)
+    src, mem = raw, None
+    if pinned_in:
+        src = torch.from_numpy(np.concatenate([raw, np.zeros((-raw.size) % 16 + 16, np.uint8)])).pin_memory()
+        mem = cb.MEM_IO(cb.MEM_HOST_PINNED, cb.MEM_HOST)
+    with cb.Context(chunk_bytes=16384) as ctx:
+        ctx.unpack_submit(src, nbytes=raw.size, cs16=cs16, meta=meta, cf32=cf32, mem=mem)
+        ret, res = ctx.wait()
+    eret, ecs, emeta = _oracle(po, raw, 0, 16384)
+    assert ret == eret
+    np.testing.assert_array_equal(cs16, ecs)
+    np.testing.assert_array_equal(meta, emeta)
+    written = ~((ecs[:, 0] == np.int16(SENT16)) & (ecs[:, 1] == np.int16(SENT16)))
+    np.testing.assert_array_equal(cf32, np.where(written[:, None], po.cs16_to_cf32(ecs), np.float32(-7.0)))
+
+
+def test_c1_at_its_stated_size(cb, po, torch_cuda):
+    """BASELINE.json configs[0]: a 4 MSPS S1G-only capture of 1 s = 2^22 words (16 MiB), unpack -> CS16 + meta + CF32,
+    no filter: the whole capture against the reference's read loop, bit for bit."""
+    torch = torch_cuda
+    n = 1 << 22
+    w = po.gen_words(n)
+    d_w = torch.from_numpy(w.view(np.int32)).to("cuda:0")
+    cs16 = torch.zeros((n, 2), dtype=torch.int16, device="cuda:0")
+    meta = torch.zeros(n, dtype=torch.uint8, device="cuda:0")
+    cf32 = torch.zeros((n, 2), dtype=torch.float32, device="cuda:0")
+    with cb.Context() as ctx:
+        ctx.unpack_submit(d_w, cs16=cs16, meta=meta, cf32=cf32)
+        ret, res = ctx.wait()
+    r_ret, r_cs16, r_meta, _ = po.smi_read(w.view(np.uint8), n)
+    assert ret == r_ret == n and res.n_sync == 2 and res.n_invalid == 0      # S at n = 0 and n = 4e6
+    np.testing.assert_array_equal(cs16.cpu().numpy(), r_cs16[:n])
+    np.testing.assert_array_equal(meta.cpu().numpy(), r_meta[:n])
+    np.testing.assert_array_equal(cf32.cpu().numpy(), po.cs16_to_cf32(r_cs16[:n]))
