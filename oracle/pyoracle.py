@@ -339,6 +339,8 @@ def ref():
         for f in ("ref_dev_smi_read", "ref_dev_radio_read"):
             getattr(R, f).restype = C.c_int
             getattr(R, f).argtypes = [_p, _p, _p, C.c_size_t]
+        R.ref_dev_read_only.restype = C.c_long
+        R.ref_dev_read_only.argtypes = [_p, C.c_size_t]
         R.ref_dev_smi_write.restype = C.c_int
         R.ref_dev_smi_write.argtypes = [_p, _p, C.c_size_t]
         R.ref_dev_read_back.restype = C.c_long
@@ -407,6 +409,20 @@ class RefDev:
                 meta[:] = sentinel & 0xFF
         ret = ref().ref_dev_smi_read(self.h, _ptr(cs16), _ptr(meta), n)
         return ret, cs16, meta
+
+    def rewind(self):
+        ref().ref_dev_rewind(self.h)
+
+    def read_only(self, n):
+        """The read(2) loop of caribou_smi_read without the decode (what the memfd copy costs)."""
+        return ref().ref_dev_read_only(self.h, n)
+
+    def smi_read_into(self, cs16, meta, n):
+        """caribou_smi_read into caller-owned arrays (no allocation in the timed region)."""
+        return ref().ref_dev_smi_read(self.h, _ptr(cs16), _ptr(meta), n)
+
+    def stream_read_into(self, buf, n):
+        return ref().ref_stream_read(self.h, _ptr(buf), n)
 
     def smi_write(self, cs16):
         """The reference's caribou_smi_write on the memfd: (return value, the 32-bit words it handed to the fd)."""

@@ -145,6 +145,22 @@ long ref_dev_read_back(void* h, uint8_t* out, size_t cap)
     return (long)done;
 }
 
+// The read(2) loop of caribou_smi_read alone (same chunking into the device's temp buffer, no decode): what the
+// memfd copy costs, so that the CPU baseline can be quoted with and without it (BASELINE.md section 3 run 1).
+long ref_dev_read_only(void* h, size_t length_samples)
+{
+    RefDev* d = (RefDev*)h;
+    caribou_smi_st* smi = &d->sys->smi;
+    size_t left = length_samples * CARIBOU_SMI_BYTES_PER_SAMPLE, done = 0;
+    while (left) {
+        const size_t cur = left > smi->native_batch_len ? smi->native_batch_len : left;
+        const ssize_t r = read(smi->filedesc, smi->read_temp_buffer, cur);
+        if (r <= 0) break;
+        done += (size_t)r; left -= (size_t)r;
+    }
+    return (long)(done / CARIBOU_SMI_BYTES_PER_SAMPLE);
+}
+
 // cariboulite_radio_read_samples-shaped call (through the shim above).
 int ref_dev_radio_read(void* h, int16_t* cs16, uint8_t* meta, size_t length_samples)
 {
@@ -189,9 +205,11 @@ template <class F>
 static size_t rail_loop(F& f, const int16_t* iq, int rail, size_t n, size_t pos, int D, float* out2)
 {
     size_t m = 0;
+    size_t ph = pos % (size_t)D;                      // decimation phase carried, not divided per sample
     for (size_t k = 0; k < n; k++) {
         const float y = f.template filter<float>((float)iq[2 * k + rail] / 4096.0f);
-        if ((pos + k) % (size_t)D == 0) { out2[2 * m + rail] = y; m++; }
+        if (ph == 0) { out2[2 * m + rail] = y; m++; }
+        if (++ph == (size_t)D) ph = 0;
     }
     return m;
 }
