@@ -119,6 +119,18 @@ struct IirTailParams {
 #ifndef CBL_IIR_K3_WARPS
 #define CBL_IIR_K3_WARPS 12      // float-staged parallel-form kernels of 3 sections: 8 (255 registers) or 12 (168, small spills)
 #endif
+// Look-back and phase 3 of a tile run one tile late, after phases 1-2 of the warp's next tile, out of the other half of
+// a double-buffered output stage (CBL_IIR_DEFER = 1, the default).  The alternative (0) runs them at once: one
+// stage per warp, so runs of up to kMaxNK kept outputs fit (256 samples at D = 8 instead of 160), tickets taken one
+// at a time.  Measured (profiles/r2_sweeps.txt, sweep 31): wide filters at D <= 4 and from three sections on gain
+// 3-7 %, the C4 kernel loses 3 % (1.092 against 1.056 ms) and filters whose look-back reads two tiles lose 8-25 % -
+// the wait for a neighbour's aggregate is real time there.  With the two-ahead ticket pipeline of the deferred form
+// it is far worse (1.52 ms): a warp then holds two consecutive tiles and processes them an iteration apart.
+#ifndef CBL_IIR_DEFER
+#define CBL_IIR_DEFER 1
+#endif
+constexpr bool kIirDefer = CBL_IIR_DEFER != 0;
+constexpr int kIirStageBufs = kIirDefer ? 2 : 1;
 __host__ __device__ constexpr int iir_target_warps(int K, bool y32) { return (K <= 2 && y32) ? 12 : ((K == 3 && y32) ? CBL_IIR_K3_WARPS : 8); }
 __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
 {
@@ -127,7 +139,7 @@ __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
     if (D == 4 && CBL_IIR_LT_D4 != 0) return CBL_IIR_LT_D4;
     const int slot = y32 ? 256 : 512;                                    // bytes per kept output of a warp
     const int per_warp = (232448 - 1024) / iir_target_warps(K, y32) - 2 * 4096 - 2 * 2 * kMaxK * 8 - 16;   // minus ring, scratch, barriers
-    int nk = per_warp / (2 * slot);
+    int nk = per_warp / (kIirStageBufs * slot);
     if (nk > kMaxNK) nk = kMaxNK;
     nk &= ~3;                                                             // phase 3 works in chunks of 4 kept outputs
     int lt = (nk * D / 32) * 32;
@@ -142,8 +154,11 @@ __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
 #define CBL_RR_ENABLE 1          // 0: staged kernel everywhere (A/B builds)
 #endif
 #ifndef CBL_RR_LT
-#define CBL_RR_LT 64
-#endif
+#define CBL_RR_LT 256          // samples per run of the rerun kernel from three sections on (the input is fetched
+#endif                         // twice, not kept in shared memory: iir_rerun.cuh)
+#ifndef CBL_RR_LT12
+#define CBL_RR_LT12 128        // ... for one or two sections: these are close to the HBM bound, and the second fetch
+#endif                         // of a tile hits L2 more often when less data is in flight (sweep: profiles/r2_sweeps.txt)
 #ifndef CBL_RR_WARPS
 #define CBL_RR_WARPS 12
 #endif
@@ -156,7 +171,7 @@ __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
 #ifndef CBL_RR_P3U
 #define CBL_RR_P3U 1             // chunks of four outputs per iteration of the rerun kernel's phase-3 loop
 #endif
-constexpr int kRerunLT   = CBL_RR_LT;
+__host__ __device__ constexpr int iir_rerun_len(int K) { return K <= 2 ? CBL_RR_LT12 : CBL_RR_LT; }
 constexpr int kRerunP3Unroll = CBL_RR_P3U;
 __host__ __device__ constexpr bool iir_is_rerun(int K, int D, bool par)
 {

@@ -53,6 +53,18 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* tma
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
         ::"r"(dst), "l"(tmap), "r"(x), "r"(y), "r"(z), "r"(bar) : "memory");
 }
+// the same with an L2 eviction-priority hint (the rerun kernel fetches every tile twice: the first fetch asks L2 to keep
+// the lines, the second one releases them).  The policy words are the fixed encodings createpolicy.fractional
+// produces for a fraction of 1.0 (the values CUTLASS's CacheHintSm90 carries).
+constexpr unsigned long long kL2EvictFirst = 0x12F0000000000000ull;
+constexpr unsigned long long kL2EvictLast  = 0x14F0000000000000ull;
+__device__ __forceinline__ void tma_load_3d_hint(uint32_t dst, const CUtensorMap* tmap, int x, int y, int z, uint32_t bar,
+                                                 unsigned long long policy)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3, %4}], [%5], %6;"
+        ::"r"(dst), "l"(tmap), "r"(x), "r"(y), "r"(z), "r"(bar), "l"(policy) : "memory");
+}
 // look-back descriptor slots: relaxed, L2-coherent 8-byte accesses; the value is its own "ready" flag
 __device__ __forceinline__ unsigned long long ld_desc(const double* p)
 {
@@ -217,9 +229,9 @@ struct IirCfg {
     static constexpr int STAGES = (NSTEP < RSTG) ? NSTEP : RSTG;
     static constexpr int RING_BYTES    = STAGES * 4096;
     static constexpr int YSLOT_BYTES   = Y32 ? 256 : 512;      // one kept output of all 32 lanes: float2 / 2 doubles each
-    static constexpr int YSTAGE_BYTES  = NK * YSLOT_BYTES;     // one tile's zero-state outputs; two of them per warp
+    static constexpr int YSTAGE_BYTES  = NK * YSLOT_BYTES;     // one tile's zero-state outputs; kIirStageBufs of them per warp
     static constexpr int SCRATCH_BYTES = 2 * S * 8 * 2;        // S_in broadcast + spare
-    static constexpr int WARP_BYTES = RING_BYTES + 2 * YSTAGE_BYTES + SCRATCH_BYTES;
+    static constexpr int WARP_BYTES = RING_BYTES + kIirStageBufs * YSTAGE_BYTES + SCRATCH_BYTES;
     // 227 KiB per CTA minus the alignment slack of the carve-up
     static constexpr int SMEM_WARPS = (232448 - 1024) / (WARP_BYTES + STAGES * 8);
     static constexpr int REG_WARPS  = iir_reg_warps(K, D, PAR, Y32);
@@ -276,8 +288,8 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     // shared-memory carve-up, as 32-bit shared-window addresses (1024-byte aligned for the 128B swizzle)
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t ring_u32 = base + warp * C::RING_BYTES;
-    const uint32_t ystage0 = base + C::WPC * C::RING_BYTES + warp * (2 * C::YSTAGE_BYTES);
-    const uint32_t scratch = base + C::WPC * (C::RING_BYTES + 2 * C::YSTAGE_BYTES) + warp * C::SCRATCH_BYTES;
+    const uint32_t ystage0 = base + C::WPC * C::RING_BYTES + warp * (kIirStageBufs * C::YSTAGE_BYTES);
+    const uint32_t scratch = base + C::WPC * (C::RING_BYTES + kIirStageBufs * C::YSTAGE_BYTES) + warp * C::SCRATCH_BYTES;
     const uint32_t bar_u32 = base + C::WPC * C::WARP_BYTES + warp * C::STAGES * 8;
 
     if (lane == 0) {
@@ -318,7 +330,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     uint32_t* const ticket = P.ticket + __ldg(P.ticket + 32 + lane);      // words 32..63 of the ticket block stay zero
     if (lane == 0) {
         tile = take_ticket(ticket);
-        next = take_ticket(ticket);
+        if (kIirDefer) next = take_ticket(ticket);      // (non-deferred form: one ticket at a time, see the loop)
     }
     tile = __shfl_sync(0xffffffffu, tile, 0);
     uint32_t stream = tile / tps, tis = tile - stream * tps;
@@ -346,9 +358,15 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
         double f[2][S];
         double va[K][2], vb[K][2];
         if (have) {
-            if (lane == 0) next2 = take_ticket(ticket);      // the tile after `next`; consumed one iteration later
-            nstream = next / tps;
-            ntis = next - nstream * tps;
+            // deferred form: the tile after `next`, consumed one iteration later.  Non-deferred form: `next` itself,
+            // first looked at when phase 1 requests the next tile's boxes - a warp that held two consecutive tiles
+            // would process them a whole iteration apart, and the neighbour that needs the second one's aggregate
+            // for its look-back would sit waiting for it
+            if (lane == 0) { if (kIirDefer) next2 = take_ticket(ticket); else next = take_ticket(ticket); }
+            if (kIirDefer) {
+                nstream = next / tps;
+                ntis = next - nstream * tps;
+            }
             const uint32_t ystage = ystage0 + buf * C::YSTAGE_BYTES;
 
             // ---- phase 1: zero-state pass over the run (started at s*, see iir.cuh)
@@ -419,8 +437,15 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                 __syncwarp();
                 if (lane == 0) {
                     const int ls = step + C::STAGES;                 // the box that follows the ones in flight
-                    if (ls < C::NSTEP) issue(stream, tis, ls, st);
-                    else if (next < P.total_tiles) issue(nstream, ntis, ls - C::NSTEP, st);
+                    if (ls < C::NSTEP) {
+                        issue(stream, tis, ls, st);
+                    } else {
+                        if (!kIirDefer) {        // the ticket taken at the top of the tile is looked at here for the first time
+                            nstream = next / tps;
+                            ntis = next - nstream * tps;
+                        }
+                        if (next < P.total_tiles) issue(nstream, ntis, ls - C::NSTEP, st);
+                    }
                 }
                 gstep++;
             }
@@ -430,6 +455,10 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
         // L2 round trip hides behind the scan.
         const int comp = lane < 2 * S ? lane : 0;
         unsigned long long pre = kDescEmpty;
+        if (!kIirDefer) {          // the tile in hand is the one whose look-back follows
+            owe = live;
+            ptile = tile; pstream = stream; ptis = tis;
+        }
         if (owe && ptis != 0)
             pre = ld_desc((P.chained ? P.desc_incl : P.desc_agg) + (size_t)(ptile - 1) * (2 * S) + comp);
 
@@ -472,9 +501,16 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             }
         }
 
-        // ---- the owed tile: decoupled look-back, then phase 3 out of the other half of the output stage
+        if (!kIirDefer && live) {
+#pragma unroll
+            for (int r = 0; r < 2; r++)
+#pragma unroll
+                for (int c = 0; c < S; c++) pf[r][c] = f[r][c];
+        }
+        // ---- the owed tile: decoupled look-back, then phase 3 out of the other half of the output stage (deferred
+        // form) / out of the stage phase 1 has just filled
         if (owe) {
-            const uint32_t ystage = ystage0 + (buf ^ 1u) * C::YSTAGE_BYTES;
+            const uint32_t ystage = ystage0 + (kIirDefer ? (buf ^ 1u) : 0u) * C::YSTAGE_BYTES;
             // state entering the tile, component `lane` (< 2S) per lane
             const int crail = comp / S, crow = comp % S;
             // Every lane walks the look-back (lanes >= 2S repeat component 0: same addresses, no extra traffic) and
@@ -718,20 +754,22 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             __syncwarp();   // this half of the output stage and the scratch are free again
         }
         if (!have) break;
-        owe = live;
-        ptile = tile; pstream = stream; ptis = tis;
-        if (live) {
+        if (kIirDefer) {
+            owe = live;
+            ptile = tile; pstream = stream; ptis = tis;
+            if (live) {
 #pragma unroll
-            for (int r = 0; r < 2; r++)
+                for (int r = 0; r < 2; r++)
 #pragma unroll
-                for (int c = 0; c < S; c++) pf[r][c] = f[r][c];
-            buf ^= 1u;
+                    for (int c = 0; c < S; c++) pf[r][c] = f[r][c];
+                buf ^= 1u;
+            }
         }
         // lane 0's view of the ticket pipeline becomes everybody's current tile
         tile = __shfl_sync(0xffffffffu, next, 0);
         stream = __shfl_sync(0xffffffffu, nstream, 0);
         tis = __shfl_sync(0xffffffffu, ntis, 0);
-        next = next2;
+        if (kIirDefer) next = next2;
     }
 }
 

@@ -3,49 +3,57 @@
 //
 // The staged kernel (iir_kernel.cuh) keeps the zero-state outputs of a run in shared memory and corrects each
 // kept one with R[m] . s0 later.  That pays when few outputs are kept; at D = 1 every sample is kept, the stage
-// limits a run to 32 samples (five times the per-tile work of the D = 8 kernel per sample) and every output costs
-// a shared-memory round trip plus 2S correction FMAs.  Here the INPUT tile stays in shared memory instead (4 bytes
-// per sample, not 8-16): phase 1 filters the run from the steady state for its end state only (2K FMAs per rail
-// and sample, no outputs), phases 2 and the look-back are those of the staged kernel, and phase 3 filters the
-// same run again from its true entry state s0 - now in exactly the reference's sample order - producing the
-// outputs straight into 32-byte stores.  FP64 work per complex sample at D = 1: 4K + 8K + 2 instead of
-// 8K + 4K + 2 plus the per-tile work of 32-sample runs; shared memory per warp: two input tiles.
+// limits a run to 32 samples and every output costs a shared-memory round trip plus 2S correction FMAs.  Here a
+// run is filtered TWICE instead: phase 1 from the steady state for its end state only (2K FMAs per rail and
+// sample, no outputs), phase 2 and the look-back are those of the staged kernel, and phase 3 filters the same
+// run again from its true entry state s0 - now in exactly the reference's sample order - producing the outputs
+// straight into 32-byte stores.  FP64 work per complex sample at D = 1: 4K + 8K + 2.
 //
-//   iteration i of a warp:   phase 1-2 of tile i (ring slot i & 1)
-//                            ticket for tile i+1 (its round trip hides behind phase 3)
-//                            look-back + phase 3 of tile i-1 (the other slot)      <- one tile late, as before
-//                            that slot is free: the TMA boxes of tile i+1 are requested into it
-// The request is consumed right away by the next iteration's phase 1; the other warps of the SMSP cover its
-// latency (a third slot buys a whole iteration of slack but costs a quarter of the warps: slower, sweep 22).
-// Tickets are taken half an iteration ahead, not two iterations as in the staged kernel: an iteration is long
-// here, and the further ahead tiles are handed out the further the warps that own neighbouring tiles drift
-// apart - with narrow filters, whose look-back reads several predecessors, a fifth of the time went into
-// waiting for aggregates (sweep 23).
+// The input is FETCHED twice as well: a tile goes through phase 1, the scan and its look-back, and is then
+// requested a second time for phase 3 - a few microseconds after the first request, so the second one is an L2
+// hit (ncu: DRAM read traffic = the input once).  Shared memory therefore holds only a small ring of 4 KiB TMA
+// boxes per warp, the run length is not tied to it (256 samples; 64 fitted when two whole tiles had to stay
+// resident), and the per-tile work - warp scan, look-back, entry states, tickets - which was a third of the time
+// at 64-sample runs is spread over four times as many samples; the look-back window shrinks with it (2 tiles
+// instead of 6 for the narrowest reference filter) and CF32 input is no longer held to 7 warps by its 8-byte samples.
+//
+// Phase 3 follows the look-back at once (the first version ran it one tile late, like the staged kernel, to keep
+// a warp from idling on a predecessor that is a little behind; the second fetch then came a whole tile later and
+// missed L2 every time - ncu: 8.6 GB read for 4.3 GB of input).  A tile is ~35k cycles long now and its predecessor
+// was claimed a ticket earlier: the aggregate it waits for is practically always there.
+//
+//   one tile of a warp:   phase 1 out of the ring (box b + R requested when box b is done; from box N - R on the
+//                         requests are the tile's own boxes again, for phase 3)
+//                         phase 2, aggregate out, look-back, entry states
+//                         ticket for the next tile (its round trip hides behind phase 3)
+//                         phase 3 out of the ring (from box N - R on the requests are the next tile's first boxes)
 #pragma once
 #include "iir_kernel.cuh"
 
 namespace cbl {
 
+#ifndef CBL_RR_RING
+#define CBL_RR_RING 4            // 4 KiB boxes in a warp's ring
+#endif
+
 template <int K, int D, int IN>
 struct RerunCfg {
     static constexpr int S     = 2 * K;
-    static constexpr int LT    = kRerunLT;
+    static constexpr int LT    = iir_rerun_len(K);
     static constexpr int NK    = LT / D;
-    static constexpr int SPS   = (IN == IN_CF32) ? 16 : 32;   // samples per 128-byte row step
+    static constexpr int SPS   = (IN == IN_CF32) ? 16 : 32;   // samples per 128-byte row step = per box
     static constexpr int NSTEP = LT / SPS;                    // 4 KiB boxes per tile
-    static constexpr int NBUF  = 2;                           // input tiles a warp holds
-    static constexpr int HALF_BYTES    = NSTEP * 4096;        // one tile
-    static constexpr int RING_BYTES    = NBUF * HALF_BYTES;
+    static constexpr int R     = CBL_RR_RING < NSTEP ? CBL_RR_RING : NSTEP;
+    static constexpr int RING_BYTES    = R * 4096;
     static constexpr int SCRATCH_BYTES = 2 * S * 8 * 2;
     static constexpr int WARP_BYTES = RING_BYTES + SCRATCH_BYTES;
-    static constexpr int SMEM_WARPS = (232448 - 1024) / (WARP_BYTES + NBUF * NSTEP * 8);
-    // registers (cuobjdump -res-usage): 113-118 (K <= 2), 156 (K = 3), 200 (K = 4) unconstrained; 12 warps allow 168,
-    // which K = 4 also fits without spilling (sweep 27: 4.85 -> 4.31 ms); CF32 input is limited to 7 warps by shared memory
+    static constexpr int SMEM_WARPS = (232448 - 1024) / (WARP_BYTES + R * 8);
+    // registers (cuobjdump -res-usage): 12 warps allow 168 per thread
     static constexpr int REG_WARPS  = (K <= 2) ? CBL_RR_WARPS : (K == 3 ? CBL_RR_WARPS3 : CBL_RR_WARPS4);
     static constexpr int WPC = SMEM_WARPS < REG_WARPS ? SMEM_WARPS : REG_WARPS;
     static_assert(WPC >= 1, "a warp's buffers do not fit shared memory");
     static_assert(LT % 32 == 0 && (D == 1 || D == 2), "phase 3 works in groups of 8 or 16 samples: whole chunks of 4 kept outputs");
-    static constexpr int SMEM_BYTES = WPC * WARP_BYTES + WPC * NBUF * NSTEP * 8 + 1024;
+    static constexpr int SMEM_BYTES = WPC * WARP_BYTES + WPC * R * 8 + 1024;
 };
 
 // four consecutive outputs of one lane, already scaled (y = gain * y/G + out_bias), in the stream's output format
@@ -132,16 +140,17 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     constexpr int S = C::S;
     constexpr bool PAR = true;
     constexpr bool INJECT = IN != IN_CF32;
+    constexpr int N = C::NSTEP, R = C::R;
     extern __shared__ uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t ring_u32 = base + warp * C::RING_BYTES;
     const uint32_t scratch = base + C::WPC * C::RING_BYTES + warp * C::SCRATCH_BYTES;
-    const uint32_t bar_u32 = base + C::WPC * C::WARP_BYTES + warp * (C::NBUF * C::NSTEP) * 8;
+    const uint32_t bar_u32 = base + C::WPC * C::WARP_BYTES + warp * R * 8;
 
     if (lane == 0) {
 #pragma unroll
-        for (int s = 0; s < C::NBUF * C::NSTEP; s++) mbar_init(bar_u32 + 8 * s, 1);
+        for (int s = 0; s < R; s++) mbar_init(bar_u32 + 8 * s, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -151,22 +160,19 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 
     const uint32_t inj_xor = P.inj_xor, inj_mul = P.inj_mul;
 
-    // all boxes of tile (stream, tis) into ring slot `half` (lane 0 only)
-    auto issue_tile = [&](uint32_t stream, uint32_t tis, uint32_t half) {
-#pragma unroll
-        for (int s = 0; s < C::NSTEP; s++) {
-            const uint32_t bar = bar_u32 + 8 * (half * C::NSTEP + s);
-            mbar_expect_tx(bar, 4096);
-            tma_load_3d(ring_u32 + half * C::HALF_BYTES + s * 4096, &tmap, s * 32, (int)tis * 32, (int)stream, bar);
-        }
+    // box `b` of tile (stream, tis) into ring slot `slot` (lane 0 only)
+    auto issue_box = [&](uint32_t stream, uint32_t tis, int b, uint32_t slot) {
+        const uint32_t bar = bar_u32 + 8 * slot;
+        mbar_expect_tx(bar, 4096);
+        tma_load_3d(ring_u32 + slot * 4096, &tmap, b * 32, (int)tis * 32, (int)stream, bar);
     };
 
-    // 16-byte piece c of this lane's row in box `box_u32`, and its samples as (rail A, rail B) doubles
+    // 16-byte piece c of this lane's row in box `box_u32`
     auto row_piece = [&](uint32_t box_u32, int c) {
         return lds128((box_u32 + lane * 128 + ((lane & 7) << 4)) ^ (uint32_t)(c << 4));
     };
 
-    uint32_t slot = 0, par = 0;    // ring slot of the tile in phases 1-2 and the parity its barriers complete with
+    uint32_t g = 0;                // boxes consumed so far (ring slot and barrier parity)
     uint32_t tile = 0xFFFFFFFFu;
     uint32_t* const ticket = P.ticket + __ldg(P.ticket + 32 + lane);      // words 32..63 of the ticket block stay zero
     if (lane == 0) {
@@ -174,27 +180,20 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     }
     tile = __shfl_sync(0xffffffffu, tile, 0);
     uint32_t stream = tile / tps, tis = tile - stream * tps;
-    if (lane == 0 && tile < P.total_tiles) issue_tile(stream, tis, 0u);
-
-    bool owe = false;
-    uint32_t ptile = 0, pstream = 0, ptis = 0;
-    double pf[2][S];
+    if (lane == 0 && tile < P.total_tiles) {
 #pragma unroll
-    for (int r = 0; r < 2; r++)
-#pragma unroll
-        for (int c = 0; c < S; c++) pf[r][c] = 0.0;
+        for (int s = 0; s < R; s++) issue_box(stream, tis, s, (uint32_t)s);
+    }
 
-    for (;;) {
-        const bool have = tile < P.total_tiles;
-        // gated stream (its capture lost word alignment, api.cu): the tile drains its boxes and is otherwise skipped
-        const bool live = have && (P.gate == nullptr || __ldg(P.gate + (size_t)stream * P.gate_stride) == 0);
-        const uint32_t half = slot;
-        const uint32_t prev = slot == 0 ? (uint32_t)C::NBUF - 1u : slot - 1u;     // the owed tile's slot
+    while (tile < P.total_tiles) {
+        // gated stream (its capture lost word alignment, api.cu): the tile drains the boxes already requested for
+        // it and is otherwise skipped
+        const bool live = P.gate == nullptr || __ldg(P.gate + (size_t)stream * P.gate_stride) == 0;
         uint32_t next = 0xFFFFFFFFu;       // meaningful in lane 0
         double f[2][S];
-        if (have) {
 
-            // ---- phase 1: the run from the steady state, end state only
+        // ---- phase 1: the run from the steady state, end state only
+        {
             double va[K][2], vb[K][2];
 #pragma unroll
             for (int k = 0; k < K; k++) {
@@ -202,11 +201,12 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 va[k][1] = vb[k][1] = T.sbias[2 * k + 1];
             }
 #pragma unroll 1
-            for (int step = 0; step < C::NSTEP; step++) {
-                mbar_wait(bar_u32 + 8 * (half * C::NSTEP + step), par);
-                const uint32_t box = ring_u32 + half * C::HALF_BYTES + step * 4096;
-                // the 128-byte row in two groups of four pieces: the loops of a tile iteration have to share the
-                // 32 KiB instruction cache of the SM with eleven other warps in other phases
+            for (int b = 0; b < N; b++) {
+                const uint32_t st = g % R;
+                mbar_wait(bar_u32 + 8 * st, (g / R) & 1u);
+                const uint32_t box = ring_u32 + st * 4096;
+                // the 128-byte row in two groups of four pieces: the loops of a tile have to share the instruction
+                // cache of the SM with eleven other warps in other phases
 #pragma unroll 1
                 for (int co = 0; co < (live ? 8 : 0); co += 4) {
                     uint4 q[4];
@@ -225,6 +225,14 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                         }
                     }
                 }
+                __syncwarp();
+                // the box R ahead in this tile's sequence: the rest of phase 1, then (live tiles) the same boxes again
+                if (lane == 0) {
+                    const int nb = b + R;
+                    if (nb < N) issue_box(stream, tis, nb, st);
+                    else if (live) issue_box(stream, tis, nb - N, st);
+                }
+                g++;
             }
 #pragma unroll
             for (int k = 0; k < K; k++) {
@@ -233,216 +241,237 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             }
         }
 
-        // the owed tile's first look-back descriptor: its L2 round trip hides behind the scan
+        if (!live) {
+            // nothing of this tile's is in flight any more; the next tile's first boxes go out after its ticket
+            if (lane == 0) next = take_ticket(ticket);
+            const uint32_t ns_ = next / tps, nt_ = next - ns_ * tps;
+            if (lane == 0 && next < P.total_tiles) {
+#pragma unroll
+                for (int s = 0; s < R; s++) issue_box(ns_, nt_, s, (g + s) % R);
+            }
+            tile = __shfl_sync(0xffffffffu, next, 0);
+            stream = __shfl_sync(0xffffffffu, ns_, 0);
+            tis = __shfl_sync(0xffffffffu, nt_, 0);
+            continue;
+        }
+
+        // the first look-back descriptor: its L2 round trip hides behind the scan
         const int comp = lane < 2 * S ? lane : 0;
         unsigned long long pre = kDescEmpty;
-        if (owe && ptis != 0)
-            pre = ld_desc((P.chained ? P.desc_incl : P.desc_agg) + (size_t)(ptile - 1) * (2 * S) + comp);
+        if (tis != 0)
+            pre = ld_desc((P.chained ? P.desc_incl : P.desc_agg) + (size_t)(tile - 1) * (2 * S) + comp);
 
-        if (have) {
-            // ---- phase 2: warp scan of run end states: E_t = sum_{j<=t} M^(t-j) f_j
+        // ---- phase 2: warp scan of run end states: E_t = sum_{j<=t} M^(t-j) f_j
 #pragma unroll
-            for (int j = 0; j < 5; j++) {
-                if (j < P.scan_rounds && live) {
-                    const int d = 1 << j;
-                    double g[2][S];
-#pragma unroll
-                    for (int r = 0; r < 2; r++)
-#pragma unroll
-                        for (int c = 0; c < S; c++) g[r][c] = shfl_up_f64(f[r][c], d);
-                    if (lane >= d) {
-#pragma unroll
-                        for (int r = 0; r < 2; r++)
-#pragma unroll
-                            for (int row = 0; row < S; row++) {
-                                double acc = f[r][row];
-#pragma unroll
-                                for (int col = col_lo<PAR>(row); col < col_hi(row); col++) acc = fma(T.Mp[j][row * S + col], g[r][col], acc);
-                                f[r][row] = acc;
-                            }
-                    }
-                }
-            }
-            if (lane == 0) next = take_ticket(ticket);      // looked at after phase 3
-            if (lane == 31 && !P.chained && live) {
-                double* agg = P.desc_agg + (size_t)tile * (2 * S);
+        for (int j = 0; j < 5; j++) {
+            if (j < P.scan_rounds) {
+                const int d = 1 << j;
+                double gq[2][S];
 #pragma unroll
                 for (int r = 0; r < 2; r++)
 #pragma unroll
-                    for (int c = 0; c < S; c++) st_desc(agg + r * S + c, f[r][c]);
+                    for (int c = 0; c < S; c++) gq[r][c] = shfl_up_f64(f[r][c], d);
+                if (lane >= d) {
+#pragma unroll
+                    for (int r = 0; r < 2; r++)
+#pragma unroll
+                        for (int row = 0; row < S; row++) {
+                            double acc = f[r][row];
+#pragma unroll
+                            for (int col = col_lo<PAR>(row); col < col_hi(row); col++) acc = fma(T.Mp[j][row * S + col], gq[r][col], acc);
+                            f[r][row] = acc;
+                        }
+                }
             }
         }
+        if (lane == 31 && !P.chained) {
+            double* agg = P.desc_agg + (size_t)tile * (2 * S);
+#pragma unroll
+            for (int r = 0; r < 2; r++)
+#pragma unroll
+                for (int c = 0; c < S; c++) st_desc(agg + r * S + c, f[r][c]);
+        }
 
-        // ---- the owed tile: decoupled look-back, then phase 3 out of its ring slot
-        if (owe) {
+        // ---- decoupled look-back: the state entering the tile
+        {
             const int crail = comp / S, crow = comp % S;
             // Every lane walks the look-back (lanes >= 2S repeat component 0: same addresses, no extra traffic) and
             // only the store is predicated: with the walk under `if (lane < 2S)` and more than one trip through its
             // loop, the two groups of lanes stayed apart all the way through phase 3 - every instruction issued
             // twice, at 16 threads (ncu, order 6 at fc = 10 kHz: profiles/r1_sweeps.txt, sweep 26).
-            {
-                double sin_c = 0.0;
-                if (ptis == 0) {
-                    sin_c = P.state_in[(size_t)pstream * (2 * S) + crail * S + crow];
-                } else {
-                    const double* first = (P.chained ? P.desc_incl : P.desc_agg) + (size_t)(ptile - 1) * (2 * S) + comp;
-                    while (pre == kDescEmpty) { __nanosleep(32); pre = ld_desc(first); }
-                    sin_c = __longlong_as_double((long long)pre);
-                    if (!P.chained) {
-                        const int depth = (int)ptis < P.window ? (int)ptis : P.window;
-                        // two tiles' aggregates are requested together (one L2 round trip for both)
-                        for (int j = 2; j <= depth; j += 2) {
-                            const bool two = j + 1 <= depth;
-                            const double* a = P.desc_agg + (size_t)(ptile - j) * (2 * S) + crail * S;
-                            const double* a2 = a - (two ? 2 * S : 0);
-                            const double* mp = P.mtile_pow + (size_t)(j - 1) * (S * S) + crow * S;
-                            unsigned long long dv[S], dw[S];
+            double sin_c = 0.0;
+            if (tis == 0) {
+                sin_c = P.state_in[(size_t)stream * (2 * S) + crail * S + crow];
+            } else {
+                const double* first = (P.chained ? P.desc_incl : P.desc_agg) + (size_t)(tile - 1) * (2 * S) + comp;
+                while (pre == kDescEmpty) { __nanosleep(32); pre = ld_desc(first); }
+                sin_c = __longlong_as_double((long long)pre);
+                if (!P.chained) {
+                    const int depth = (int)tis < P.window ? (int)tis : P.window;
+                    // two tiles' aggregates are requested together (one L2 round trip for both)
+                    for (int j = 2; j <= depth; j += 2) {
+                        const bool two = j + 1 <= depth;
+                        const double* a = P.desc_agg + (size_t)(tile - j) * (2 * S) + crail * S;
+                        const double* a2 = a - (two ? 2 * S : 0);
+                        const double* mp = P.mtile_pow + (size_t)(j - 1) * (S * S) + crow * S;
+                        unsigned long long dv[S], dw[S];
 #pragma unroll
-                            for (int col = 0; col < S; col++) { dv[col] = ld_desc(a + col); dw[col] = ld_desc(a2 + col); }
+                        for (int col = 0; col < S; col++) { dv[col] = ld_desc(a + col); dw[col] = ld_desc(a2 + col); }
+#pragma unroll
+                        for (int col = 0; col < S; col++) {
+                            while (dv[col] == kDescEmpty) { __nanosleep(32); dv[col] = ld_desc(a + col); }
+                            sin_c = fma(__ldg(mp + col), __longlong_as_double((long long)dv[col]), sin_c);
+                        }
+                        if (two) {
 #pragma unroll
                             for (int col = 0; col < S; col++) {
-                                while (dv[col] == kDescEmpty) { __nanosleep(32); dv[col] = ld_desc(a + col); }
-                                sin_c = fma(__ldg(mp + col), __longlong_as_double((long long)dv[col]), sin_c);
-                            }
-                            if (two) {
-#pragma unroll
-                                for (int col = 0; col < S; col++) {
-                                    while (dw[col] == kDescEmpty) { __nanosleep(32); dw[col] = ld_desc(a2 + col); }
-                                    sin_c = fma(__ldg(mp + S * S + col), __longlong_as_double((long long)dw[col]), sin_c);
-                                }
-                            }
-                        }
-                        if ((int)ptis <= P.window) {     // the window reaches the start of the stream
-                            const double* a = P.state_in + (size_t)pstream * (2 * S) + crail * S;
-                            const double* mp = P.mtile_pow + (size_t)ptis * (S * S) + crow * S;
-#pragma unroll
-                            for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), __ldg(a + col), sin_c);
-                        }
-                    }
-                }
-                if (lane < 2 * S) sts64(scratch + lane * 8, sin_c);
-            }
-            __syncwarp();
-            double sin[2][S];
-#pragma unroll
-            for (int r = 0; r < 2; r++)
-#pragma unroll
-                for (int c = 0; c < S; c++) sin[r][c] = lds64(scratch + (r * S + c) * 8);
-
-            // true state entering this lane's run: s0 = M^lane S_in + E_{lane-1}
-            double s0[2][S];
-#pragma unroll
-            for (int r = 0; r < 2; r++)
-#pragma unroll
-                for (int c = 0; c < S; c++) {
-                    const double e = shfl_up_f64(pf[r][c], 1);
-                    s0[r][c] = lane == 0 ? 0.0 : e;
-                }
-#pragma unroll
-            for (int row = 0; row < S; row++)
-#pragma unroll
-                for (int col = col_lo<PAR>(row); col < col_hi(row); col++) {
-                    const double m = __ldg(P.plane + (row * S + col) * 33 + lane);      // (M^lane)[row][col]
-                    s0[0][row] = fma(m, sin[0][col], s0[0][row]);
-                    s0[1][row] = fma(m, sin[1][col], s0[1][row]);
-                }
-
-            // true end state of the tile (chained mode) / of the stream (last tile)
-            const bool last_tile = (ptis == tps - 1);
-            if (P.chained || (last_tile && P.write_state)) {
-                const int lastl = last_tile && P.write_state ? (int)P.last_tile_runs - 1 : 31;
-                if (lane == lastl) {
-                    double* incl = P.desc_incl + (size_t)ptile * (2 * S);
-#pragma unroll
-                    for (int row = 0; row < S; row++) {
-                        double ea = pf[0][row], eb = pf[1][row];
-#pragma unroll
-                        for (int col = col_lo<PAR>(row); col < col_hi(row); col++) {
-                            const double m = __ldg(P.plane + (row * S + col) * 33 + lastl + 1);
-                            ea = fma(m, sin[0][col], ea);
-                            eb = fma(m, sin[1][col], eb);
-                        }
-                        if (P.chained) { st_desc(incl + row, ea); st_desc(incl + S + row, eb); }
-                        if (last_tile && P.write_state) {
-                            P.state_out[(size_t)pstream * (2 * S) + row] = ea;
-                            P.state_out[(size_t)pstream * (2 * S) + S + row] = eb;
-                        }
-                    }
-                }
-            }
-
-            // ---- phase 3: the run again, from its true entry state (offset by the steady state the injected
-            // inputs imply), outputs at the kept positions
-            const uint32_t run = ptis * 32u + lane;
-            if (run < P.n_runs) {
-                double va[K][2], vb[K][2];
-#pragma unroll
-                for (int k = 0; k < K; k++) {
-                    va[k][0] = T.sbias[2 * k] + s0[0][2 * k];     va[k][1] = T.sbias[2 * k + 1] + s0[0][2 * k + 1];
-                    vb[k][0] = T.sbias[2 * k] + s0[1][2 * k];     vb[k][1] = T.sbias[2 * k + 1] + s0[1][2 * k + 1];
-                }
-                uint64_t o = (uint64_t)pstream * P.out_stride + (uint64_t)run * C::NK;
-                constexpr int PER = (IN == IN_CF32) ? 2 : 4;      // samples per 16-byte piece
-                constexpr int PP  = 4 * D / PER;                  // pieces that hold four kept outputs = one store
-                const uint32_t tile_u32 = ring_u32 + prev * C::HALF_BYTES;
-                // one chunk of four kept outputs per iteration, not unrolled (one copy of the format switch in
-                // store_out4); the next chunk's pieces are read while this one is filtered
-                auto chunk_pieces = [&](int ch, uint4 (&q)[PP]) {
-                    const int p0 = ch * PP;                       // piece within the run: box p0 / 8, piece p0 % 8
-#pragma unroll
-                    for (int i = 0; i < PP; i++) q[i] = row_piece(tile_u32 + (uint32_t)(p0 >> 3) * 4096u, (p0 & 7) + i);
-                };
-                const bool fast_f32 = P.out_mode == OUT_F32 && P.out_vec != 0;
-                uint4 qn[PP];
-                chunk_pieces(0, qn);
-#pragma unroll (kRerunP3Unroll)
-                for (int ch = 0; ch < C::NK / 4; ch++) {
-                    uint4 q[PP];
-#pragma unroll
-                    for (int i = 0; i < PP; i++) q[i] = qn[i];
-                    if (ch + 1 < C::NK / 4) chunk_pieces(ch + 1, qn);
-                    double yi[4], yq[4];
-#pragma unroll
-                    for (int ci = 0; ci < PP; ci++) {
-                        const uint32_t wv[4] = {q[ci].x, q[ci].y, q[ci].z, q[ci].w};
-#pragma unroll
-                        for (int e = 0; e < PER; e++) {
-                            const int j = ci * PER + e;          // sample within the chunk (chunks start on multiples of D)
-                            double xa, xb;
-                            if (INJECT) inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
-                            else sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
-                            if (j % D == 0) {
-                                yi[j / D] = fma(filter_step<K, PAR, true>(T, va, xa), T.gain, T.out_bias);
-                                yq[j / D] = fma(filter_step<K, PAR, true>(T, vb, xb), T.gain, T.out_bias);
-                            } else {
-                                filter_step<K, PAR, false>(T, va, xa);
-                                filter_step<K, PAR, false>(T, vb, xb);
+                                while (dw[col] == kDescEmpty) { __nanosleep(32); dw[col] = ld_desc(a2 + col); }
+                                sin_c = fma(__ldg(mp + S * S + col), __longlong_as_double((long long)dw[col]), sin_c);
                             }
                         }
                     }
-                    if (fast_f32) {      // plain CF32 into an aligned buffer: one test instead of the format switch
-                        stg_cf32x4(reinterpret_cast<float2*>(P.out) + o, make_float2((float)yi[0], (float)yq[0]),
-                                   make_float2((float)yi[1], (float)yq[1]), make_float2((float)yi[2], (float)yq[2]),
-                                   make_float2((float)yi[3], (float)yq[3]));
-                    } else {
-                        store_out4(P, o, yi, yq);
+                    if ((int)tis <= P.window) {     // the window reaches the start of the stream
+                        const double* a = P.state_in + (size_t)stream * (2 * S) + crail * S;
+                        const double* mp = P.mtile_pow + (size_t)tis * (S * S) + crow * S;
+#pragma unroll
+                        for (int col = 0; col < S; col++) sin_c = fma(__ldg(mp + col), __ldg(a + col), sin_c);
                     }
-                    o += 4;
                 }
             }
-            __syncwarp();   // the owed tile's ring slot and the scratch are free again
+            if (lane < 2 * S) sts64(scratch + lane * 8, sin_c);
         }
-        if (!have) break;
-        // the slot the owed tile just left takes this warp's next tile
-        const uint32_t nstream = next / tps, ntis = next - nstream * tps;
-        if (lane == 0 && next < P.total_tiles) issue_tile(nstream, ntis, prev);
-        owe = live;
-        ptile = tile; pstream = stream; ptis = tis;
+        __syncwarp();
+        if (lane == 0) next = take_ticket(ticket);          // looked at towards the end of phase 3
+        double sin[2][S];
 #pragma unroll
         for (int r = 0; r < 2; r++)
 #pragma unroll
-            for (int c = 0; c < S; c++) pf[r][c] = f[r][c];
-        if (++slot == (uint32_t)C::NBUF) { slot = 0; par ^= 1u; }
+            for (int c = 0; c < S; c++) sin[r][c] = lds64(scratch + (r * S + c) * 8);
+
+        // true state entering this lane's run: s0 = M^lane S_in + E_{lane-1}
+        double s0[2][S];
+#pragma unroll
+        for (int r = 0; r < 2; r++)
+#pragma unroll
+            for (int c = 0; c < S; c++) {
+                const double e = shfl_up_f64(f[r][c], 1);
+                s0[r][c] = lane == 0 ? 0.0 : e;
+            }
+#pragma unroll
+        for (int row = 0; row < S; row++)
+#pragma unroll
+            for (int col = col_lo<PAR>(row); col < col_hi(row); col++) {
+                const double m = __ldg(P.plane + (row * S + col) * 33 + lane);      // (M^lane)[row][col]
+                s0[0][row] = fma(m, sin[0][col], s0[0][row]);
+                s0[1][row] = fma(m, sin[1][col], s0[1][row]);
+            }
+
+        // true end state of the tile (chained mode) / of the stream (last tile)
+        const bool last_tile = (tis == tps - 1);
+        if (P.chained || (last_tile && P.write_state)) {
+            const int lastl = last_tile && P.write_state ? (int)P.last_tile_runs - 1 : 31;
+            if (lane == lastl) {
+                double* incl = P.desc_incl + (size_t)tile * (2 * S);
+#pragma unroll
+                for (int row = 0; row < S; row++) {
+                    double ea = f[0][row], eb = f[1][row];
+#pragma unroll
+                    for (int col = col_lo<PAR>(row); col < col_hi(row); col++) {
+                        const double m = __ldg(P.plane + (row * S + col) * 33 + lastl + 1);
+                        ea = fma(m, sin[0][col], ea);
+                        eb = fma(m, sin[1][col], eb);
+                    }
+                    if (P.chained) { st_desc(incl + row, ea); st_desc(incl + S + row, eb); }
+                    if (last_tile && P.write_state) {
+                        P.state_out[(size_t)stream * (2 * S) + row] = ea;
+                        P.state_out[(size_t)stream * (2 * S) + S + row] = eb;
+                    }
+                }
+            }
+        }
+
+        // ---- phase 3: the run again, box by box, from its true entry state (offset by the steady state the
+        // injected inputs imply), outputs at the kept positions
+        uint32_t nstream = 0, ntis = 0;
+        {
+            const uint32_t run = tis * 32u + lane;
+            const bool mine = run < P.n_runs;
+            double va[K][2], vb[K][2];
+#pragma unroll
+            for (int k = 0; k < K; k++) {
+                va[k][0] = T.sbias[2 * k] + s0[0][2 * k];     va[k][1] = T.sbias[2 * k + 1] + s0[0][2 * k + 1];
+                vb[k][0] = T.sbias[2 * k] + s0[1][2 * k];     vb[k][1] = T.sbias[2 * k + 1] + s0[1][2 * k + 1];
+            }
+            uint64_t o = (uint64_t)stream * P.out_stride + (uint64_t)run * C::NK;
+            constexpr int PER = (IN == IN_CF32) ? 2 : 4;      // samples per 16-byte piece
+            constexpr int PP  = 4 * D / PER;                  // pieces that hold four kept outputs = one store
+            constexpr int CPB = 8 / PP;                       // chunks of four kept outputs per box
+            static_assert(PP >= 1 && 8 % PP == 0, "a box holds whole chunks");
+            const bool fast_f32 = P.out_mode == OUT_F32 && P.out_vec != 0;
+#pragma unroll 1
+            for (int b = 0; b < N; b++) {
+                const uint32_t st = g % R;
+                mbar_wait(bar_u32 + 8 * st, (g / R) & 1u);
+                const uint32_t box = ring_u32 + st * 4096;
+                if (mine) {
+                    // chunks of four kept outputs, kRerunP3Unroll per iteration (one copy of the format switch in
+                    // store_out4 each); the next chunk's pieces are read while this one is filtered
+                    uint4 qn[PP];
+#pragma unroll
+                    for (int i = 0; i < PP; i++) qn[i] = row_piece(box, i);
+#pragma unroll (kRerunP3Unroll)
+                    for (int ch = 0; ch < CPB; ch++) {
+                        uint4 q[PP];
+#pragma unroll
+                        for (int i = 0; i < PP; i++) q[i] = qn[i];
+                        if (ch + 1 < CPB) {
+#pragma unroll
+                            for (int i = 0; i < PP; i++) qn[i] = row_piece(box, (ch + 1) * PP + i);
+                        }
+                        double yi[4], yq[4];
+#pragma unroll
+                        for (int ci = 0; ci < PP; ci++) {
+                            const uint32_t wv[4] = {q[ci].x, q[ci].y, q[ci].z, q[ci].w};
+#pragma unroll
+                            for (int e = 0; e < PER; e++) {
+                                const int j = ci * PER + e;          // sample within the chunk (chunks start on multiples of D)
+                                double xa, xb;
+                                if (INJECT) inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
+                                else sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
+                                if (j % D == 0) {
+                                    yi[j / D] = fma(filter_step<K, PAR, true>(T, va, xa), T.gain, T.out_bias);
+                                    yq[j / D] = fma(filter_step<K, PAR, true>(T, vb, xb), T.gain, T.out_bias);
+                                } else {
+                                    filter_step<K, PAR, false>(T, va, xa);
+                                    filter_step<K, PAR, false>(T, vb, xb);
+                                }
+                            }
+                        }
+                        if (fast_f32) {      // plain CF32 into an aligned buffer: one test instead of the format switch
+                            stg_cf32x4(reinterpret_cast<float2*>(P.out) + o, make_float2((float)yi[0], (float)yq[0]),
+                                       make_float2((float)yi[1], (float)yq[1]), make_float2((float)yi[2], (float)yq[2]),
+                                       make_float2((float)yi[3], (float)yq[3]));
+                        } else {
+                            store_out4(P, o, yi, yq);
+                        }
+                        o += 4;
+                    }
+                }
+                __syncwarp();
+                // the box R ahead: the rest of this tile, then the first boxes of the next one
+                if (lane == 0) {
+                    const int nb = b + R;
+                    if (nb < N) {
+                        issue_box(stream, tis, nb, st);
+                    } else {
+                        nstream = next / tps;
+                        ntis = next - nstream * tps;
+                        if (next < P.total_tiles) issue_box(nstream, ntis, nb - N, st);
+                    }
+                }
+                g++;
+            }
+        }
         tile = __shfl_sync(0xffffffffu, next, 0);
         stream = __shfl_sync(0xffffffffu, nstream, 0);
         tis = __shfl_sync(0xffffffffu, ntis, 0);

@@ -39,7 +39,7 @@ def test_full_rate_every_input_kind(cb, po, torch_cuda, order, fc, kind):
     out = torch.zeros((n, 2), dtype=torch.float32, device="cuda:0")
     with cb.Context(sos=sos, decimation=1, parity=cb.PARITY_F32) as ctx:
         fi = ctx.filter_info()
-        assert fi.run_len == 64 and fi.decimation == 1          # the rerun plan (tests/test_host_plan.py)
+        assert fi.run_len % 32 == 0 and fi.run_len >= 64 and fi.decimation == 1          # the rerun plan (tests/test_host_plan.py)
         if kind == "words":
             pad = np.zeros((n + 3) & ~3, np.uint32)
             pad[:n] = w
@@ -201,7 +201,7 @@ def test_decimate_by_two_from_three_sections_on(cb, po, torch_cuda, order, fc, k
     ref = po.filter_cf32_f32(sos, x, ci, cq)[::D]
     out = torch.zeros((n // D, 2), dtype=torch.float32, device="cuda:0")
     with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32) as ctx:
-        assert ctx.filter_info().run_len == 64
+        assert ctx.filter_info().run_len >= 64
         if kind == "words":
             ctx.filter_submit(cb.IN_WORDS, _dev(torch, w.view(np.int32)), n, out)
         else:

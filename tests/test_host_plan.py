@@ -48,9 +48,10 @@ def test_run_lengths_follow_the_shared_memory_budget(emul, po):
                 assert p["kept"] == p["run_len"] // D and p["kept"] % 4 == 0
                 assert p["par"] == 1                              # Butterworth poles are distinct: parallel form
                 if p["rerun"]:
-                    # full-rate streams (csrc/iir_rerun.cuh): the input tile is what stays in shared memory, there is
-                    # no stage of kept outputs to bound the run and no float staging
-                    assert (D == 1 or (D == 2 and len(sos) >= 3)) and p["y32"] == 0 and p["run_len"] == 64
+                    # full-rate streams (csrc/iir_rerun.cuh): the input is fetched twice instead of staged, so no
+                    # stage of kept outputs bounds the run and there is no float staging
+                    assert (D == 1 or (D == 2 and len(sos) >= 3)) and p["y32"] == 0
+                    assert p["run_len"] == (128 if len(sos) <= 2 else 256)
                 else:
                     assert p["kept"] <= 32 and p["y32"] == y32
     assert plan_info(emul, po.butter_lowpass_sos(4, 4e6, 250e3), 1, 1, force_cascade=1)["rerun"] == 0   # cascade form: staged kernel
