@@ -160,7 +160,8 @@ int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t
             void* d_out, size_t out_stride, const int32_t* gate, uint32_t gate_stride, bool commit, uint32_t max_tiles,
             double* state)
 {
-    const FilterPlan& P = c->plan;
+    const FilterPlan& P = pick_plan(c, n);
+    const bool small = &P == &c->plan_small;
     if (!state) state = c->d_state;
     const uint32_t ns = c->win_cnt;                               // streams of this launch (a window of the batch)
     const size_t st_off = (size_t)c->win0 * 2 * P.S;             // their filter states
@@ -202,8 +203,9 @@ int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t
         p.write_state = (commit && whole) ? 1 : 0;
         p.layout = layout;
         p.out_mode = c->out_mode;
-        p.mtile_pow = c->d_mtile_pow;
-        p.plane = c->d_plane;
+        p.mtile_pow = small ? c->d_mtile_pow_small : c->d_mtile_pow;
+        p.plane = small ? c->d_plane_small : c->d_plane;
+        p.rr_boxes = (uint32_t)(LT / (in_kind == IN_CF32 ? 16 : 32));
         p.desc_agg = c->desc_agg.as<double>();
         p.desc_incl = c->desc_incl.as<double>();
         p.ticket = c->d_ticket;
@@ -269,6 +271,13 @@ int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t
     }
     CBL_CHECK(cudaGetLastError());
     return CARIBOU_CUDA_OK;
+}
+
+const FilterPlan& pick_plan(const caribou_cuda_ctx* c, size_t n)
+{
+    if (!c->has_small) return c->plan;
+    const uint64_t tiles = ((uint64_t)(n / (size_t)c->plan.LT) + 31) / 32 * c->win_cnt;
+    return tiles < (uint64_t)c->num_sms * 12 ? c->plan_small : c->plan;
 }
 
 // ------------------------------------------------------------------ alignment search for a batch
@@ -493,6 +502,15 @@ caribou_cuda_ctx* caribou_cuda_create(const caribou_cuda_config* cfg_in)
             !cuda_ok(cudaMalloc(&c->d_state_next, ns * 2 * P.S * 8), "cudaMalloc")) return fail();
         cudaMemcpy(c->d_plane, P.plane.data(), P.plane.size() * 8, cudaMemcpyHostToDevice);
         cudaMemcpy(c->d_mtile_pow, P.mtile_pow.data(), P.mtile_pow.size() * 8, cudaMemcpyHostToDevice);
+        if (P.rerun && P.LT > kRerunSmallLT) {
+            if (!make_filter_plan(cfg.n_sos, cfg.sos, cfg.decimation, false, c->out_mode == OUT_F32, &c->plan_small, &msg, kRerunSmallLT)) { set_error("%s", msg); return fail(); }
+            const FilterPlan& Q = c->plan_small;
+            if (!cuda_ok(cudaMalloc(&c->d_plane_small, Q.plane.size() * 8), "cudaMalloc") ||
+                !cuda_ok(cudaMalloc(&c->d_mtile_pow_small, Q.mtile_pow.size() * 8), "cudaMalloc")) return fail();
+            cudaMemcpy(c->d_plane_small, Q.plane.data(), Q.plane.size() * 8, cudaMemcpyHostToDevice);
+            cudaMemcpy(c->d_mtile_pow_small, Q.mtile_pow.data(), Q.mtile_pow.size() * 8, cudaMemcpyHostToDevice);
+            c->has_small = Q.rerun && Q.par == P.par;
+        }
         cudaMemset(c->d_state, 0, ns * 2 * P.S * 8);
         cudaMemset(c->d_state_next, 0, ns * 2 * P.S * 8);
         c->has_filter = true;
@@ -513,6 +531,8 @@ void caribou_cuda_destroy(caribou_cuda_ctx* c)
     for (DevBuf* b : bufs) b->release();
     if (c->d_plane) cudaFree(c->d_plane);
     if (c->d_mtile_pow) cudaFree(c->d_mtile_pow);
+    if (c->d_plane_small) cudaFree(c->d_plane_small);
+    if (c->d_mtile_pow_small) cudaFree(c->d_mtile_pow_small);
     if (c->d_state) cudaFree(c->d_state);
     if (c->d_state_next) cudaFree(c->d_state_next);
     for (cudaEvent_t e : c->pipe_ev) if (e) cudaEventDestroy(e);
@@ -840,9 +860,10 @@ int caribou_cuda_filter_fixup(caribou_cuda_ctx* c, int in_kind, const void* in, 
     CBL_CHECK(cudaMemcpyAsync(c->d_state, ker.data(), ker.size() * 8, cudaMemcpyHostToDevice, c->stream));
     CBL_CHECK(cudaStreamSynchronize(c->stream));       // `ker` is pageable: the copy has landed before it is reused
     const size_t fix = caribou_cuda_fixup_samples(c, n);
-    const uint32_t tile_samples = 32u * (uint32_t)P.LT;
+    const int LTn = pick_plan(c, n).LT;                  // the plan run_iir will take for this shard
+    const uint32_t tile_samples = 32u * (uint32_t)LTn;
     uint32_t max_tiles = (uint32_t)((fix + tile_samples - 1) / tile_samples);
-    const uint64_t tiles_ps = (n / P.LT + 31) / 32;
+    const uint64_t tiles_ps = (n / LTn + 31) / 32;
     if (max_tiles == 0 || max_tiles >= tiles_ps) {
         // no useful contraction (or a short shard): filter the whole shard again from the true state;
         // the kernels then leave the true end state in d_state themselves

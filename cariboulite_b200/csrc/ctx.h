@@ -68,6 +68,9 @@ int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t
 // alignment search of the window's streams; returns the chunk count (>= 0) or an error code.
 // with_gates: also raise the sticky per-stream gates the fused launches look at
 int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes, bool with_gates);
+// the plan run_iir takes for a submit of n samples per stream (the short-run plan when the long-run one would leave most
+// of the GPU without a tile)
+const FilterPlan& pick_plan(const caribou_cuda_ctx* c, size_t n);
 int mirror_counters(caribou_cuda_ctx* c);
 int ensure_scale(caribou_cuda_ctx* c, int in_kind);
 // blocks until every queued rx submit has been carried out (misaligned captures redone on the slow path)
@@ -95,6 +98,12 @@ struct caribou_cuda_ctx {
     size_t out_elem = 8;
     double* d_plane = nullptr;
     double* d_mtile_pow = nullptr;
+    // rerun plans only: the same filter with short runs (kRerunSmallLT) for submits too small to fill the GPU with the
+    // long-run plan's tiles (an MTU of 131072 samples is 16 tiles of 32 x 256-sample runs, but 64 of 32 x 64)
+    bool has_small = false;
+    cbl::FilterPlan plan_small;
+    double* d_plane_small = nullptr;
+    double* d_mtile_pow_small = nullptr;
     double* d_state = nullptr;        // [n_streams][2S] kernel coordinates
     double* d_state_next = nullptr;
     uint64_t pos = 0;                 // samples consumed per stream since create/reset

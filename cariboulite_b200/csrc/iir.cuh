@@ -93,6 +93,8 @@ struct IirParams {
     uint32_t  inj_xor, inj_mul;
     int       scan_rounds;      // Kogge-Stone rounds of the warp scan that can still contribute (<= 5)
     int       out_vec;          // CF32 output may be stored 32 bytes at a time (base and stream stride 32-byte aligned)
+    uint32_t  rr_boxes;         // rerun kernel: 4 KiB boxes per tile = run length / samples per 128-byte row piece (runtime:
+                                // small submits take a plan with short runs so that they still spread over the GPU)
 };
 
 struct IirTailParams {
@@ -172,6 +174,7 @@ __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
 #define CBL_RR_P3U 1             // chunks of four outputs per iteration of the rerun kernel's phase-3 loop
 #endif
 __host__ __device__ constexpr int iir_rerun_len(int K) { return K <= 2 ? CBL_RR_LT12 : CBL_RR_LT; }
+constexpr int kRerunSmallLT = 64;       // run length of the second plan a context keeps for submits too small to fill the GPU
 constexpr int kRerunP3Unroll = CBL_RR_P3U;
 __host__ __device__ constexpr bool iir_is_rerun(int K, int D, bool par)
 {

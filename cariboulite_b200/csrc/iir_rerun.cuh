@@ -39,11 +39,9 @@ namespace cbl {
 template <int K, int D, int IN>
 struct RerunCfg {
     static constexpr int S     = 2 * K;
-    static constexpr int LT    = iir_rerun_len(K);
-    static constexpr int NK    = LT / D;
     static constexpr int SPS   = (IN == IN_CF32) ? 16 : 32;   // samples per 128-byte row step = per box
-    static constexpr int NSTEP = LT / SPS;                    // 4 KiB boxes per tile
-    static constexpr int R     = CBL_RR_RING < NSTEP ? CBL_RR_RING : NSTEP;
+    static constexpr int R     = CBL_RR_RING;                 // ring slots (a tile of fewer boxes uses as many as it has)
+    // the run length is a launch parameter (IirParams::rr_boxes boxes of SPS samples): the plan fixes it
     static constexpr int RING_BYTES    = R * 4096;
     static constexpr int SCRATCH_BYTES = 2 * S * 8 * 2;
     static constexpr int WARP_BYTES = RING_BYTES + SCRATCH_BYTES;
@@ -52,7 +50,7 @@ struct RerunCfg {
     static constexpr int REG_WARPS  = (K <= 2) ? CBL_RR_WARPS : (K == 3 ? CBL_RR_WARPS3 : CBL_RR_WARPS4);
     static constexpr int WPC = SMEM_WARPS < REG_WARPS ? SMEM_WARPS : REG_WARPS;
     static_assert(WPC >= 1, "a warp's buffers do not fit shared memory");
-    static_assert(LT % 32 == 0 && (D == 1 || D == 2), "phase 3 works in groups of 8 or 16 samples: whole chunks of 4 kept outputs");
+    static_assert(D == 1 || D == 2, "phase 3 works in groups of 8 or 16 samples: whole chunks of 4 kept outputs");
     static constexpr int SMEM_BYTES = WPC * WARP_BYTES + WPC * R * 8 + 1024;
 };
 
@@ -140,17 +138,18 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     constexpr int S = C::S;
     constexpr bool PAR = true;
     constexpr bool INJECT = IN != IN_CF32;
-    constexpr int N = C::NSTEP, R = C::R;
+    const int N = (int)P.rr_boxes;                              // boxes per tile
+    const uint32_t R = N < C::R ? (uint32_t)N : (uint32_t)C::R;  // ring slots in use
     extern __shared__ uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t ring_u32 = base + warp * C::RING_BYTES;
     const uint32_t scratch = base + C::WPC * C::RING_BYTES + warp * C::SCRATCH_BYTES;
-    const uint32_t bar_u32 = base + C::WPC * C::WARP_BYTES + warp * R * 8;
+    const uint32_t bar_u32 = base + C::WPC * C::WARP_BYTES + warp * C::R * 8;
 
     if (lane == 0) {
 #pragma unroll
-        for (int s = 0; s < R; s++) mbar_init(bar_u32 + 8 * s, 1);
+        for (int s = 0; s < C::R; s++) mbar_init(bar_u32 + 8 * s, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -172,7 +171,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         return lds128((box_u32 + lane * 128 + ((lane & 7) << 4)) ^ (uint32_t)(c << 4));
     };
 
-    uint32_t g = 0;                // boxes consumed so far (ring slot and barrier parity)
+    uint32_t slot = 0, par = 0;    // ring slot of the next box to consume and the parity its barrier completes with
     uint32_t tile = 0xFFFFFFFFu;
     uint32_t* const ticket = P.ticket + __ldg(P.ticket + 32 + lane);      // words 32..63 of the ticket block stay zero
     if (lane == 0) {
@@ -181,8 +180,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     tile = __shfl_sync(0xffffffffu, tile, 0);
     uint32_t stream = tile / tps, tis = tile - stream * tps;
     if (lane == 0 && tile < P.total_tiles) {
-#pragma unroll
-        for (int s = 0; s < R; s++) issue_box(stream, tis, s, (uint32_t)s);
+        for (uint32_t s = 0; s < R; s++) issue_box(stream, tis, (int)s, s);
     }
 
     while (tile < P.total_tiles) {
@@ -202,8 +200,8 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             }
 #pragma unroll 1
             for (int b = 0; b < N; b++) {
-                const uint32_t st = g % R;
-                mbar_wait(bar_u32 + 8 * st, (g / R) & 1u);
+                const uint32_t st = slot;
+                mbar_wait(bar_u32 + 8 * st, par);
                 const uint32_t box = ring_u32 + st * 4096;
                 // the 128-byte row in two groups of four pieces: the loops of a tile have to share the instruction
                 // cache of the SM with eleven other warps in other phases
@@ -228,11 +226,11 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 __syncwarp();
                 // the box R ahead in this tile's sequence: the rest of phase 1, then (live tiles) the same boxes again
                 if (lane == 0) {
-                    const int nb = b + R;
+                    const int nb = b + (int)R;
                     if (nb < N) issue_box(stream, tis, nb, st);
                     else if (live) issue_box(stream, tis, nb - N, st);
                 }
-                g++;
+                if (++slot == R) { slot = 0; par ^= 1u; }
             }
 #pragma unroll
             for (int k = 0; k < K; k++) {
@@ -246,8 +244,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             if (lane == 0) next = take_ticket(ticket);
             const uint32_t ns_ = next / tps, nt_ = next - ns_ * tps;
             if (lane == 0 && next < P.total_tiles) {
-#pragma unroll
-                for (int s = 0; s < R; s++) issue_box(ns_, nt_, s, (g + s) % R);
+                for (uint32_t s = 0; s < R; s++) issue_box(ns_, nt_, (int)s, (slot + s) % R);
             }
             tile = __shfl_sync(0xffffffffu, next, 0);
             stream = __shfl_sync(0xffffffffu, ns_, 0);
@@ -402,7 +399,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 va[k][0] = T.sbias[2 * k] + s0[0][2 * k];     va[k][1] = T.sbias[2 * k + 1] + s0[0][2 * k + 1];
                 vb[k][0] = T.sbias[2 * k] + s0[1][2 * k];     vb[k][1] = T.sbias[2 * k + 1] + s0[1][2 * k + 1];
             }
-            uint64_t o = (uint64_t)stream * P.out_stride + (uint64_t)run * C::NK;
+            uint64_t o = (uint64_t)stream * P.out_stride + (uint64_t)run * (uint32_t)(N * C::SPS / D);
             constexpr int PER = (IN == IN_CF32) ? 2 : 4;      // samples per 16-byte piece
             constexpr int PP  = 4 * D / PER;                  // pieces that hold four kept outputs = one store
             constexpr int CPB = 8 / PP;                       // chunks of four kept outputs per box
@@ -410,8 +407,8 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             const bool fast_f32 = P.out_mode == OUT_F32 && P.out_vec != 0;
 #pragma unroll 1
             for (int b = 0; b < N; b++) {
-                const uint32_t st = g % R;
-                mbar_wait(bar_u32 + 8 * st, (g / R) & 1u);
+                const uint32_t st = slot;
+                mbar_wait(bar_u32 + 8 * st, par);
                 const uint32_t box = ring_u32 + st * 4096;
                 if (mine) {
                     // chunks of four kept outputs, kRerunP3Unroll per iteration (one copy of the format switch in
@@ -460,7 +457,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 __syncwarp();
                 // the box R ahead: the rest of this tile, then the first boxes of the next one
                 if (lane == 0) {
-                    const int nb = b + R;
+                    const int nb = b + (int)R;
                     if (nb < N) {
                         issue_box(stream, tis, nb, st);
                     } else {
@@ -469,7 +466,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                         if (next < P.total_tiles) issue_box(nstream, ntis, nb - N, st);
                     }
                 }
-                g++;
+                if (++slot == R) { slot = 0; par ^= 1u; }
             }
         }
         tile = __shfl_sync(0xffffffffu, next, 0);

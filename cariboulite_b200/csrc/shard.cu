@@ -249,9 +249,10 @@ static int shard_fixup(caribou_cuda_ctx* c)
     const FilterPlan& P = c->plan;
     const int32_t* gate = s->in_kind == IN_WORDS ? &c->d_counters->any_misaligned : nullptr;
     const size_t fix = caribou_cuda_fixup_samples(c, s->n);
-    const uint32_t tile_samples = 32u * (uint32_t)P.LT;
+    const int LTn = pick_plan(c, s->n).LT;               // the plan run_iir will take for this shard
+    const uint32_t tile_samples = 32u * (uint32_t)LTn;
     const uint32_t max_tiles = (uint32_t)((fix + tile_samples - 1) / tile_samples);
-    const uint64_t tiles_ps = (s->n / P.LT + 31) / 32;
+    const uint64_t tiles_ps = (s->n / LTn + 31) / 32;
     if (max_tiles == 0 || max_tiles >= tiles_ps) {
         // no useful contraction, or a short shard: the whole shard again (tail included) from a scratch copy of s_in
         CBL_CHECK(cudaMemcpyAsync(s->d_work, s->d_sin, s->per_rank * 8, cudaMemcpyDeviceToDevice, c->stream));

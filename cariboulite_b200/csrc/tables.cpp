@@ -312,7 +312,8 @@ bool state_map(const Realisation& Rc, const std::vector<ld>& sc, const Realisati
 }
 }  // namespace
 
-bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, bool want_y32, FilterPlan* P, const char** msg)
+bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, bool want_y32, FilterPlan* P, const char** msg,
+                      int rerun_lt)
 {
     static const char* e_k = "n_sos must be 1..4";
     static const char* e_d = "decimation must be one of 1,2,4,8,16,32";
@@ -417,7 +418,7 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, 
     // (the rerun kernel of full-rate streams stages nothing: its run length comes from the input tile)
     P->rerun = iir_is_rerun(K, D, P->par);
     P->y32 = !P->rerun && want_y32 && iir_has_y32(K, P->par);
-    P->LT = P->rerun ? iir_rerun_len(K) : iir_run_len(K, D, P->y32);
+    P->LT = P->rerun ? (rerun_lt > 0 ? rerun_lt : iir_rerun_len(K)) : iir_run_len(K, D, P->y32);
     P->NK = P->LT / D;
     for (int k = 0; k < K; k++) {
         P->tables.a1[k] = (double)F.a1[k]; P->tables.a2[k] = (double)F.a2[k];

@@ -37,7 +37,9 @@ struct FilterPlan {
 
 // false (with msg) if the cascade cannot be handled (b0 == 0, non-finite coefficients, ...)
 // want_y32: the output is plain CF32 (float-staged kernels, longer runs) - plan->y32 says whether they will be used
-bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, bool want_y32, FilterPlan* plan, const char** msg);
+// rerun_lt > 0: run length of a rerun plan (the library keeps a second, short-run plan for small submits)
+bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, bool want_y32, FilterPlan* plan, const char** msg,
+                      int rerun_lt = 0);
 
 // A^n in REFERENCE state coordinates (row-major S x S doubles)
 void plan_shard_matrix(const FilterPlan& plan, uint64_t n, double* m);
