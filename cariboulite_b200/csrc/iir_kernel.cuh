@@ -22,7 +22,10 @@
 #ifndef CBL_P1_UNROLL
 #define CBL_P1_UNROLL 8
 #endif
-namespace cbl { constexpr int kP1Unroll = CBL_P1_UNROLL; }
+#ifndef CBL_P3_UNROLL
+#define CBL_P3_UNROLL 5          // float-staged phase 3: up to this many chunks of four kept outputs are unrolled completely
+#endif                           // (R[m][c] become constant-bank operands of the DFMAs instead of LDC.64 loads: C4 1.054 -> 1.027 ms)
+namespace cbl { constexpr int kP1Unroll = CBL_P1_UNROLL; constexpr int kP3Unroll = CBL_P3_UNROLL; }
 
 namespace cbl {
 
@@ -231,6 +234,7 @@ struct IirCfg {
     static constexpr int YSLOT_BYTES   = Y32 ? 256 : 512;      // one kept output of all 32 lanes: float2 / 2 doubles each
     static constexpr int YSTAGE_BYTES  = NK * YSLOT_BYTES;     // one tile's zero-state outputs; kIirStageBufs of them per warp
     static constexpr int SCRATCH_BYTES = 2 * S * 8 * 2;        // S_in broadcast + spare
+    static constexpr int P3U = (NK / 4 <= kP3Unroll) ? (NK / 4 > 0 ? NK / 4 : 1) : 1;   // phase-3 chunks unrolled (all or none)
     static constexpr int WARP_BYTES = RING_BYTES + kIirStageBufs * YSTAGE_BYTES + SCRATCH_BYTES;
     // 227 KiB per CTA minus the alignment slack of the carve-up
     static constexpr int SMEM_WARPS = (232448 - 1024) / (WARP_BYTES + STAGES * 8);
@@ -613,7 +617,7 @@ iir_scan_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                     // staged values are gain * y_zs already, T.R is gain * R (run_iir scales it for these launches)
                     float2* o = reinterpret_cast<float2*>(P.out) + o0;
                     static_assert(C::NK % 4 == 0, "kept outputs per run come in chunks of 4");
-#pragma unroll 1
+#pragma unroll (C::P3U)
                     for (int m0 = 0; m0 < C::NK; m0 += 4) {
                         float2 r[4];
 #pragma unroll
