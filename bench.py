@@ -642,9 +642,11 @@ def c5_leg(a, cb, torch, dist, dev, stream, rank, local_rank, world, barrier, ma
     torch.cuda.synchronize(dev); barrier()
     assert ctx.wait()[0] == n
     ms = max_over_ranks(e0.elapsed_time(e1)) / reps
-    pass_ms, hand_ms = ctx.shard_profile()
-    hand_ms = max_over_ranks(hand_ms)
+    pass_ms, hand_own = ctx.shard_profile()
+    hand_ms = max_over_ranks(hand_own)
+    hand_min = -max_over_ranks(-hand_own)      # the rank that finished pass 1 last waits for nobody: the pure cost
     fix = int(ctx.fixup_samples(n))
+    mode = ctx.shard_mode
     ctx.close()
     del d_w, d_out
     torch.cuda.empty_cache()
@@ -677,11 +679,13 @@ def c5_leg(a, cb, torch, dist, dev, stream, rank, local_rank, world, barrier, ma
     return {"workload": "C5: one %d-word stream time-chunked over %d GPU(s), %d call(s) of %d words per rank, fused "
                         "unpack->order-%d LPF->decimate-by-%d, state hand-off on the device" % (total, world, calls, n, FILTER[0], DECIM),
             "words_total": total, "words_per_rank_per_call": n, "calls": calls, "value": v, "unit": UNIT,
-            "ms_per_pass": ms, "ms_per_call": ms / calls, "pass1_ms": pass_ms, "handoff_ms": hand_ms,
-            "handoff_what": "ncclAllGather + composition kernel + fix-up of the leading tiles (device time, max over ranks)",
+            "ms_per_pass": ms, "ms_per_call": ms / calls, "pass1_ms": pass_ms, "handoff_ms": hand_ms, "handoff_ms_min_over_ranks": hand_min,
+            "handoff_what": "exchange of the end vectors + composition kernel + fix-up of the leading tiles: device time from the end of a "
+                            "rank's pass 1; the max over ranks includes waiting for the slowest rank's pass 1, the min is the rank that waits for nobody",
             "fixup_samples": fix, "rel_rms": prefix, "rel_rms_what": "first min(2^26, shard) samples against the sequential CPU oracle",
             "worst_boundary_window": worst_win, "efficiency_vs_c4_kernel": v / c4_value,
-            "shard_gib": n * 4 / 2**30, "api": "caribou_cuda_shard_submit"}
+            "shard_gib": n * 4 / 2**30, "api": "caribou_cuda_shard_submit",
+            "handoff_mode": {0: "ncclAllGather", 1: "ncclSend/ncclRecv chain", 2: "peer stores over NVLink (CUDA IPC) + flags"}[mode]}
 
 
 def time_launches(torch, stream, fn, sync, reps=10, warm=3):

@@ -65,7 +65,7 @@ def MEM_IO(mem_in, mem_out):
 
 
 SHARD_ID_BYTES = 128
-SHARD_ALLGATHER, SHARD_CHAIN = 0, 1
+SHARD_ALLGATHER, SHARD_CHAIN, SHARD_PEER = 0, 1, 2
 
 
 class Result(C.Structure):
@@ -144,6 +144,7 @@ def lib():
         "caribou_cuda_shard_init": (i, [vp, i, i, vp]),
         "caribou_cuda_shard_attach_comm": (i, [vp, i, i, vp]),
         "caribou_cuda_shard_set_mode": (i, [vp, i]),
+        "caribou_cuda_shard_mode": (i, [vp]),
         "caribou_cuda_shard_submit": (i, [vp, i, vp, sz, sz, vp, sz]),
         "caribou_cuda_shard_begin": (i, [vp, i, vp, sz, sz, vp, sz]),
         "caribou_cuda_shard_gather_buffer": (vp, [vp, C.POINTER(sz)]),
@@ -178,7 +179,7 @@ EXPORTED_SYMBOLS = [
     "caribou_cuda_async_ring", "caribou_cuda_async_close",
     "caribou_cuda_stream_results", "caribou_cuda_radio_read_cf32",
     "caribou_cuda_shard_unique_id", "caribou_cuda_shard_init", "caribou_cuda_shard_attach_comm",
-    "caribou_cuda_shard_set_mode", "caribou_cuda_shard_submit", "caribou_cuda_shard_begin",
+    "caribou_cuda_shard_set_mode", "caribou_cuda_shard_mode", "caribou_cuda_shard_submit", "caribou_cuda_shard_begin",
     "caribou_cuda_shard_gather_buffer", "caribou_cuda_shard_finish", "caribou_cuda_shard_exchange_local",
     "caribou_cuda_shard_profile",
 ]
@@ -317,6 +318,10 @@ class Context:
 
     def shard_set_mode(self, mode):
         return self._check(lib().caribou_cuda_shard_set_mode(self.h, mode))
+
+    @property
+    def shard_mode(self):
+        return self._check(lib().caribou_cuda_shard_mode(self.h))
 
     def shard_submit(self, in_kind, x, n_samples, out, in_stride=0, out_stride=0):
         return self._check(lib().caribou_cuda_shard_submit(self.h, in_kind, _ptr(x), n_samples, in_stride, _ptr(out), out_stride))

@@ -1130,6 +1130,10 @@ int64_t caribou_cuda_wait(caribou_cuda_ctx* c, caribou_cuda_result* res)
     if (resolve_queue(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     int64_t ret = c->last_ret, ret_b = 0;
     if (c->last_is_shard && c->h_counters->any_misaligned != 0) ret = CARIBOU_CUDA_ERR_SYNC;   // shards are aligned chunks or nothing
+    if (c->last_is_shard && c->h_sflags[3 * (size_t)c->cfg.n_streams + 1] != 0) {
+        set_error("time sharding: a peer's end vector never arrived");
+        return CARIBOU_CUDA_ERR;
+    }
     if (c->last_is_unpack) {
         const int nsub = n_subs_of(c);
         int64_t r[2] = {0, 0};

@@ -8,6 +8,10 @@
 //                   s_in(g) = sum_{j<g} M^(g-1-j) f_j + M^g carry ,  carry' = sum_{j<G} M^(G-1-j) f_j + M^G carry
 //               chain:                ncclRecv s_in(g) from g-1, s_in(g+1) = M s_in(g) + f_g, ncclSend to g+1,
 //                                     the last rank broadcasts the carry (G-1 serial hops)
+//               peer (default when the GPUs can map each other's memory): every rank's exchange buffer is opened in
+//                   every other rank's process (CUDA IPC, handles all-gathered once through NCCL); a one-CTA kernel
+//                   stores f_g straight into all peers' buffers over NVLink and releases a sequence flag, the
+//                   composition kernel acquires the flags - no collective launch on the path at all
 //             M = A^n in kernel coordinates; its powers are computed on the host once per shard length
 //   fix-up    the leading tiles a non-zero incoming state can still change above 2^-60 are filtered again from
 //             s_in(g), read from device memory; the context's state becomes carry', so calls chain like on one GPU
@@ -20,6 +24,7 @@
 // host-side (numpy, long double) statement of the same composition for the CPU tests.
 #include <dlfcn.h>
 #include <nccl.h>
+#include <stdlib.h>
 #include <string.h>
 #include <mutex>
 #include <new>
@@ -35,6 +40,7 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
@@ -56,13 +62,14 @@ static NcclApi* nccl_api()
         api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
         api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
         api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
+        api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
         api.Send = reinterpret_cast<decltype(api.Send)>(sym("ncclSend"));
         api.Recv = reinterpret_cast<decltype(api.Recv)>(sym("ncclRecv"));
         api.Broadcast = reinterpret_cast<decltype(api.Broadcast)>(sym("ncclBroadcast"));
         api.GroupStart = reinterpret_cast<decltype(api.GroupStart)>(sym("ncclGroupStart"));
         api.GroupEnd = reinterpret_cast<decltype(api.GroupEnd)>(sym("ncclGroupEnd"));
         api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
-        if (api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.Send && api.Recv &&
+        if (api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.AllReduce && api.Send && api.Recv &&
             api.Broadcast && api.GroupStart && api.GroupEnd && api.GetErrorString)
             api.handle = h;
     });
@@ -93,6 +100,14 @@ struct Shard {
     double* d_carry = nullptr;      // [per_rank]  state after the last rank's shard
     double* d_mpow = nullptr;       // [world + 1][S * S]  powers of M = A^n (kernel coordinates)
     uint64_t mpow_n = 0;            // shard length the powers were computed for (0: none)
+    // peer exchange (mode 2): d_px = [2 parities][world][per_rank] doubles, then [2][world] sequence flags; peers store into it
+    bool peer_ok = false;
+    double* d_px = nullptr;
+    double** d_peers = nullptr;     // [world] every rank's d_px in this process's address space
+    std::vector<void*> peer_maps;   // what cudaIpcOpenMemHandle returned (to close)
+    int* d_perr = nullptr;          // set by a composition kernel that gave up waiting for a peer's flag
+    unsigned long long seq = 0;     // sharded calls so far
+    bool committed = false;         // the composition kernel of this call has written the carry into the context's state
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};   // profiling: start, after pass 1, end
     bool ev_valid = false;
     // the call between begin and finish
@@ -109,6 +124,10 @@ void shard_release(Shard* s)
     if (s->d_work) cudaFree(s->d_work);
     if (s->d_carry) cudaFree(s->d_carry);
     if (s->d_mpow) cudaFree(s->d_mpow);
+    for (void* m : s->peer_maps) if (m) cudaIpcCloseMemHandle(m);
+    if (s->d_px) cudaFree(s->d_px);
+    if (s->d_peers) cudaFree(s->d_peers);
+    if (s->d_perr) cudaFree(s->d_perr);
     for (cudaEvent_t e : s->ev) if (e) cudaEventDestroy(e);
     delete s;
 }
@@ -123,10 +142,55 @@ struct ComposeParams {
     const double* mpow;         // [world + 1][S * S]
     double* s_in;               // [n_comp]
     double* carry_out;          // [n_comp]
+    // peer mode: sequence flags of the ranks' end vectors (nullptr: f is complete when the kernel starts)
+    const unsigned long long* flags;
+    unsigned long long seq;
+    int* err;
+    // single-CTA launches also commit the carry into the context's state (one launch less on the hand-off path),
+    // unless *gate says the shard was misaligned
+    double* commit;
+    const int32_t* gate;
 };
+
+// one system-scope acquire load / release store (the flags live in memory other GPUs write)
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v)
+{
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// peer mode: this rank's end vector into slot `rank` of EVERY rank's exchange buffer (its own included), then the flag
+__global__ void shard_push_kernel(double* const* peers, const double* f_own, uint32_t n_comp, int world, int rank,
+                                  size_t par_off, size_t flag_off, unsigned long long seq)
+{
+    for (int j = 0; j < world; j++) {
+        double* dst = peers[j] + par_off + (size_t)rank * n_comp;
+        for (uint32_t t = threadIdx.x; t < n_comp; t += blockDim.x) dst[t] = f_own[t];
+    }
+    __threadfence_system();
+    __syncthreads();
+    for (int j = threadIdx.x; j < world; j += blockDim.x)
+        st_release_sys(reinterpret_cast<unsigned long long*>(peers[j] + flag_off) + rank, seq);
+}
 
 __global__ void shard_compose_kernel(const ComposeParams p)
 {
+    if (p.flags != nullptr) {
+        // wait until every rank's end vector of this call has landed (bounded: a peer that died must not hang the GPU)
+        for (int j = threadIdx.x; j < p.world; j += blockDim.x) {
+            unsigned long long spins = 0;
+            while (ld_acquire_sys(p.flags + j) != p.seq) {
+                __nanosleep(64);
+                if (++spins > (1ull << 22)) { *p.err = 1; break; }     // a few seconds
+            }
+        }
+        __syncthreads();
+    }
     for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < p.n_comp; t += gridDim.x * blockDim.x) {
         const int row = (int)(t % (uint32_t)p.S);
         const uint32_t vec = t - (uint32_t)row;                 // first component of this (stream, rail) vector
@@ -143,6 +207,10 @@ __global__ void shard_compose_kernel(const ComposeParams p)
         for (int j = 0; j < p.world; j++) co += mv(p.world - 1 - j, p.f + (size_t)j * p.n_comp);
         p.s_in[t] = sin;
         p.carry_out[t] = co;
+    }
+    if (p.commit != nullptr && (p.gate == nullptr || *p.gate == 0)) {      // gridDim.x == 1: every read of the old carry is done
+        __syncthreads();
+        for (uint32_t t = threadIdx.x; t < p.n_comp; t += blockDim.x) p.commit[t] = p.carry_out[t];
     }
 }
 
@@ -180,6 +248,63 @@ static int shard_alloc(caribou_cuda_ctx* c, int rank, int world)
     CBL_CHECK(cudaMemsetAsync(s->d_f, 0, (size_t)world * s->per_rank * 8, c->stream));
     for (cudaEvent_t& e : s->ev) CBL_CHECK(cudaEventCreate(&e));
     CBL_CHECK(cudaStreamSynchronize(c->stream));
+    return CARIBOU_CUDA_OK;
+}
+
+// Peer exchange set-up (once per communicator): every rank's exchange buffer is mapped into every other rank's process.
+// All ranks take the same decision: the outcome of the mapping is min-reduced over the communicator.
+static int shard_peer_setup(caribou_cuda_ctx* c)
+{
+    Shard* s = c->shard;
+    NcclApi* a = nccl_api();
+    if (!a || !s->comm || s->world < 2 || getenv("CARIBOU_CUDA_NO_PEER")) return CARIBOU_CUDA_OK;
+    const size_t doubles = 2 * (size_t)s->world * s->per_rank + 2 * (size_t)s->world;
+    CBL_CHECK(cudaMalloc(&s->d_px, doubles * 8));
+    CBL_CHECK(cudaMemsetAsync(s->d_px, 0, doubles * 8, c->stream));
+    CBL_CHECK(cudaMalloc(&s->d_perr, 4));
+    CBL_CHECK(cudaMemsetAsync(s->d_perr, 0, 4, c->stream));
+    CBL_CHECK(cudaMalloc(&s->d_peers, (size_t)s->world * sizeof(double*)));
+    // handles: [world] x (64-byte handle + 1 int "ok so far")
+    struct Slot { cudaIpcMemHandle_t h; int ok; int pad[15]; };
+    static_assert(sizeof(Slot) == 128, "slot layout");
+    std::vector<Slot> slots((size_t)s->world);
+    memset(slots.data(), 0, slots.size() * sizeof(Slot));
+    Slot& mine = slots[(size_t)s->rank];
+    mine.ok = cudaIpcGetMemHandle(&mine.h, s->d_px) == cudaSuccess ? 1 : 0;
+    cudaGetLastError();
+    Slot* d_slots = nullptr;
+    CBL_CHECK(cudaMalloc(&d_slots, slots.size() * sizeof(Slot)));
+    auto fail = [&](void) { cudaFree(d_slots); return CARIBOU_CUDA_ERR; };
+    if (!cuda_ok(cudaMemcpyAsync(d_slots + s->rank, &mine, sizeof(Slot), cudaMemcpyHostToDevice, c->stream), "H2D") ||
+        !nccl_ok(a, a->AllGather(d_slots + s->rank, d_slots, sizeof(Slot), ncclChar, s->comm, c->stream), "ncclAllGather(handles)") ||
+        !cuda_ok(cudaMemcpyAsync(slots.data(), d_slots, slots.size() * sizeof(Slot), cudaMemcpyDeviceToHost, c->stream), "D2H") ||
+        !cuda_ok(cudaStreamSynchronize(c->stream), "cudaStreamSynchronize")) return fail();
+    int ok = 1;
+    std::vector<double*> ptrs((size_t)s->world, nullptr);
+    for (int j = 0; j < s->world && ok; j++) {
+        if (!slots[(size_t)j].ok) { ok = 0; break; }
+        if (j == s->rank) { ptrs[(size_t)j] = s->d_px; continue; }
+        void* m = nullptr;
+        if (cudaIpcOpenMemHandle(&m, slots[(size_t)j].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; break; }
+        s->peer_maps.push_back(m);
+        ptrs[(size_t)j] = static_cast<double*>(m);
+    }
+    // one verdict for all ranks
+    int* d_ok = reinterpret_cast<int*>(d_slots);
+    if (!cuda_ok(cudaMemcpyAsync(d_ok, &ok, 4, cudaMemcpyHostToDevice, c->stream), "H2D") ||
+        !nccl_ok(a, a->AllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, s->comm, c->stream), "ncclAllReduce(ok)") ||
+        !cuda_ok(cudaMemcpyAsync(&ok, d_ok, 4, cudaMemcpyDeviceToHost, c->stream), "D2H") ||
+        !cuda_ok(cudaStreamSynchronize(c->stream), "cudaStreamSynchronize")) return fail();
+    cudaFree(d_slots);
+    if (!ok) {       // some pair of GPUs cannot map each other: everybody stays on the NCCL modes
+        for (void* m : s->peer_maps) if (m) cudaIpcCloseMemHandle(m);
+        s->peer_maps.clear();
+        return CARIBOU_CUDA_OK;
+    }
+    CBL_CHECK(cudaMemcpyAsync(s->d_peers, ptrs.data(), ptrs.size() * sizeof(double*), cudaMemcpyHostToDevice, c->stream));
+    CBL_CHECK(cudaStreamSynchronize(c->stream));
+    s->peer_ok = true;
+    s->mode = 2;
     return CARIBOU_CUDA_OK;
 }
 
@@ -263,23 +388,37 @@ static int shard_fixup(caribou_cuda_ctx* c)
             return CARIBOU_CUDA_ERR;
     }
     // the stream's state after this call: every rank holds the same carry
-    launch_commit_state(c->d_state, s->d_carry, (size_t)c->cfg.n_streams, (size_t)2 * P.S, gate, 0, c->stream);
-    c->launches++;
+    if (!s->committed) {
+        launch_commit_state(c->d_state, s->d_carry, (size_t)c->cfg.n_streams, (size_t)2 * P.S, gate, 0, c->stream);
+        c->launches++;
+    }
     c->pos += s->n * (uint64_t)s->world;
+    if (s->d_perr)   // a composition kernel that gave up on a peer's flag: wait() reports the call as failed
+        CBL_CHECK(cudaMemcpyAsync(c->h_sflags + 3 * (size_t)c->cfg.n_streams + 1, s->d_perr, 4, cudaMemcpyDeviceToHost, c->stream));
     if (c->profiling) { CBL_CHECK(cudaEventRecord(s->ev[2], c->stream)); s->ev_valid = true; }
     s->open = false;
     CBL_CHECK(cudaGetLastError());
     return CARIBOU_CUDA_OK;
 }
 
-static int shard_compose(caribou_cuda_ctx* c)
+static int shard_compose(caribou_cuda_ctx* c, bool peer = false)
 {
     Shard* s = c->shard;
     ComposeParams p;
     p.S = c->plan.S; p.world = s->world; p.rank = s->rank;
     p.n_comp = (uint32_t)s->per_rank;
     p.f = s->d_f; p.carry = c->d_state; p.mpow = s->d_mpow; p.s_in = s->d_sin; p.carry_out = s->d_carry;
+    p.flags = nullptr; p.seq = 0; p.err = s->d_perr;
+    if (peer) {
+        const size_t par = (size_t)(s->seq & 1);
+        p.f = s->d_px + par * s->world * s->per_rank;
+        p.flags = reinterpret_cast<const unsigned long long*>(s->d_px + 2 * (size_t)s->world * s->per_rank) + par * s->world;
+        p.seq = s->seq;
+    }
     const unsigned threads = 128, grid = (unsigned)std::min<size_t>((s->per_rank + threads - 1) / threads, 64);
+    p.commit = grid == 1 ? c->d_state : nullptr;
+    p.gate = s->in_kind == IN_WORDS ? &c->d_counters->any_misaligned : nullptr;
+    s->committed = grid == 1;
     shard_compose_kernel<<<grid, threads, 0, c->stream>>>(p);
     c->launches++;
     CBL_CHECK(cudaGetLastError());
@@ -314,7 +453,7 @@ int caribou_cuda_shard_init(caribou_cuda_ctx* c, int rank, int world, const void
     memcpy(&u, id, sizeof(u));
     CBL_NCCL(a, a->CommInitRank(&c->shard->comm, world, u, rank));
     c->shard->own_comm = true;
-    return CARIBOU_CUDA_OK;
+    return shard_peer_setup(c);
 }
 
 int caribou_cuda_shard_attach_comm(caribou_cuda_ctx* c, int rank, int world, void* nccl_comm)
@@ -324,14 +463,21 @@ int caribou_cuda_shard_attach_comm(caribou_cuda_ctx* c, int rank, int world, voi
     if (shard_alloc(c, rank, world) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     c->shard->comm = static_cast<ncclComm_t>(nccl_comm);
     c->shard->own_comm = false;
-    return CARIBOU_CUDA_OK;
+    return shard_peer_setup(c);
 }
 
 int caribou_cuda_shard_set_mode(caribou_cuda_ctx* c, int mode)
 {
-    if (!c || !c->shard || mode < 0 || mode > 1) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    if (!c || !c->shard || mode < 0 || mode > 2) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
+    if (mode == 2 && !c->shard->peer_ok) { set_error("peer exchange is not available on this communicator"); return CARIBOU_CUDA_ERR; }
     c->shard->mode = mode;
     return CARIBOU_CUDA_OK;
+}
+
+int caribou_cuda_shard_mode(caribou_cuda_ctx* c)
+{
+    if (!c || !c->shard) { set_error("call caribou_cuda_shard_init first"); return CARIBOU_CUDA_ERR; }
+    return c->shard->mode;
 }
 
 int caribou_cuda_shard_begin(caribou_cuda_ctx* c, int in_kind, const void* in, size_t n, size_t in_stride, void* out, size_t out_stride)
@@ -367,6 +513,16 @@ int caribou_cuda_shard_submit(caribou_cuda_ctx* c, int in_kind, const void* in, 
     NcclApi* a = nccl_api();
     if (!a) return CARIBOU_CUDA_ERR;
     double* f_own = s->d_f + (size_t)s->rank * s->per_rank;
+    if (s->mode == 2) {
+        s->seq++;
+        const size_t par = (size_t)(s->seq & 1);
+        shard_push_kernel<<<1, 128, 0, c->stream>>>(s->d_peers, f_own, (uint32_t)s->per_rank, s->world, s->rank,
+                                                    par * s->world * s->per_rank,
+                                                    2 * (size_t)s->world * s->per_rank + par * s->world, s->seq);
+        c->launches++;
+        if (shard_compose(c, true) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        return shard_fixup(c);
+    }
     if (s->mode == 0) {
         CBL_NCCL(a, a->AllGather(f_own, s->d_f, s->per_rank, ncclDouble, s->comm, c->stream));
         if (shard_compose(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
@@ -381,6 +537,7 @@ int caribou_cuda_shard_submit(caribou_cuda_ctx* c, int in_kind, const void* in, 
     c->launches++;
     if (s->rank < s->world - 1) CBL_NCCL(a, a->Send(s->d_carry, s->per_rank, ncclDouble, s->rank + 1, s->comm, c->stream));
     CBL_NCCL(a, a->Broadcast(s->d_carry, s->d_carry, s->per_rank, ncclDouble, s->world - 1, s->comm, c->stream));
+    s->committed = false;
     return shard_fixup(c);
 }
 

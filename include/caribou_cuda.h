@@ -244,7 +244,11 @@ int    caribou_cuda_filter_fixup(caribou_cuda_ctx* ctx, int in_kind, const void*
 int    caribou_cuda_shard_unique_id(void* id /* CARIBOU_CUDA_SHARD_ID_BYTES */);
 int    caribou_cuda_shard_init(caribou_cuda_ctx* ctx, int rank, int world, const void* id);
 int    caribou_cuda_shard_attach_comm(caribou_cuda_ctx* ctx, int rank, int world, void* nccl_comm);
-int    caribou_cuda_shard_set_mode(caribou_cuda_ctx* ctx, int mode);   /* 0: all-gather (default), 1: send/recv chain */
+/* 0: ncclAllGather, 1: ncclSend/ncclRecv chain, 2: peer stores - a kernel writes the end vector straight into every
+ * rank's exchange buffer over NVLink (buffers mapped with CUDA IPC at init; the default whenever every pair of GPUs of
+ * the communicator can map each other, else 0).  All ranks must use the same mode.  caribou_cuda_shard_mode returns it. */
+int    caribou_cuda_shard_set_mode(caribou_cuda_ctx* ctx, int mode);
+int    caribou_cuda_shard_mode(caribou_cuda_ctx* ctx);
 int    caribou_cuda_shard_submit(caribou_cuda_ctx* ctx, int in_kind, const void* in, size_t n_samples,
                                  size_t in_stride_elems, void* out, size_t out_stride_elems);
 int    caribou_cuda_shard_begin(caribou_cuda_ctx* ctx, int in_kind, const void* in, size_t n_samples,

@@ -47,7 +47,9 @@ def main():
     ids = [cb.shard_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(ids, src=0)
     ctx.shard_init(rank, world, ids[0])
-    ctx.shard_set_mode(cb.SHARD_CHAIN if a.mode == "chain" else cb.SHARD_ALLGATHER)
+    default_mode = ctx.shard_mode
+    if a.mode != "default":
+        ctx.shard_set_mode({"chain": cb.SHARD_CHAIN, "allgather": cb.SHARD_ALLGATHER, "peer": cb.SHARD_PEER}[a.mode])
     ctx.set_profiling(True)
     d_w = torch.empty(n, dtype=torch.int32, device=dev)
     d_out = torch.zeros((a.calls, n // D, 2), dtype=torch.float32, device=dev)
@@ -87,7 +89,7 @@ def main():
             wmax = max(wmax, float(ew))
         err = {"rel_rms": [float(v) for v in e], "worst_boundary_window": wmax}
         ok = bool(np.all(e <= 1e-5) and wmax <= 1e-5)
-        print(json.dumps({"world": world, "mode": a.mode, "words_per_rank_per_call": n, "calls": a.calls, "ok": ok,
+        print(json.dumps({"world": world, "mode": a.mode, "default_mode": default_mode, "mode_used": ctx.shard_mode, "words_per_rank_per_call": n, "calls": a.calls, "ok": ok,
                           "err": err, "fixup_samples": int(ctx.fixup_samples(n)),
                           "process_ms_per_call": [round(t * 1e3, 3) for t in t_hand],
                           "pass_ms": [round(t[0], 4) for t in t_dev], "handoff_fixup_ms": [round(t[1], 4) for t in t_dev]}),

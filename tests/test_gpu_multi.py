@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("mode", ["allgather", "chain"])
+@pytest.mark.parametrize("mode", ["allgather", "chain", "peer"])
 def test_time_chunked_stream_over_gpus(torch_cuda, mode):
     n = torch_cuda.cuda.device_count()
     if n < 2:
