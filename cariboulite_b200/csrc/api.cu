@@ -363,10 +363,11 @@ static int run_unpack(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, s
         set_error("unpack: index lists are 32-bit - at most 2^32 words per batch when they are requested");
         return CARIBOU_CUDA_ERR;
     }
-    if (!c->desc_inv.reserve((size_t)n_tiles * 20 + 16) || !c->desc_syn.reserve(((size_t)ns + 1) * 16)) return CARIBOU_CUDA_ERR;
-    // running (n_invalid, n_sync) after each stream's launch: slot s is read by launch s, slot s + 1 written by it
+    if (!c->desc_inv.reserve((size_t)n_tiles * 20 + 32) || !c->desc_syn.reserve(((size_t)ns + 1) * 16)) return CARIBOU_CUDA_ERR;
+    // running (n_invalid, n_sync): launch k reads what launch k - 1 wrote.  The first launch reads zeros from the 16
+    // bytes in front of the tile counts (one memset covers both), the last one writes the context's counters.
+    uint64_t* zero_totals = c->desc_inv.as<uint64_t>();
     uint64_t* run_totals = c->desc_syn.as<uint64_t>();
-    CBL_CHECK(cudaMemsetAsync(run_totals, 0, 16, c->stream));
     const bool prof = c->profiling && !c->has_filter;
     if (prof) prof_mark(c, 0);
     for (uint32_t st = st0; st < st1; st++) {
@@ -400,27 +401,25 @@ static int run_unpack(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, s
         p.inv_idx = o.invalid_idx; p.inv_cap = o.invalid_cap;
         p.syn_idx = o.sync_idx; p.syn_cap = o.sync_cap;
         p.index_base = (uint64_t)st * (nbytes / 4);
-        p.tile_counts = c->desc_inv.as<uint64_t>();
+        p.tile_counts = c->desc_inv.as<uint64_t>() + 2;
         p.tile_offsets = p.tile_counts + n_tiles;
         p.work = reinterpret_cast<uint32_t*>(p.tile_offsets + n_tiles);
         p.n_work = p.work + n_tiles;
-        p.totals_in = run_totals + 2 * (size_t)(st - st0);
-        p.totals_out = run_totals + 2 * (size_t)(st - st0) + 2;
+        p.totals_in = st == st0 ? zero_totals : run_totals + 2 * (size_t)(st - st0 - 1);
+        p.totals_out = st + 1 == st1 ? c->d_counters->totals : run_totals + 2 * (size_t)(st - st0);
         p.n_tiles = n_tiles;
-        CBL_CHECK(cudaMemsetAsync(c->desc_inv.p, 0, (size_t)n_tiles * 8, c->stream));
+        if (st == st0) CBL_CHECK(cudaMemsetAsync(zero_totals, 0, 16 + (size_t)n_tiles * 8, c->stream));
+        else CBL_CHECK(cudaMemsetAsync(p.tile_counts, 0, (size_t)n_tiles * 8, c->stream));
         c->launches += (uint64_t)launch_unpack(p, c->num_sms, c->stream);
     }
     if (prof) prof_mark(c, 1);
-    CBL_CHECK(cudaMemcpyAsync(c->d_counters->totals, run_totals + 2 * (size_t)(st1 - st0), 16, cudaMemcpyDeviceToDevice, c->stream));
     CBL_CHECK(cudaGetLastError());
     return CARIBOU_CUDA_OK;
 }
 
 int mirror_counters(caribou_cuda_ctx* c)
 {
-    CBL_CHECK(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
-    CBL_CHECK(cudaMemcpyAsync(c->h_first_bad, c->d_first_bad, (size_t)c->cfg.n_streams * 2 * 4, cudaMemcpyDeviceToHost, c->stream));
-    CBL_CHECK(cudaMemcpyAsync(c->h_sflags, c->d_sflags, ((size_t)c->cfg.n_streams * 3 + 4) * 4, cudaMemcpyDeviceToHost, c->stream));
+    CBL_CHECK(cudaMemcpyAsync(c->h_ctrl, c->d_ctrl, c->ctrl_bytes, cudaMemcpyDeviceToHost, c->stream));
     return CARIBOU_CUDA_OK;
 }
 
@@ -474,13 +473,19 @@ caribou_cuda_ctx* caribou_cuda_create(const caribou_cuda_config* cfg_in)
     }
     const size_t ns = (size_t)cfg.n_streams;
     c->win0 = 0; c->win_cnt = (uint32_t)ns;
+    // one control block on the device and its page-locked mirror (one copy per submit brings all of it down):
+    // [Counters][first_bad: ns x 2][sflags: 3 ns + 4]
+    static_assert(sizeof(Counters) % 8 == 0, "control block layout");
+    c->ctrl_bytes = sizeof(Counters) + ns * 2 * 4 + (ns * 3 + 4) * 4;
     if (!cuda_ok(cudaMalloc(&c->d_ticket, 256), "cudaMalloc") ||
-        !cuda_ok(cudaMalloc(&c->d_counters, sizeof(Counters)), "cudaMalloc") ||
-        !cuda_ok(cudaMalloc(&c->d_first_bad, ns * 2 * 4), "cudaMalloc") ||
-        !cuda_ok(cudaMallocHost(&c->h_counters, sizeof(Counters)), "cudaMallocHost") ||
-        !cuda_ok(cudaMallocHost(&c->h_first_bad, ns * 2 * 4), "cudaMallocHost") ||
-        !cuda_ok(cudaMalloc(&c->d_sflags, (ns * 3 + 4) * 4), "cudaMalloc") ||
-        !cuda_ok(cudaMallocHost(&c->h_sflags, (ns * 3 + 4) * 4), "cudaMallocHost")) return fail();
+        !cuda_ok(cudaMalloc(&c->d_ctrl, c->ctrl_bytes), "cudaMalloc") ||
+        !cuda_ok(cudaMallocHost(&c->h_ctrl, c->ctrl_bytes), "cudaMallocHost")) return fail();
+    c->d_counters = reinterpret_cast<Counters*>(c->d_ctrl);
+    c->h_counters = reinterpret_cast<Counters*>(c->h_ctrl);
+    c->d_first_bad = reinterpret_cast<int32_t*>(c->d_ctrl + sizeof(Counters));
+    c->h_first_bad = reinterpret_cast<int32_t*>(c->h_ctrl + sizeof(Counters));
+    c->d_sflags = c->d_first_bad + ns * 2;
+    c->h_sflags = c->h_first_bad + ns * 2;
     cudaMemset(c->d_sflags, 0, (ns * 3 + 4) * 4);
     cudaMemset(c->d_sflags + ns, 0x7f, ns * 4);
     memset(c->h_sflags, 0, (ns * 3 + 4) * 4);
@@ -539,13 +544,9 @@ void caribou_cuda_destroy(caribou_cuda_ctx* c)
     if (c->h2d_stream) cudaStreamDestroy(c->h2d_stream);
     if (c->d2h_stream) cudaStreamDestroy(c->d2h_stream);
     if (c->d_ticket) cudaFree(c->d_ticket);
-    if (c->d_counters) cudaFree(c->d_counters);
-    if (c->d_first_bad) cudaFree(c->d_first_bad);
+    if (c->d_ctrl) cudaFree(c->d_ctrl);
     if (c->d_tone) cudaFree(c->d_tone);
-    if (c->h_counters) cudaFreeHost(c->h_counters);
-    if (c->h_first_bad) cudaFreeHost(c->h_first_bad);
-    if (c->d_sflags) cudaFree(c->d_sflags);
-    if (c->h_sflags) cudaFreeHost(c->h_sflags);
+    if (c->h_ctrl) cudaFreeHost(c->h_ctrl);
     c->h_bounce.release();
     for (cudaEvent_t e : c->prof_ev) if (e) cudaEventDestroy(e);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);

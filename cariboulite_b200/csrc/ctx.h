@@ -115,6 +115,9 @@ struct caribou_cuda_ctx {
     // unpack
     cbl::DevBuf offs;                 // [n_streams][2][n_chunks] int32
     cbl::DevBuf desc_inv, desc_syn;
+    uint8_t* d_ctrl = nullptr;        // control block: counters, first bad chunks, per-stream flags (pointers below)
+    uint8_t* h_ctrl = nullptr;        // its page-locked mirror
+    size_t ctrl_bytes = 0;
     cbl::Counters* d_counters = nullptr;
     cbl::Counters* h_counters = nullptr;   // pinned
     int32_t* d_first_bad = nullptr;   // [n_streams][2]
