@@ -593,7 +593,7 @@ def c5_leg(a, cb, torch, dist, dev, stream, rank, local_rank, world, barrier, ma
     contiguous range [g W/G, (g+1) W/G), device-generated in place), the fused path with the C4 filter (so that the
     figure compares with the C4 kernel), IIR state handed from GPU to GPU on the device (caribou_cuda_shard_submit:
     ncclAllGather on the context's stream, composition kernel, fix-up from device memory).  At N = 1 the stream goes
-    through as 8 carried calls.  Parity against the sequential CPU oracle on a 2^26-sample prefix (rank 0) and on a
+    through as 8 carried calls.  Parity against the sequential CPU oracle on a 2^28-sample prefix (rank 0) and on a
     window straddling every shard boundary (each rank checks the one it receives)."""
     total = 1 << a.c5_log2_words
     calls = 8 if world == 1 else 1
@@ -626,7 +626,7 @@ def c5_leg(a, cb, torch, dist, dev, stream, rank, local_rank, world, barrier, ma
     one_pass()                                   # first pass from zero state: the one parity looks at
     assert ctx.wait()[0] == n
     lead, win = 1 << 16, 1 << 14
-    npre = min(1 << 26, n)
+    npre = min(1 << 28, n)
     first_heads = [d_out[k, :win // DECIM].cpu().numpy() for k in range(calls)]
     first_prefix = d_out[0, :npre // DECIM].cpu().numpy() if rank == 0 else None
     ctx.set_profiling(True)
@@ -682,7 +682,7 @@ def c5_leg(a, cb, torch, dist, dev, stream, rank, local_rank, world, barrier, ma
             "ms_per_pass": ms, "ms_per_call": ms / calls, "pass1_ms": pass_ms, "handoff_ms": hand_ms, "handoff_ms_min_over_ranks": hand_min,
             "handoff_what": "exchange of the end vectors + composition kernel + fix-up of the leading tiles: device time from the end of a "
                             "rank's pass 1; the max over ranks includes waiting for the slowest rank's pass 1, the min is the rank that waits for nobody",
-            "fixup_samples": fix, "rel_rms": prefix, "rel_rms_what": "first min(2^26, shard) samples against the sequential CPU oracle",
+            "fixup_samples": fix, "rel_rms": prefix, "rel_rms_what": "first min(2^28, shard) samples against the sequential CPU oracle",
             "worst_boundary_window": worst_win, "efficiency_vs_c4_kernel": v / c4_value,
             "shard_gib": n * 4 / 2**30, "api": "caribou_cuda_shard_submit",
             "handoff_mode": {0: "ncclAllGather", 1: "ncclSend/ncclRecv chain", 2: "peer stores over NVLink (CUDA IPC) + flags"}[mode]}
