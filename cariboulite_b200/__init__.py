@@ -151,6 +151,7 @@ def lib():
         "caribou_cuda_shard_finish": (i, [vp]),
         "caribou_cuda_shard_exchange_local": (i, [C.POINTER(vp), i]),
         "caribou_cuda_shard_profile": (i, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+        "caribou_cuda_unpack_noalloc": (i, [i, vp, i, sz, vp, sz, C.POINTER(UnpackOut), vp]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)
@@ -181,12 +182,33 @@ EXPORTED_SYMBOLS = [
     "caribou_cuda_shard_unique_id", "caribou_cuda_shard_init", "caribou_cuda_shard_attach_comm",
     "caribou_cuda_shard_set_mode", "caribou_cuda_shard_mode", "caribou_cuda_shard_submit", "caribou_cuda_shard_begin",
     "caribou_cuda_shard_gather_buffer", "caribou_cuda_shard_finish", "caribou_cuda_shard_exchange_local",
-    "caribou_cuda_shard_profile",
+    "caribou_cuda_shard_profile", "caribou_cuda_unpack_noalloc",
 ]
 
 
 def last_error():
     return lib().caribou_cuda_last_error().decode()
+
+
+NOALLOC_MAX_BYTES = 64 << 20
+NOALLOC_MAX_CHUNKS = 16384
+
+
+def unpack_noalloc(raw, nbytes, cs16=None, meta=None, cf32=None, invalid_idx=None, sync_idx=None, result=None,
+                   device=0, stream=None, channel=0, chunk_bytes=0):
+    """caribou_cuda_unpack_noalloc: kernel (a) on device buffers with the library's fixed scratch array - no
+    context, no allocation, asynchronous on `stream` (a cudaStream_t as int, None = default stream).  `result` is
+    device memory for one caribou_cuda_result (56 bytes) or None."""
+    o = UnpackOut()
+    o.cs16, o.meta, o.cf32 = _ptr(cs16), _ptr(meta), _ptr(cf32)
+    if invalid_idx is not None:
+        o.invalid_idx, o.invalid_cap = _ptr(invalid_idx), invalid_idx.numel()
+    if sync_idx is not None:
+        o.sync_idx, o.sync_cap = _ptr(sync_idx), sync_idx.numel()
+    r = lib().caribou_cuda_unpack_noalloc(device, stream, channel, chunk_bytes, _ptr(raw), nbytes, C.byref(o), _ptr(result))
+    if r != 0:
+        raise CaribouCudaError(last_error())
+    return r
 
 
 def butter_lowpass(order, fs, fc):

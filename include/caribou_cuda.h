@@ -178,6 +178,31 @@ int caribou_cuda_unpack_submit(caribou_cuda_ctx* ctx, const void* bytes, size_t 
                                size_t stream_stride_bytes, int mem,
                                const caribou_cuda_unpack_out* out);
 
+/* Kernel (a) without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same kernels and same outputs as caribou_cuda_unpack_submit on DEVICE memory for one single-channel capture,
+ * but no context: the per-chunk offsets, per-tile flag counts, their scan and the work list live in ONE fixed
+ * device array inside the library (CARIBOU_CUDA_NOALLOC_SCRATCH_BYTES per GPU that loads the library, held until the
+ * process exits).  The call makes no cudaMalloc / cudaFree / host allocation and creates no stream or event: it only
+ * queues memsets and kernels on `cuda_stream` (a cudaStream_t; NULL = the default stream) and returns without
+ * synchronising.
+ *   device        CUDA device index (made current)
+ *   channel       CARIBOU_CUDA_CH_S1G / CARIBOU_CUDA_CH_HIF (which 13-bit field is I)
+ *   chunk_bytes   read(2) granularity, 0 -> 524288; multiple of 16
+ *   d_bytes       nbytes of raw SMI data in DEVICE memory, 16-byte aligned
+ *   out           DEVICE pointers (any may be NULL; the *_b members must be NULL; index lists allowed)
+ *   d_result      DEVICE memory for one caribou_cuda_result (may be NULL): what caribou_cuda_wait would report
+ * Limits: nbytes <= CARIBOU_CUDA_NOALLOC_MAX_BYTES and ceil(nbytes / chunk_bytes) <= CARIBOU_CUDA_NOALLOC_MAX_CHUNKS;
+ * anything larger is rejected with CARIBOU_CUDA_ERR and a message (caribou_cuda_last_error), nothing is launched.
+ * Every call on a GPU shares the one array: calls are safe back to back on one stream (each clears what it needs),
+ * calls that overlap on the GPU (different streams without an event between them, or different threads) RACE. */
+#define CARIBOU_CUDA_NOALLOC_MAX_BYTES     (64u << 20)   /* 2^24 SMI words per call */
+#define CARIBOU_CUDA_NOALLOC_MAX_CHUNKS    16384
+#define CARIBOU_CUDA_NOALLOC_SCRATCH_BYTES 147520
+int caribou_cuda_unpack_noalloc(int device, void* cuda_stream, int channel, size_t chunk_bytes,
+                                const void* d_bytes, size_t nbytes, const caribou_cuda_unpack_out* out,
+                                caribou_cuda_result* d_result);
+
 /* ---------------------------------------------------------------- kernel (b): IIR + decimate
  * SoapySDR::Stream::ReadSamples' filter loop and format conversion
  * (LC/soapy_api/CaribouliteStream.cpp:282-367) on `n_samples` per stream, as a block-parallel
