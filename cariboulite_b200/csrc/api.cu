@@ -188,8 +188,12 @@ int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t
             return CARIBOU_CUDA_ERR;
         CUtensorMap tm;
         if (!make_run_tmap(&tm, d_in, LT, (int)(es / 4), n_runs, ns, (uint64_t)in_stride * es)) return CARIBOU_CUDA_ERR;
-        CBL_CHECK(cudaMemsetAsync(desc.p, 0xFF, total * 2 * P.S * 8, c->stream));      // kDescEmpty everywhere
-        CBL_CHECK(cudaMemsetAsync(c->d_ticket, 0, 4, c->stream));
+        if (c->desc_precleared) {
+            c->desc_precleared = false;       // the sharded hand-off's composition kernel has emptied both (shard.cu)
+        } else {
+            CBL_CHECK(cudaMemsetAsync(desc.p, 0xFF, total * 2 * P.S * 8, c->stream));      // kDescEmpty everywhere
+            CBL_CHECK(cudaMemsetAsync(c->d_ticket, 0, 4, c->stream));
+        }
         IirParams p;
         memset(&p, 0, sizeof(p));
         p.n_streams = ns;

@@ -117,6 +117,7 @@ struct caribou_cuda_ctx {
     cbl::DevBuf desc_inv, desc_syn;
     uint8_t* d_ctrl = nullptr;        // control block: counters, first bad chunks, per-stream flags (pointers below)
     uint8_t* h_ctrl = nullptr;        // its page-locked mirror
+    bool desc_precleared = false;     // the next run_iir finds its descriptors and ticket already emptied (shard.cu)
     size_t ctrl_bytes = 0;
     cbl::Counters* d_counters = nullptr;
     cbl::Counters* h_counters = nullptr;   // pinned

@@ -105,7 +105,8 @@ struct Shard {
     double* d_px = nullptr;
     double** d_peers = nullptr;     // [world] every rank's d_px in this process's address space
     std::vector<void*> peer_maps;   // what cudaIpcOpenMemHandle returned (to close)
-    int* d_perr = nullptr;          // set by a composition kernel that gave up waiting for a peer's flag
+    int* err_host = nullptr;        // device view of the control block's "a peer never arrived" slot in page-locked host memory
+    bool precleared = false;        // this call's composition kernel has emptied the fix-up launch's descriptors and ticket
     unsigned long long seq = 0;     // sharded calls so far
     bool committed = false;         // the composition kernel of this call has written the carry into the context's state
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};   // profiling: start, after pass 1, end
@@ -127,7 +128,6 @@ void shard_release(Shard* s)
     for (void* m : s->peer_maps) if (m) cudaIpcCloseMemHandle(m);
     if (s->d_px) cudaFree(s->d_px);
     if (s->d_peers) cudaFree(s->d_peers);
-    if (s->d_perr) cudaFree(s->d_perr);
     for (cudaEvent_t e : s->ev) if (e) cudaEventDestroy(e);
     delete s;
 }
@@ -146,10 +146,20 @@ struct ComposeParams {
     const unsigned long long* flags;
     unsigned long long seq;
     int* err;
+    int* err_host;              // the same verdict in the context's page-locked control block (what wait() reads)
     // single-CTA launches also commit the carry into the context's state (one launch less on the hand-off path),
     // unless *gate says the shard was misaligned
     double* commit;
     const int32_t* gate;
+    // peer mode: the push of this rank's end vector is the first thing the kernel does (peers == nullptr: no push)
+    double* const* peers;
+    const double* f_own;
+    size_t par_off, flag_off;
+    // the fix-up launch that follows needs its look-back descriptors empty and its ticket zero: done here instead of
+    // by two memsets on the stream (clear_n doubles of kDescEmpty; nullptr: the launch clears them itself)
+    unsigned long long* clear_desc;
+    uint32_t clear_n;
+    uint32_t* clear_ticket;
 };
 
 // one system-scope acquire load / release store (the flags live in memory other GPUs write)
@@ -165,8 +175,9 @@ __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned l
 }
 
 // peer mode: this rank's end vector into slot `rank` of EVERY rank's exchange buffer (its own included), then the flag
-__global__ void shard_push_kernel(double* const* peers, const double* f_own, uint32_t n_comp, int world, int rank,
-                                  size_t par_off, size_t flag_off, unsigned long long seq)
+// (one CTA)
+__device__ __forceinline__ void shard_push(double* const* peers, const double* f_own, uint32_t n_comp, int world, int rank,
+                                           size_t par_off, size_t flag_off, unsigned long long seq)
 {
     for (int j = 0; j < world; j++) {
         double* dst = peers[j] + par_off + (size_t)rank * n_comp;
@@ -178,15 +189,23 @@ __global__ void shard_push_kernel(double* const* peers, const double* f_own, uin
         st_release_sys(reinterpret_cast<unsigned long long*>(peers[j] + flag_off) + rank, seq);
 }
 
+// The whole hand-off in one launch: push (peer mode), wait for the peers' vectors, compose s_in and the carry, empty
+// the descriptors and the ticket of the fix-up launch, commit the carry (single-CTA launches).
 __global__ void shard_compose_kernel(const ComposeParams p)
 {
+    if (p.peers != nullptr && blockIdx.x == 0)
+        shard_push(p.peers, p.f_own, p.n_comp, p.world, p.rank, p.par_off, p.flag_off, p.seq);
+    if (p.clear_desc != nullptr) {
+        for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < p.clear_n; t += gridDim.x * blockDim.x) p.clear_desc[t] = kDescEmpty;
+        if (blockIdx.x == 0 && threadIdx.x == 0) *p.clear_ticket = 0;
+    }
     if (p.flags != nullptr) {
         // wait until every rank's end vector of this call has landed (bounded: a peer that died must not hang the GPU)
         for (int j = threadIdx.x; j < p.world; j += blockDim.x) {
             unsigned long long spins = 0;
             while (ld_acquire_sys(p.flags + j) != p.seq) {
                 __nanosleep(64);
-                if (++spins > (1ull << 22)) { *p.err = 1; break; }     // a few seconds
+                if (++spins > (1ull << 22)) { *p.err = 1; *p.err_host = 1; break; }     // a few seconds
             }
         }
         __syncthreads();
@@ -246,6 +265,14 @@ static int shard_alloc(caribou_cuda_ctx* c, int rank, int world)
         !cuda_ok(cudaMalloc(&s->d_mpow, (size_t)(world + 1) * S * S * 8), "cudaMalloc"))
         return CARIBOU_CUDA_ERR;
     CBL_CHECK(cudaMemsetAsync(s->d_f, 0, (size_t)world * s->per_rank * 8, c->stream));
+    {
+        // a composition kernel that gives up on a peer says so in the device control block (sticky, mirrored by every
+        // later call) and straight in the page-locked host copy wait() reads (no copy on the hand-off path for it)
+        void* dp = nullptr;
+        CBL_CHECK(cudaHostGetDevicePointer(&dp, c->h_ctrl, 0));
+        s->err_host = reinterpret_cast<int*>(static_cast<uint8_t*>(dp) +
+                                             (reinterpret_cast<uint8_t*>(c->h_sflags + 3 * (size_t)c->cfg.n_streams + 1) - reinterpret_cast<uint8_t*>(c->h_ctrl)));
+    }
     for (cudaEvent_t& e : s->ev) CBL_CHECK(cudaEventCreate(&e));
     CBL_CHECK(cudaStreamSynchronize(c->stream));
     return CARIBOU_CUDA_OK;
@@ -261,8 +288,6 @@ static int shard_peer_setup(caribou_cuda_ctx* c)
     const size_t doubles = 2 * (size_t)s->world * s->per_rank + 2 * (size_t)s->world;
     CBL_CHECK(cudaMalloc(&s->d_px, doubles * 8));
     CBL_CHECK(cudaMemsetAsync(s->d_px, 0, doubles * 8, c->stream));
-    CBL_CHECK(cudaMalloc(&s->d_perr, 4));
-    CBL_CHECK(cudaMemsetAsync(s->d_perr, 0, 4, c->stream));
     CBL_CHECK(cudaMalloc(&s->d_peers, (size_t)s->world * sizeof(double*)));
     // handles: [world] x (64-byte handle + 1 int "ok so far")
     struct Slot { cudaIpcMemHandle_t h; int ok; int pad[15]; };
@@ -367,34 +392,46 @@ static int shard_begin(caribou_cuda_ctx* c, int in_kind, const void* in, size_t 
     return CARIBOU_CUDA_OK;
 }
 
+// what the fix-up of this call launches: the leading tiles only (partial), or the whole shard again
+struct FixPlan { bool partial; uint32_t max_tiles; };
+static FixPlan shard_fix_plan(caribou_cuda_ctx* c)
+{
+    Shard* s = c->shard;
+    const size_t fix = caribou_cuda_fixup_samples(c, s->n);
+    const int LTn = pick_plan(c, s->n).LT;               // the plan run_iir will take for this shard
+    const uint32_t tile_samples = 32u * (uint32_t)LTn;
+    const uint32_t max_tiles = (uint32_t)((fix + tile_samples - 1) / tile_samples);
+    const uint64_t tiles_ps = (s->n / LTn + 31) / 32;
+    FixPlan f;
+    f.partial = !(max_tiles == 0 || max_tiles >= tiles_ps);
+    f.max_tiles = max_tiles;
+    return f;
+}
+
 // fix-up from d_sin and the new carry into the context's state
 static int shard_fixup(caribou_cuda_ctx* c)
 {
     Shard* s = c->shard;
     const FilterPlan& P = c->plan;
     const int32_t* gate = s->in_kind == IN_WORDS ? &c->d_counters->any_misaligned : nullptr;
-    const size_t fix = caribou_cuda_fixup_samples(c, s->n);
-    const int LTn = pick_plan(c, s->n).LT;               // the plan run_iir will take for this shard
-    const uint32_t tile_samples = 32u * (uint32_t)LTn;
-    const uint32_t max_tiles = (uint32_t)((fix + tile_samples - 1) / tile_samples);
-    const uint64_t tiles_ps = (s->n / LTn + 31) / 32;
-    if (max_tiles == 0 || max_tiles >= tiles_ps) {
+    const FixPlan fp = shard_fix_plan(c);
+    if (!fp.partial) {
         // no useful contraction, or a short shard: the whole shard again (tail included) from a scratch copy of s_in
         CBL_CHECK(cudaMemcpyAsync(s->d_work, s->d_sin, s->per_rank * 8, cudaMemcpyDeviceToDevice, c->stream));
         if (run_iir(c, s->in_kind, s->in, s->n, s->in_stride, s->out, s->out_stride, gate, 0, true, 0, s->d_work) != CARIBOU_CUDA_OK)
             return CARIBOU_CUDA_ERR;
     } else {
-        if (run_iir(c, s->in_kind, s->in, s->n, s->in_stride, s->out, s->out_stride, gate, 0, false, max_tiles, s->d_sin) != CARIBOU_CUDA_OK)
+        c->desc_precleared = s->precleared;     // consumed by this run_iir
+        if (run_iir(c, s->in_kind, s->in, s->n, s->in_stride, s->out, s->out_stride, gate, 0, false, fp.max_tiles, s->d_sin) != CARIBOU_CUDA_OK)
             return CARIBOU_CUDA_ERR;
     }
+    s->precleared = false;
     // the stream's state after this call: every rank holds the same carry
     if (!s->committed) {
         launch_commit_state(c->d_state, s->d_carry, (size_t)c->cfg.n_streams, (size_t)2 * P.S, gate, 0, c->stream);
         c->launches++;
     }
     c->pos += s->n * (uint64_t)s->world;
-    if (s->d_perr)   // a composition kernel that gave up on a peer's flag: wait() reports the call as failed
-        CBL_CHECK(cudaMemcpyAsync(c->h_sflags + 3 * (size_t)c->cfg.n_streams + 1, s->d_perr, 4, cudaMemcpyDeviceToHost, c->stream));
     if (c->profiling) { CBL_CHECK(cudaEventRecord(s->ev[2], c->stream)); s->ev_valid = true; }
     s->open = false;
     CBL_CHECK(cudaGetLastError());
@@ -404,16 +441,39 @@ static int shard_fixup(caribou_cuda_ctx* c)
 static int shard_compose(caribou_cuda_ctx* c, bool peer = false)
 {
     Shard* s = c->shard;
+    const size_t ns = (size_t)c->cfg.n_streams;
     ComposeParams p;
+    memset(&p, 0, sizeof(p));
     p.S = c->plan.S; p.world = s->world; p.rank = s->rank;
     p.n_comp = (uint32_t)s->per_rank;
     p.f = s->d_f; p.carry = c->d_state; p.mpow = s->d_mpow; p.s_in = s->d_sin; p.carry_out = s->d_carry;
-    p.flags = nullptr; p.seq = 0; p.err = s->d_perr;
+    p.flags = nullptr; p.seq = 0;
+    p.err = c->d_sflags + 3 * ns + 1;
+    p.err_host = s->err_host;
     if (peer) {
         const size_t par = (size_t)(s->seq & 1);
         p.f = s->d_px + par * s->world * s->per_rank;
         p.flags = reinterpret_cast<const unsigned long long*>(s->d_px + 2 * (size_t)s->world * s->per_rank) + par * s->world;
         p.seq = s->seq;
+        p.peers = s->d_peers;
+        p.f_own = s->d_f + (size_t)s->rank * s->per_rank;
+        p.par_off = par * s->world * s->per_rank;
+        p.flag_off = 2 * (size_t)s->world * s->per_rank + par * s->world;
+    }
+    // a fix-up of a few leading tiles: its descriptors and ticket are emptied here (pass 1 used more tiles of the same
+    // plan, so the buffers exist and are large enough)
+    s->precleared = false;
+    const FixPlan fp = shard_fix_plan(c);
+    if (fp.partial) {
+        const FilterPlan& P = pick_plan(c, s->n);
+        DevBuf& desc = P.chained ? c->desc_incl : c->desc_agg;
+        const uint64_t doubles = (uint64_t)fp.max_tiles * c->win_cnt * 2 * P.S;
+        if (desc.p && doubles * 8 <= desc.cap && doubles <= (1u << 16)) {
+            p.clear_desc = desc.as<unsigned long long>();
+            p.clear_n = (uint32_t)doubles;
+            p.clear_ticket = c->d_ticket;
+            s->precleared = true;
+        }
     }
     const unsigned threads = 128, grid = (unsigned)std::min<size_t>((s->per_rank + threads - 1) / threads, 64);
     p.commit = grid == 1 ? c->d_state : nullptr;
@@ -515,12 +575,7 @@ int caribou_cuda_shard_submit(caribou_cuda_ctx* c, int in_kind, const void* in, 
     double* f_own = s->d_f + (size_t)s->rank * s->per_rank;
     if (s->mode == 2) {
         s->seq++;
-        const size_t par = (size_t)(s->seq & 1);
-        shard_push_kernel<<<1, 128, 0, c->stream>>>(s->d_peers, f_own, (uint32_t)s->per_rank, s->world, s->rank,
-                                                    par * s->world * s->per_rank,
-                                                    2 * (size_t)s->world * s->per_rank + par * s->world, s->seq);
-        c->launches++;
-        if (shard_compose(c, true) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        if (shard_compose(c, true) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;     // push + wait + compose in one launch
         return shard_fixup(c);
     }
     if (s->mode == 0) {
