@@ -13,7 +13,7 @@ LIB = os.path.join(HERE, "libcaribou_cuda%s.so" % ("_" + VARIANT if VARIANT else
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 CU = ["unpack.cu", "iir.cu", "iir_k1.cu", "iir_k2.cu", "iir_k3.cu", "iir_k4.cu", "iir_k1y.cu", "iir_k2y.cu", "iir_k3y.cu",
-      "iir_k4y.cu", "iir_r1.cu", "iir_r2.cu", "iir_r3.cu", "iir_r4.cu", "tx.cu", "api.cu", "shard.cu", "compat.cu", "noalloc.cu"]
+      "iir_k4y.cu", "iir_r1.cu", "iir_r2.cu", "iir_r3.cu", "iir_r4.cu", "iir_ra1.cu", "iir_ra2.cu", "iir_ra3.cu", "iir_ra4.cu", "tx.cu", "api.cu", "shard.cu", "compat.cu", "noalloc.cu"]
 CPP = ["tables.cpp", "ring.cpp"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall"]
 

@@ -246,6 +246,21 @@ int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t
         if (y32)
             for (int m = 0; m < kMaxNK; m++)
                 for (int i = 0; i < kMaxS; i++) Tl.R[m][i] *= T.gain;
+        // AP form of the rerun kernel's phase 3 (iir_rerun.cuh): the (1 + q)^2K numerator on the integer samples, then
+        // the all-pole cascade (constants: tables.cpp plan_ap_launch)
+        static const bool no_ap = getenv("CARIBOU_CUDA_NO_AP") != nullptr;
+        if (P.rerun && P.ap && in_kind != IN_CF32 && !no_ap) {
+            ApLaunch L;
+            plan_ap_launch(P, in_kind == IN_WORDS, T.gain, &L);
+            p.ap = 1;
+            p.ap_exp = L.exp; p.ap_mul = L.mul; p.ap_xor = L.xorw;
+            for (int i = 0; i < P.S; i++) {
+                for (int k = 0; k < P.S; k++) Tl.R[i][k] = L.T[i][k];
+                Tl.R[kApBiasRow][i] = L.bias[i];
+            }
+            Tl.gain = L.gain;
+            Tl.out_bias = L.out_bias;
+        }
         prof_mark(c, 0);
         const int kin = (in_kind == IN_WORDS && layout) ? IN_WORDS_HIF : in_kind;
         const int e = launch_iir(P.K, P.D, kin, P.par, y32, tm, p, Tl, c->num_sms, c->stream);

@@ -7,13 +7,22 @@ iir_launch_fn iir_launch_k1(int, int, bool, bool); iir_launch_fn iir_launch_k2(i
 iir_launch_fn iir_launch_k3(int, int, bool, bool); iir_launch_fn iir_launch_k4(int, int, bool, bool);
 iir_launch_fn iir_rerun_k1(int, int); iir_launch_fn iir_rerun_k2(int, int);      // iir_r{1,2,3,4}.cu
 iir_launch_fn iir_rerun_k3(int, int); iir_launch_fn iir_rerun_k4(int, int);
+iir_launch_fn iir_rerun_ap_k1(int, int); iir_launch_fn iir_rerun_ap_k2(int, int);      // iir_ra{1,2,3,4}.cu
+iir_launch_fn iir_rerun_ap_k3(int, int); iir_launch_fn iir_rerun_ap_k4(int, int);
 
 
 int launch_iir(int K, int D, int in_kind, bool par, bool y32, const CUtensorMap& tmap, const IirParams& p,
                const IirTables& t, int num_sms, cudaStream_t st)
 {
     iir_launch_fn fn = nullptr;
-    if (iir_is_rerun(K, D, par)) {
+    if (iir_is_rerun(K, D, par) && p.ap) {
+        switch (K) {
+            case 1: fn = iir_rerun_ap_k1(D, in_kind); break;
+            case 2: fn = iir_rerun_ap_k2(D, in_kind); break;
+            case 3: fn = iir_rerun_ap_k3(D, in_kind); break;
+            case 4: fn = iir_rerun_ap_k4(D, in_kind); break;
+        }
+    } else if (iir_is_rerun(K, D, par)) {
         switch (K) {
             case 1: fn = iir_rerun_k1(D, in_kind); break;
             case 2: fn = iir_rerun_k2(D, in_kind); break;

@@ -57,13 +57,16 @@ struct IirTables {
     double out_bias;                      // added after the gain: -c * Hn(1) * gain (0 when the input carries no offset)
     double sbias[kMaxS];                  // s*: state every run starts from (0 when the input carries no offset)
     double Mp[5][kMaxS * kMaxS];          // M^(2^j), row-major S x S (S = 2K)
-    double R[kMaxNK][kMaxS];              // R[m] = Cu A^(m D)
+    double R[kMaxNK][kMaxS];              // R[m] = Cu A^(m D).  The rerun kernel has no use for it; its AP form keeps
+                                          // Tap there (rows 0..S-1) and the all-pole bias state (row kApBiasRow)
     // fixed-point staging of the float-output kernels fed with integers: phase 1 stores the low word of
     // gain * y_zs + stage_mo (stage_mo = 1.5 * 2^(52-F) + 2^(31-F), folded into out_bias), phase 3 rebuilds the
     // double from that word and stage_hi and subtracts stage_mo again - no FP64<->FP32 conversion on the way
     double stage_mo;
     uint32_t stage_hi, stage_pad;
 };
+
+constexpr int kApBiasRow = kMaxS;         // IirTables::R row of the AP form's bias state
 
 struct IirParams {
     uint32_t n_streams;
@@ -93,6 +96,10 @@ struct IirParams {
     uint32_t  inj_xor, inj_mul;
     int       scan_rounds;      // Kogge-Stone rounds of the warp scan that can still contribute (<= 5)
     int       out_vec;          // CF32 output may be stored 32 bytes at a time (base and stream stride 32-byte aligned)
+    // rerun kernel, AP form of phase 3 (iir_rerun.cuh): exponent bits added in the last two-tap sum, the power of two
+    // that spreads the sum over the double's register pair, the offset-binary flip of both halves of an input word
+    int       ap;
+    uint32_t  ap_exp, ap_mul, ap_xor;
     uint32_t  rr_boxes;         // rerun kernel: 4 KiB boxes per tile = run length / samples per 128-byte row piece (runtime:
                                 // small submits take a plan with short runs so that they still spread over the GPU)
 };

@@ -1,0 +1,5 @@
+// Kernel (b), rerun form with the AP phase 3 (iir_rerun.cuh), instantiations for cascades of 3 biquad(s).
+#include "iir_rerun.cuh"
+namespace cbl {
+iir_launch_fn iir_rerun_ap_k3(int D, int in_kind) { return rerun_ap_pick_launch<3>(D, in_kind); }
+}

@@ -36,18 +36,22 @@ namespace cbl {
 #define CBL_RR_RING 4            // 4 KiB boxes in a warp's ring
 #endif
 
-template <int K, int D, int IN>
+#ifndef CBL_RR_AP_WARPS
+#define CBL_RR_AP_WARPS 16       // warps per SM of the AP form up to three sections (its serial section chain wants more
+#endif                           // warps to hide behind; 128 registers each), with a ring of three boxes so that they fit
+template <int K, int D, int IN, bool AP = false>
 struct RerunCfg {
     static constexpr int S     = 2 * K;
     static constexpr int SPS   = (IN == IN_CF32) ? 16 : 32;   // samples per 128-byte row step = per box
-    static constexpr int R     = CBL_RR_RING;                 // ring slots (a tile of fewer boxes uses as many as it has)
+    static constexpr bool WIDE = AP && K <= 3 && CBL_RR_AP_WARPS > 12;
+    static constexpr int R     = WIDE ? 3 : CBL_RR_RING;      // ring slots (a tile of fewer boxes uses as many as it has)
     // the run length is a launch parameter (IirParams::rr_boxes boxes of SPS samples): the plan fixes it
     static constexpr int RING_BYTES    = R * 4096;
     static constexpr int SCRATCH_BYTES = 2 * S * 8 * 2;
     static constexpr int WARP_BYTES = RING_BYTES + SCRATCH_BYTES;
     static constexpr int SMEM_WARPS = (232448 - 1024) / (WARP_BYTES + R * 8);
     // registers (cuobjdump -res-usage): 12 warps allow 168 per thread
-    static constexpr int REG_WARPS  = (K <= 2) ? CBL_RR_WARPS : (K == 3 ? CBL_RR_WARPS3 : CBL_RR_WARPS4);
+    static constexpr int REG_WARPS  = WIDE ? CBL_RR_AP_WARPS : ((K <= 2) ? CBL_RR_WARPS : (K == 3 ? CBL_RR_WARPS3 : CBL_RR_WARPS4));
     static constexpr int WPC = SMEM_WARPS < REG_WARPS ? SMEM_WARPS : REG_WARPS;
     static_assert(WPC >= 1, "a warp's buffers do not fit shared memory");
     static_assert(D == 1 || D == 2, "phase 3 works in groups of 8 or 16 samples: whole chunks of 4 kept outputs");
@@ -129,12 +133,14 @@ __device__ __forceinline__ void store_out4(const IirParams& P, uint64_t o, const
     }
 }
 
-template <int K, int D, int IN>
-__global__ void __launch_bounds__((RerunCfg<K, D, IN>::WPC) * 32, 1)
+// AP: phase 3 in the "integer FIR + all-pole cascade" form (see the phase-3 block); integer inputs of filters whose
+// zeros all sit at z = -1 (every Butterworth low-pass).
+template <int K, int D, int IN, bool AP = false>
+__global__ void __launch_bounds__((RerunCfg<K, D, IN, AP>::WPC) * 32, 1)
 iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ IirParams P,
                  const __grid_constant__ IirTables T)
 {
-    using C = RerunCfg<K, D, IN>;
+    using C = RerunCfg<K, D, IN, AP>;
     constexpr int S = C::S;
     constexpr bool PAR = true;
     constexpr bool INJECT = IN != IN_CF32;
@@ -394,11 +400,45 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             const uint32_t run = tis * 32u + lane;
             const bool mine = run < P.n_runs;
             double va[K][2], vb[K][2];
+            // AP form.  H(q) = G (1 + q)^2K / prod_k (1 + a1_k q + a2_k q^2): the numerator is applied to the INTEGER
+            // samples - a cascade of 2K two-tap sums, exact; for SMI words the first three stages act on both 13-bit
+            // fields at once in the 16-bit halves of one register - the result is dropped into a double's mantissa
+            // (the last sum also adds the exponent bits, one IMAD.WIDE spreads it over the register pair), and the
+            // all-pole cascade that is left costs 2 FMAs per section, rail and sample with the output for free:
+            // 4K + 2 FMAs per complex sample instead of the parallel form's 8K + 2.  The run starts from "all earlier
+            // samples were zero" (histories preset to the offset-binary zero) and the all-pole state
+            // sigma0 = bias + Tap s0, Tap = the map between the two realisations' zero-input responses (tables.cpp).
+            constexpr bool APW = IN != IN_CS16;                         // SMI words: 13-bit fields, packed stages
+            constexpr int  SG = 2 * K;                                  // two-tap stages
+            constexpr int  NPK = AP ? (APW ? (SG < 3 ? SG : 3) : 0) : 0;  // stages on the packed halves
+            constexpr int  NUP = AP ? SG - NPK : 0;                     // stages per rail after unpacking
+            constexpr uint32_t BETA = APW ? 4096u : 32768u;             // offset-binary zero
+            uint32_t hp[NPK > 0 ? NPK : 1], ga[NUP > 0 ? NUP : 1], gb[NUP > 0 ? NUP : 1];
+            const uint32_t ap_exp = P.ap_exp, ap_mul = P.ap_mul, ap_xor = P.ap_xor;
+            if constexpr (AP) {
 #pragma unroll
-            for (int k = 0; k < K; k++) {
-                va[k][0] = T.sbias[2 * k] + s0[0][2 * k];     va[k][1] = T.sbias[2 * k + 1] + s0[0][2 * k + 1];
-                vb[k][0] = T.sbias[2 * k] + s0[1][2 * k];     vb[k][1] = T.sbias[2 * k + 1] + s0[1][2 * k + 1];
+                for (int i = 0; i < NPK; i++) hp[i] = (BETA << i) * 0x00010001u;
+#pragma unroll
+                for (int i = 0; i < NUP; i++) ga[i] = gb[i] = BETA << (NPK + i);
+#pragma unroll
+                for (int row = 0; row < S; row++) {
+                    double ea = T.R[kApBiasRow][row], eb = ea;
+#pragma unroll
+                    for (int col = 0; col < S; col++) {
+                        ea = fma(T.R[row][col], s0[0][col], ea);
+                        eb = fma(T.R[row][col], s0[1][col], eb);
+                    }
+                    va[row / 2][row % 2] = ea;
+                    vb[row / 2][row % 2] = eb;
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < K; k++) {
+                    va[k][0] = T.sbias[2 * k] + s0[0][2 * k];     va[k][1] = T.sbias[2 * k + 1] + s0[0][2 * k + 1];
+                    vb[k][0] = T.sbias[2 * k] + s0[1][2 * k];     vb[k][1] = T.sbias[2 * k + 1] + s0[1][2 * k + 1];
+                }
             }
+            (void)hp; (void)ga; (void)gb; (void)ap_exp; (void)ap_mul; (void)ap_xor;
             uint64_t o = (uint64_t)stream * P.out_stride + (uint64_t)run * (uint32_t)(N * C::SPS / D);
             constexpr int PER = (IN == IN_CF32) ? 2 : 4;      // samples per 16-byte piece
             constexpr int PP  = 4 * D / PER;                  // pieces that hold four kept outputs = one store
@@ -432,15 +472,51 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 #pragma unroll
                             for (int e = 0; e < PER; e++) {
                                 const int j = ci * PER + e;          // sample within the chunk (chunks start on multiples of D)
-                                double xa, xb;
-                                if (INJECT) inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
-                                else sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
-                                if (j % D == 0) {
-                                    yi[j / D] = fma(filter_step<K, PAR, true>(T, va, xa), T.gain, T.out_bias);
-                                    yq[j / D] = fma(filter_step<K, PAR, true>(T, vb, xb), T.gain, T.out_bias);
+                                [[maybe_unused]] double xa, xb;
+                                if constexpr (AP) {
+                                    uint32_t ta, tb;
+                                    if constexpr (APW) {
+                                        uint32_t pk = and_xor<0x1FFF1FFFu>(wv[e] >> 1, ap_xor);   // both fields, offset binary
+#pragma unroll
+                                        for (int i = 0; i < NPK; i++) { const uint32_t t = pk + hp[i]; hp[i] = pk; pk = t; }
+                                        const uint32_t lo = pk & 0xFFFFu, hi = pk >> 16;
+                                        ta = IN == IN_WORDS ? hi : lo;       // rail A = I: bits 29:17 (S1G) / 13:1 (HiF)
+                                        tb = IN == IN_WORDS ? lo : hi;
+                                    } else {
+                                        const uint32_t u = wv[e] ^ ap_xor;   // 0x80008000: both int16 halves, offset binary
+                                        ta = u & 0xFFFFu;
+                                        tb = u >> 16;
+                                    }
+#pragma unroll
+                                    for (int i = 0; i < NUP; i++) {
+                                        const uint32_t xe = i == NUP - 1 ? ap_exp : 0u;
+                                        const uint32_t t = ta + ga[i] + xe, u = tb + gb[i] + xe;
+                                        ga[i] = ta; gb[i] = tb;
+                                        ta = t; tb = u;
+                                    }
+                                    if (NUP == 0) { ta += ap_exp; tb += ap_exp; }
+                                    double ia = mul_wide_f64(ta, ap_mul), ib = mul_wide_f64(tb, ap_mul);
+#pragma unroll
+                                    for (int k = 0; k < K; k++) {
+                                        const double wa = fma(-T.a1[k], va[k][0], fma(-T.a2[k], va[k][1], ia));
+                                        const double wb = fma(-T.a1[k], vb[k][0], fma(-T.a2[k], vb[k][1], ib));
+                                        va[k][1] = va[k][0]; va[k][0] = wa; ia = wa;
+                                        vb[k][1] = vb[k][0]; vb[k][0] = wb; ib = wb;
+                                    }
+                                    if (j % D == 0) {
+                                        yi[j / D] = fma(ia, T.gain, T.out_bias);
+                                        yq[j / D] = fma(ib, T.gain, T.out_bias);
+                                    }
                                 } else {
-                                    filter_step<K, PAR, false>(T, va, xa);
-                                    filter_step<K, PAR, false>(T, vb, xb);
+                                    if (INJECT) inject_f64<IN>(wv[e], inj_xor, inj_mul, xa, xb);
+                                    else sample_to_f64<IN, false>(wv[2 * e], wv[2 * e + 1], xa, xb);
+                                    if (j % D == 0) {
+                                        yi[j / D] = fma(filter_step<K, PAR, true>(T, va, xa), T.gain, T.out_bias);
+                                        yq[j / D] = fma(filter_step<K, PAR, true>(T, vb, xb), T.gain, T.out_bias);
+                                    } else {
+                                        filter_step<K, PAR, false>(T, va, xa);
+                                        filter_step<K, PAR, false>(T, vb, xb);
+                                    }
                                 }
                             }
                         }
@@ -475,11 +551,11 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     }
 }
 
-template <int K, int D, int IN>
+template <int K, int D, int IN, bool AP = false>
 int launch_rerun_t(const CUtensorMap& tmap, const IirParams& p, const IirTables& t, int num_sms, cudaStream_t st)
 {
-    using C = RerunCfg<K, D, IN>;
-    auto kern = iir_rerun_kernel<K, D, IN>;
+    using C = RerunCfg<K, D, IN, AP>;
+    auto kern = iir_rerun_kernel<K, D, IN, AP>;
     static bool ready_dev[kMaxDevices] = {false};      // per device: the shared-memory opt-in is a per-device attribute
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
@@ -512,6 +588,23 @@ template <int KK>
 iir_launch_fn rerun_pick_launch(int D, int in_kind)
 {
     return D == 1 ? rerun_pick_kind<KK, 1>(in_kind) : (D == 2 ? rerun_pick_kind<KK, 2>(in_kind) : nullptr);
+}
+
+// the AP form of phase 3 (integer inputs only)
+template <int KK, int D>
+iir_launch_fn rerun_ap_pick_kind(int in_kind)
+{
+    if constexpr (iir_is_rerun(KK, D, true)) {
+        if (in_kind == IN_WORDS) return &launch_rerun_t<KK, D, IN_WORDS, true>;
+        if (in_kind == IN_WORDS_HIF) return &launch_rerun_t<KK, D, IN_WORDS_HIF, true>;
+        if (in_kind == IN_CS16) return &launch_rerun_t<KK, D, IN_CS16, true>;
+    }
+    return nullptr;
+}
+template <int KK>
+iir_launch_fn rerun_ap_pick_launch(int D, int in_kind)
+{
+    return D == 1 ? rerun_ap_pick_kind<KK, 1>(in_kind) : (D == 2 ? rerun_ap_pick_kind<KK, 2>(in_kind) : nullptr);
 }
 
 }  // namespace cbl

@@ -310,6 +310,69 @@ bool state_map(const Realisation& Rc, const std::vector<ld>& sc, const Realisati
         for (int j = 0; j < S; j++) T->a[i][j] = a[(size_t)prow[i * S + j] * w + nu] * sp[i] / sc[j];
     return true;
 }
+
+// ------------------------------------------------------------------ AP form (iir_rerun.cuh, phase 3)
+// one sample of the all-pole cascade: state (v1,v2) per section, returns the last section's w
+template <class F>
+F ap_step(int K, const F* a1, const F* a2, F* s, F in)
+{
+    for (int k = 0; k < K; k++) {
+        const F w = in - a1[k] * s[2 * k] - a2[k] * s[2 * k + 1];
+        s[2 * k + 1] = s[2 * k];
+        s[2 * k] = w;
+        in = w;
+    }
+    return in;
+}
+// Tap with: all-pole cascade started from Tap s (and "all earlier samples zero" in the numerator) continues the
+// parallel realisation started from s.  Both zero-input responses are sums of the same pole modes, so matching their
+// first S samples matches them for good: O_ap Tap = O_par.  The observability matrices of the reference's narrow
+// filters are conditioned like 1e12..1e16 - solved in binary128, the result is good to double precision.
+bool ap_state_map(const Form& Fp, int K, double (*Tap)[kMaxS])
+{
+    typedef __float128 qf;
+    const int S = 2 * K;
+    qf a1[kMaxK], a2[kMaxK], c1[kMaxK], c2[kMaxK];
+    for (int k = 0; k < K; k++) { a1[k] = (qf)Fp.a1[k]; a2[k] = (qf)Fp.a2[k]; c1[k] = (qf)Fp.c1[k]; c2[k] = (qf)Fp.c2[k]; }
+    qf M[kMaxS][2 * kMaxS];
+    for (int j = 0; j < S; j++) {
+        qf sp[kMaxS], sa[kMaxS];
+        for (int i = 0; i < S; i++) sp[i] = sa[i] = (i == j) ? (qf)1 : (qf)0;
+        for (int n = 0; n < S; n++) {
+            // parallel form, zero input: out = sum alpha v1 + beta v2, then the state moves on
+            qf o = 0, ns[kMaxS];
+            for (int k = 0; k < K; k++) {
+                o += c1[k] * sp[2 * k] + c2[k] * sp[2 * k + 1];
+                ns[2 * k] = -a1[k] * sp[2 * k] - a2[k] * sp[2 * k + 1];
+                ns[2 * k + 1] = sp[2 * k];
+            }
+            for (int i = 0; i < S; i++) sp[i] = ns[i];
+            M[n][S + j] = o;
+            M[n][j] = ap_step<qf>(K, a1, a2, sa, (qf)0);
+        }
+    }
+    auto qabs = [](qf v) { return v < 0 ? -v : v; };
+    for (int c = 0; c < S; c++) {
+        int piv = c;
+        for (int r = c + 1; r < S; r++) if (qabs(M[r][c]) > qabs(M[piv][c])) piv = r;
+        if (!(qabs(M[piv][c]) > 0)) return false;
+        if (piv != c) for (int j = 0; j < 2 * S; j++) std::swap(M[piv][j], M[c][j]);
+        const qf inv = (qf)1 / M[c][c];
+        for (int j = 0; j < 2 * S; j++) M[c][j] *= inv;
+        for (int r = 0; r < S; r++) {
+            if (r == c) continue;
+            const qf f = M[r][c];
+            if (f == 0) continue;
+            for (int j = 0; j < 2 * S; j++) M[r][j] -= f * M[c][j];
+        }
+    }
+    for (int i = 0; i < S; i++)
+        for (int j = 0; j < S; j++) {
+            Tap[i][j] = (double)M[i][S + j];
+            if (!std::isfinite(Tap[i][j])) return false;
+        }
+    return true;
+}
 }  // namespace
 
 bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, bool want_y32, FilterPlan* P, const char** msg,
@@ -438,6 +501,60 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, 
                 P->Trk[i][j] = (ld)P->g[i / 2] * a[(size_t)i * w + S + j];
             }
     }
+    // ---- AP form of the rerun kernel's phase 3: zeros all at z = -1, poles away from z = 1
+    P->ap = false; P->ap_stages = 0; P->ap_err = 0;
+    if (P->rerun && P->par) {
+        bool ok = true;
+        int stages = 0;
+        for (int k = 0; k < K && ok; k++) {
+            if (Fc.c1[k] == 2 && Fc.c2[k] == 1 && Fc.a2[k] != 0) stages += 2;
+            else ok = false;
+        }
+        ok = ok && stages == 2 * K && ap_state_map(F, K, P->Tap);
+        ld prod = 1;
+        for (int k = 0; k < K && ok; k++) {
+            const ld d = 1 + F.a1[k] + F.a2[k];
+            if (!(fabsl(d) > 0)) { ok = false; break; }
+            prod /= d;
+            P->sstar_ap[2 * k] = P->sstar_ap[2 * k + 1] = prod;
+        }
+        if (ok) {
+            // the parallel form runs a deterministic full-scale signal, its state is mapped, and both forms go on:
+            // the all-pole cascade on the binomially summed samples (earlier samples zero), all in long double
+            ld sp[kMaxS] = {0}, np_[kMaxS], op, e2 = 0, p2 = 0, a1l[kMaxK], a2l[kMaxK];
+            for (int k = 0; k < K; k++) { a1l[k] = F.a1[k]; a2l[k] = F.a2[k]; }
+            uint64_t lcg = 0xD1B54A32D192ED03ull;
+            auto sig = [&](int n) {
+                lcg = lcg * 6364136223846793005ull + 1442695040888963407ull;
+                return (ld)((int)((lcg >> 40) & 8191) - 4096) + 3000 * cosl(0.0078539816339744830962L * n);
+            };
+            const int N1 = 6000, N2 = 3000;
+            for (int n = 0; n < N1; n++) {
+                form_step(F, sp, sig(n), np_, &op);
+                for (int i = 0; i < S; i++) sp[i] = np_[i];
+            }
+            ld sa[kMaxS];
+            for (int i = 0; i < S; i++) {
+                ld acc = 0;
+                for (int j = 0; j < S; j++) acc += (ld)P->Tap[i][j] * sp[j];
+                sa[i] = acc;
+            }
+            ld hist[2 * kMaxK + 1] = {0};
+            for (int n = 0; n < N2; n++) {
+                const ld x = sig(N1 + n);
+                form_step(F, sp, x, np_, &op);
+                for (int i = 0; i < S; i++) sp[i] = np_[i];
+                ld t = x;                               // (1 + q)^stages with zero history: stage i keeps its last input
+                for (int i = 0; i < stages; i++) { const ld u = t + hist[i]; hist[i] = t; t = u; }
+                const ld oa = ap_step<ld>(K, a1l, a2l, sa, t);
+                e2 += (op - oa) * (op - oa); p2 += op * op;
+            }
+            P->ap_err = (double)sqrtl(e2 / (p2 > 0 ? p2 : 1));
+            ok = P->ap_err < 1e-11;
+        }
+        P->ap = ok;
+        P->ap_stages = ok ? stages : 0;
+    }
     const Mat& A = R.A;
     const ld* Cu = R.Cu;
     for (int i = 0; i < S; i++) for (int j = 0; j < S; j++) P->A[i][j] = A.a[i][j];
@@ -529,6 +646,29 @@ bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, 
         P->decay_samples = last_bad + 64;
     }
     return true;
+}
+
+void plan_ap_launch(const FilterPlan& P, bool words, double gain, ApLaunch* L)
+{
+    const int SG = P.ap_stages;
+    const double beta = words ? 4096.0 : 32768.0;
+    const double tmax = ldexp(2 * beta - 1, SG);                        // largest sum
+    int bits = 0;
+    frexp(tmax, &bits);                                                 // tmax < 2^bits
+    const int j = bits - 20 > 1 ? bits - 20 : 1;
+    const int emax = (1 << (12 - j)) - 1;                               // biased exponent that still fits the 32-bit word
+    const int E = 1023 + 20 + j < emax ? 1023 + 20 + j : emax;
+    const double kappa = ldexp(1.0, E - 1023 - (20 + j));
+    const ld Cb = ldexpl(1.0L, 20 + j) + (ld)ldexp(beta, SG);
+    L->exp = (uint32_t)E << (20 + j);
+    L->mul = 1u << (32 - j);
+    L->xorw = words ? 0x10001000u : 0x80008000u;
+    for (int i = 0; i < P.S; i++) {
+        for (int k = 0; k < P.S; k++) L->T[i][k] = kappa * P.Tap[i][k];
+        L->bias[i] = (double)((ld)kappa * Cb * P.sstar_ap[i]);
+    }
+    L->gain = gain / kappa;
+    L->out_bias = (double)(-(ld)gain * Cb * P.sstar_ap[P.S - 2]);
 }
 
 void plan_power_kernel(const FilterPlan& P, uint64_t n, double* m)

@@ -33,6 +33,13 @@ struct FilterPlan {
     long double A[kMaxS][kMaxS];  // one-sample transition, kernel coordinates
     uint64_t decay_samples = 0;   // n with |A^n| (scaled) < 2^-60 for all larger n (0 if chained)
     std::vector<long double> scale;  // typical magnitude of each state component
+    // AP form of the rerun kernel's phase 3 (iir_rerun.cuh): every section's zeros are a double zero at z = -1 (or one
+    // zero there for a first-order section), so y / G = (1 + q)^ap_stages applied to the samples, then an all-pole cascade
+    bool ap = false;
+    int ap_stages = 0;            // two-tap integer stages = number of zeros at z = -1
+    double ap_err = 0;            // AP continuation against the parallel form from a mapped mid-stream state, rel. rms
+    double Tap[kMaxS][kMaxS];     // all-pole state (v1,v2 per section; earlier samples taken as zero) <- kernel state
+    long double sstar_ap[kMaxS];  // all-pole steady state under a unit constant input; [2K-2] is also its output
 };
 
 // false (with msg) if the cascade cannot be handled (b0 == 0, non-finite coefficients, ...)
@@ -40,6 +47,17 @@ struct FilterPlan {
 // rerun_lt > 0: run length of a rerun plan (the library keeps a second, short-run plan for small submits)
 bool make_filter_plan(int K, const double (*sos)[6], int D, bool force_cascade, bool want_y32, FilterPlan* plan, const char** msg,
                       int rerun_lt = 0);
+
+// Launch constants of the AP form for one input kind (SMI words: 13-bit fields, offset 4096; CS16: offset 32768) and
+// output gain.  The binomial sum t = sum_i C(stages, i) u[n-i] of the offset-binary samples u = x + beta is dropped into
+// a double by  X = bits((t + exp) * mul)  = kappa (2^(20+j) + t) = kappa (Cb + N(q) x),  kappa a power of two.
+struct ApLaunch {
+    uint32_t exp, mul, xorw;      // exponent bits added in the last sum, 2^(32-j), offset-binary flip of both halves of a word
+    double gain, out_bias;        // y = fma(w_K, gain, out_bias)
+    double T[kMaxS][kMaxS];       // kappa * Tap
+    double bias[kMaxS];           // all-pole state under the constant kappa * Cb
+};
+void plan_ap_launch(const FilterPlan& plan, bool words, double gain, ApLaunch* out);
 
 // A^n in REFERENCE state coordinates (row-major S x S doubles)
 void plan_shard_matrix(const FilterPlan& plan, uint64_t n, double* m);

@@ -96,6 +96,56 @@ int emul_run(int K, const double* sos, int D, int force_cascade, int want_y32, d
     return P.par ? 1 : 0;
 }
 
+// The AP form of the rerun kernel's phase 3 (iir_rerun.cuh), one rail of integer samples: every run starts from the
+// sequentially carried true state (kernel coordinates), mapped to the all-pole state; the numerator is the integer
+// two-tap cascade with "earlier samples zero", the sum enters the double through the same 32-bit word and multiply
+// the kernel uses.  info[0] = ap, [1] = stages, [2] = ap_err.  Returns 1 if the plan takes the AP form, 0 if not.
+int emul_run_ap(int K, const double* sos, int D, int words, double out_scale, const int32_t* x, size_t n,
+                const double* state_ref_in, double* out, double* state_ref_out, double* info)
+{
+    FilterPlan P; const char* msg = "";
+    if (!make_filter_plan(K, (const double(*)[6])sos, D, false, false, &P, &msg)) return -1;
+    info[0] = P.ap; info[1] = P.ap_stages; info[2] = P.ap_err;
+    if (!P.rerun || !P.ap) return 0;
+    const int S = P.S, LT = P.LT, NK = P.NK, SG = P.ap_stages;
+    if (n % LT) return -2;
+    ApLaunch L;
+    plan_ap_launch(P, words != 0, P.g[K] * out_scale, &L);
+    const uint32_t beta = words ? 4096u : 32768u;
+    double s0[kMaxS];
+    plan_state_to_kernel(P, state_ref_in, s0);
+    for (size_t r = 0; r < n / LT; r++) {
+        double sg[kMaxS];
+        for (int i = 0; i < S; i++) {
+            double acc = L.bias[i];
+            for (int c = 0; c < S; c++) acc = fma(L.T[i][c], s0[c], acc);
+            sg[i] = acc;
+        }
+        uint32_t hist[2 * kMaxK];
+        for (int i = 0; i < SG; i++) hist[i] = beta << i;
+        double v[kMaxS];
+        for (int i = 0; i < S; i++) v[i] = s0[i];
+        for (int t = 0; t < LT; t++) {
+            const int32_t xi = x[r * LT + t];
+            uint32_t u = (uint32_t)(xi + (int32_t)beta);
+            for (int i = 0; i < SG; i++) { const uint32_t s = u + hist[i]; hist[i] = u; u = s; }
+            const unsigned long long bits = (unsigned long long)(u + L.exp) * L.mul;
+            double in;
+            memcpy(&in, &bits, 8);
+            for (int k = 0; k < K; k++) {
+                const double w = fma(-P.tables.a1[k], sg[2 * k], fma(-P.tables.a2[k], sg[2 * k + 1], in));
+                sg[2 * k + 1] = sg[2 * k]; sg[2 * k] = w; in = w;
+            }
+            if (t % D == 0) out[r * NK + t / D] = fma(in, L.gain, L.out_bias);
+            double y;
+            step(P, v, (double)xi, &y);          // the true state carried on (the kernel gets it from the scan)
+        }
+        for (int i = 0; i < S; i++) s0[i] = v[i];
+    }
+    plan_state_to_ref(P, s0, state_ref_out);
+    return 1;
+}
+
 // max |Mp[j] - M^(2^j)| relative to the largest entry of that power, and sparsity check of the pattern the kernel assumes
 double emul_check_powers(int K, const double* sos, int D, int force_cascade, int want_y32)
 {

@@ -96,3 +96,50 @@ def test_run_matrix_powers_and_sparsity(emul, po):
                 for force_cascade in (0, 1):
                     w = emul.emul_check_powers(len(sos), sos.ctypes.data, D, force_cascade, y32)
                     assert 0 <= w < 1e-12, (order, D, y32, force_cascade, w)
+
+
+@pytest.mark.parametrize("order,fc", [(2, 100e3), (4, 250e3), (6, 10e3), (6, 25e3), (6, 50e3), (8, 10e3), (8, 400e3)])
+@pytest.mark.parametrize("D,words", [(1, 1), (1, 0), (2, 1)])
+def test_ap_form_of_the_rerun_kernel_matches_the_sequential_cascade(emul, po, order, fc, D, words):
+    """csrc/iir_rerun.cuh, AP phase 3: (1 + q)^2K on the integer samples (earlier samples zero at every run start),
+    the sum dropped into a double's mantissa, all-pole cascade from the mapped entry state - against the oracle's
+    sequential cascade, full-scale input, non-trivial incoming state."""
+    sos = po.butter_lowpass_sos(order, 4e6, fc)
+    K = len(sos)
+    emul.emul_run_ap.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_size_t, C.c_void_p,
+                                 C.c_void_p, C.c_void_p, C.c_void_p]
+    p = plan_info(emul, sos, D, 0)
+    if not p["rerun"]:
+        pytest.skip("staged kernel for this (order, D)")
+    n = p["run_len"] * 24
+    rng = np.random.default_rng(order * 10 + D)
+    full = 4096 if words else 32768
+    x = np.clip(np.round(0.7 * full * np.cos(2 * np.pi * 5e3 * np.arange(n) / 4e6)) + rng.integers(-full // 4, full // 4, n),
+                -full, full - 1).astype(np.int32)
+    x[:64] = -full                                                    # both extremes of the field
+    x[64:128] = full - 1
+    ref_c = po.Cascade(sos)
+    st_in = rng.standard_normal(2 * K) * 100
+    ref_c.state = st_in
+    ref = ref_c.run_f64(x.astype(np.float64))[::D]
+    out = np.zeros(n // D)
+    st_out = np.zeros(2 * K)
+    info = np.zeros(3)
+    r = emul.emul_run_ap(K, sos.ctypes.data, D, words, 1.0, x.ctypes.data, n, st_in.ctypes.data, out.ctypes.data,
+                         st_out.ctypes.data, info.ctypes.data)
+    assert r == 1 and info[0] == 1 and info[1] == 2 * K and info[2] < 1e-11, (r, info)
+    assert np.sqrt(np.mean((out - ref) ** 2)) / np.sqrt(np.mean(ref ** 2)) < 2e-9
+
+
+def test_ap_form_is_refused_for_other_numerators(emul, po):
+    """Zeros elsewhere than z = -1 (here: a scaled b1) keep the parallel-form phase 3."""
+    sos = po.butter_lowpass_sos(4, 4e6, 250e3).copy()
+    sos[1, 1] *= 0.999
+    emul.emul_run_ap.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_size_t, C.c_void_p,
+                                 C.c_void_p, C.c_void_p, C.c_void_p]
+    x = np.zeros(128 * 4, np.int32)
+    st = np.zeros(4)
+    out = np.zeros(x.size)
+    info = np.zeros(3)
+    assert emul.emul_run_ap(2, sos.ctypes.data, 1, 1, 1.0, x.ctypes.data, x.size, st.ctypes.data, out.ctypes.data,
+                            st.ctypes.data, info.ctypes.data) == 0 and info[0] == 0
