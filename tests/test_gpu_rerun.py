@@ -211,3 +211,39 @@ def test_decimate_by_two_from_three_sections_on(cb, po, torch_cuda, order, fc, k
         st = ctx.get_state()
     assert np.all(rel_rms(out.cpu().numpy(), ref) <= TOL)
     np.testing.assert_allclose(st, np.concatenate([ci.state, cq.state]), rtol=1e-9, atol=0)
+
+
+@pytest.mark.parametrize("order,fc,D", [(2, 100e3, 1), (4, 250e3, 1), (6, 10e3, 1), (6, 50e3, 2), (8, 10e3, 1), (8, 400e3, 2)])
+@pytest.mark.parametrize("kind", ["words", "words_hif", "cs16"])
+def test_full_rate_field_extremes(cb, po, torch_cuda, order, fc, D, kind):
+    """The AP form of phase 3 (csrc/iir_rerun.cuh: the (1 + q)^2K numerator as integer two-tap sums, three of them on
+    both 13-bit fields in the 16-bit halves of one register, the sum dropped into a double's mantissa) has bit budgets:
+    long stretches at both ends of the field range, one rail at +max while the other sits at -max, and alternating
+    extremes must come out like the sequential cascade.  CS16 input over the whole int16 range."""
+    torch = torch_cuda
+    n = 1 << 17
+    sos = po.butter_lowpass_sos(order, 4e6, fc)
+    rng = np.random.default_rng(order + D)
+    lo, hi = (-4096, 4095) if kind != "cs16" else (-32768, 32767)
+    i = rng.integers(lo, hi + 1, n)
+    q = rng.integers(lo, hi + 1, n)
+    i[1000:9000] = hi; q[1000:9000] = lo                 # opposite ends, longer than any run
+    i[20000:28000] = lo; q[20000:28000] = lo
+    i[40000:48000] = hi; q[40000:48000] = hi
+    i[60000:61000:2] = hi; i[60001:61000:2] = lo          # Nyquist at full scale
+    q[60000:61000:2] = lo; q[60001:61000:2] = hi
+    iq = np.stack([i, q], 1).astype(np.int16)
+    ref = po.filter_cf32_f32(sos, (iq.astype(np.float32) / np.float32(4096.0)))[::D]
+    out = torch.zeros((n // D, 2), dtype=torch.float32, device="cuda:0")
+    ch = cb.CH_HIF if kind == "words_hif" else cb.CH_S1G
+    with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32, channel=ch) as ctx:
+        if kind == "cs16":
+            ctx.filter_submit(cb.IN_CS16, _dev(torch, iq), n, out)
+        else:
+            w = po.make_word(i, q, 0, po.CH_HIF if kind == "words_hif" else po.CH_S1G).astype(np.uint32)
+            ctx.filter_submit(cb.IN_WORDS, _dev(torch, w.view(np.int32)), n, out)
+        assert ctx.wait()[0] == n
+    got = out.cpu().numpy()
+    assert np.all(rel_rms(got, ref) <= TOL)
+    # and sample by sample around the stretches (a lost carry would be a step of 2^13 or more of an LSB)
+    assert np.max(np.abs(got.astype(np.float64) - ref)) <= 2e-6 * max(1.0, np.max(np.abs(ref)))
