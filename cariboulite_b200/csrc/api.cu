@@ -1214,7 +1214,10 @@ int caribou_cuda_filter_info(caribou_cuda_ctx* c, caribou_cuda_filter_info_t* in
     info->lookback_window = P.window; info->chained = P.chained ? 1 : 0;
     info->decay_samples = P.decay_samples;
     info->parallel_form_error = P.par_err;
-    snprintf(info->note, sizeof(info->note), "%s", P.form_note);
+    if (P.rerun && P.ap)
+        snprintf(info->note, sizeof(info->note), "integer inputs: numerator as integer two-tap sums + all-pole cascade (%.1e)", P.ap_err);
+    else
+        snprintf(info->note, sizeof(info->note), "%s", P.form_note);
     return CARIBOU_CUDA_OK;
 }
 

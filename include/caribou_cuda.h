@@ -96,7 +96,8 @@ typedef struct {
     int      chained;              /* 1: no useful contraction, tiles wait for the predecessor's inclusive state */
     uint64_t decay_samples;        /* samples after which an initial state has decayed below 2^-60 (0 if chained) */
     double   parallel_form_error;  /* parallel vs cascade realisation, rel. rms in extended precision */
-    char     note[96];             /* why the cascade form was kept, if it was */
+    char     note[96];             /* why the cascade form was kept, if it was; full-rate plans that apply the numerator
+                                      as integer two-tap sums say so here (with the form's measured error) */
 } caribou_cuda_filter_info_t;
 
 /* Output buffers of the unpack stage.  Any pointer may be NULL (= not wanted), as in

@@ -247,3 +247,22 @@ def test_full_rate_field_extremes(cb, po, torch_cuda, order, fc, D, kind):
     assert np.all(rel_rms(got, ref) <= TOL)
     # and sample by sample around the stretches (a lost carry would be a step of 2^13 or more of an LSB)
     assert np.max(np.abs(got.astype(np.float64) - ref)) <= 2e-6 * max(1.0, np.max(np.abs(ref)))
+
+
+def test_filter_info_names_the_integer_numerator_form(cb, po, torch_cuda):
+    """Even-order Butterworth low-passes at full rate take the AP form of phase 3 (zeros all at z = -1); a filter with
+    other zeros keeps the parallel-form phase 3 and is still right."""
+    torch = torch_cuda
+    n = 1 << 16
+    w = po.gen_words(n, seed=2)
+    d_w = _dev(torch, w.view(np.int32))
+    for order, fc, scale_b1, expect in ((6, 25e3, 1.0, True), (4, 250e3, 0.97, False), (5, 100e3, 1.0, False)):
+        sos = po.butter_lowpass_sos(order, 4e6, fc).copy()
+        sos[-1, 1] *= scale_b1
+        out = torch.zeros((n, 2), dtype=torch.float32, device="cuda:0")
+        with cb.Context(sos=sos, decimation=1, parity=cb.PARITY_F32) as ctx:
+            note = ctx.filter_info().note.decode()
+            assert ("integer two-tap sums" in note) == expect, (order, note)
+            ctx.rx_submit(d_w, n * 4, out)
+            assert ctx.wait()[0] == n
+        assert np.all(rel_rms(out.cpu().numpy(), po.rx_path_f32(w, sos, 1)) <= TOL), order
