@@ -32,6 +32,12 @@
 
 namespace cbl {
 
+#ifndef CBL_RR_L2HINT
+#define CBL_RR_L2HINT 0          // L2 eviction-priority hints on the two requests of a box (sweeps 29 and 40: no gain)
+#endif
+#ifndef CBL_RR_RESIDENT
+#define CBL_RR_RESIDENT 1        // tiles that fit the ring are not fetched a second time
+#endif
 #ifndef CBL_RR_RING
 #define CBL_RR_RING 4            // 4 KiB boxes in a warp's ring
 #endif
@@ -146,6 +152,9 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     constexpr bool INJECT = IN != IN_CF32;
     const int N = (int)P.rr_boxes;                              // boxes per tile
     const uint32_t R = N < C::R ? (uint32_t)N : (uint32_t)C::R;  // ring slots in use
+    // a tile that fits the ring stays in shared memory between the passes: no second fetch (the ring slot of box b is
+    // handed to box b of the warp's next tile when phase 3 is done with it)
+    const bool resident = CBL_RR_RESIDENT != 0 && (uint32_t)N == R;
     extern __shared__ uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -166,10 +175,17 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     const uint32_t inj_xor = P.inj_xor, inj_mul = P.inj_mul;
 
     // box `b` of tile (stream, tis) into ring slot `slot` (lane 0 only)
-    auto issue_box = [&](uint32_t stream, uint32_t tis, int b, uint32_t slot) {
+    // `again`: the second request of a box (phase 3).  CBL_RR_L2HINT: the first request asks L2 to keep the lines
+    // (evict_last), the second one releases them (evict_first)
+    auto issue_box = [&](uint32_t stream, uint32_t tis, int b, uint32_t slot, bool again = false) {
         const uint32_t bar = bar_u32 + 8 * slot;
         mbar_expect_tx(bar, 4096);
+#if CBL_RR_L2HINT
+        tma_load_3d_hint(ring_u32 + slot * 4096, &tmap, b * 32, (int)tis * 32, (int)stream, bar, again ? kL2EvictFirst : kL2EvictLast);
+#else
+        (void)again;
         tma_load_3d(ring_u32 + slot * 4096, &tmap, b * 32, (int)tis * 32, (int)stream, bar);
+#endif
     };
 
     // 16-byte piece c of this lane's row in box `box_u32`
@@ -234,10 +250,12 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 if (lane == 0) {
                     const int nb = b + (int)R;
                     if (nb < N) issue_box(stream, tis, nb, st);
-                    else if (live) issue_box(stream, tis, nb - N, st);
+                    else if (live && !resident) issue_box(stream, tis, nb - N, st, true);
                 }
                 if (++slot == R) { slot = 0; par ^= 1u; }
             }
+            // resident tile: its boxes were not requested again, phase 3 looks at the barrier phases phase 1 saw
+            if (resident && live) par ^= 1u;
 #pragma unroll
             for (int k = 0; k < K; k++) {
                 f[0][2 * k] = va[k][0] - T.sbias[2 * k]; f[0][2 * k + 1] = va[k][1] - T.sbias[2 * k + 1];
@@ -535,7 +553,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 if (lane == 0) {
                     const int nb = b + (int)R;
                     if (nb < N) {
-                        issue_box(stream, tis, nb, st);
+                        issue_box(stream, tis, nb, st, true);
                     } else {
                         nstream = next / tps;
                         ntis = next - nstream * tps;
