@@ -176,6 +176,7 @@ int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t
     T.out_bias = -bias * P.hn1 * T.gain;
     const int layout = c->cfg.channel == CARIBOU_CUDA_CH_HIF ? 1 : 0;
     const size_t es = in_elem_bytes(in_kind);
+    bool need_commit = false;
 
     if (n_runs > 0) {
         uint64_t tiles_ps = (n_runs + 31) / 32;
@@ -188,9 +189,11 @@ int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t
             return CARIBOU_CUDA_ERR;
         CUtensorMap tm;
         if (!make_run_tmap(&tm, d_in, LT, (int)(es / 4), n_runs, ns, (uint64_t)in_stride * es)) return CARIBOU_CUDA_ERR;
-        if (c->desc_precleared) {
-            c->desc_precleared = false;       // the sharded hand-off's composition kernel has emptied both (shard.cu)
-        } else {
+        // an earlier kernel of this submit may have emptied exactly these descriptors and the ticket already (the
+        // control-block preparation of the rx path, the sharded hand-off's composition kernel)
+        const bool precleared = c->precleared_ptr == desc.p && c->precleared_doubles == total * 2 * P.S;
+        c->precleared_ptr = nullptr;
+        if (!precleared) {
             CBL_CHECK(cudaMemsetAsync(desc.p, 0xFF, total * 2 * P.S * 8, c->stream));      // kDescEmpty everywhere
             CBL_CHECK(cudaMemsetAsync(c->d_ticket, 0, 4, c->stream));
         }
@@ -267,22 +270,22 @@ int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t
         prof_mark(c, 1);
         if (e != 0) { cuda_ok((cudaError_t)e, "iir_scan_kernel launch"); return CARIBOU_CUDA_ERR; }
         c->launches++;
-        if (p.write_state) {
-            launch_commit_state(state + st_off, c->d_state_next + st_off, ns, (size_t)2 * P.S, gate, gate_stride, c->stream);
-            c->launches++;
-        }
+        need_commit = p.write_state != 0;
     }
-    if (n_main < n && max_tiles == 0) {
+    // the remainder that fills no run, and the commit of the state the scan kernel left in its scratch array, are one
+    // launch: the tail kernel starts from that array and writes the context's state (first == n: commit only)
+    if ((n_main < n && max_tiles == 0) || need_commit) {
         IirTailParams t;
         memset(&t, 0, sizeof(t));
         t.n_streams = ns;
         t.in = d_in; t.in_stride = in_stride;
-        t.first = n_main; t.n = n;
+        t.first = n_main; t.n = max_tiles == 0 ? n : n_main;
         t.out = d_out; t.out_stride = out_stride;
         t.in_kind = in_kind; t.layout = layout; t.out_mode = c->out_mode; t.K = P.K; t.D = P.D; t.par = P.par ? 1 : 0;
         for (int k = 0; k < P.K; k++) { t.a1[k] = T.a1[k]; t.a2[k] = T.a2[k]; t.c1[k] = T.c1[k]; t.c2[k] = T.c2[k]; }
         t.gain = T.gain;
         t.state = state + st_off;
+        t.state_src = need_commit ? c->d_state_next + st_off : nullptr;
         t.gate = gate;
         t.gate_stride = gate_stride;
         launch_iir_tail(t, c->stream);
@@ -326,7 +329,31 @@ static SubGeom sub_geom(const caribou_cuda_ctx* c, const void* d_bytes, size_t n
     return g;
 }
 
-int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes, bool with_gates)
+// Everything the alignment search and the scan kernel that follows need reset, in one launch instead of five memsets:
+// first-bad-chunk slots to "none", the counters and per-capture misalignment counts to zero, the scan kernel's
+// look-back descriptors to "empty" and its ticket to zero.
+struct PrepParams {
+    int32_t* first_bad; uint32_t n_first_bad;
+    uint32_t* counters; uint32_t n_counters;        // 32-bit words, nullptr: leave alone
+    int32_t* nmis; uint32_t n_nmis;
+    unsigned long long* desc; uint32_t n_desc;
+    uint32_t* ticket;
+};
+__global__ void ctrl_prep_kernel(const PrepParams p)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x, nt = gridDim.x * blockDim.x;
+    for (uint32_t i = t; i < p.n_first_bad; i += nt) p.first_bad[i] = 0x7f7f7f7f;
+    if (p.counters) for (uint32_t i = t; i < p.n_counters; i += nt) p.counters[i] = 0u;
+    if (p.nmis) for (uint32_t i = t; i < p.n_nmis; i += nt) p.nmis[i] = 0;
+    if (p.desc) {
+        for (uint32_t i = t; i < p.n_desc; i += nt) p.desc[i] = kDescEmpty;
+        if (t == 0) *p.ticket = 0u;
+    }
+}
+
+// iir_n > 0: a run_iir over iir_n samples per stream of the same window follows at once (whole streams, raw words):
+// its descriptors and ticket are emptied here as well
+int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes, bool with_gates, size_t iir_n)
 {
     // d_bytes points at the first stream of the current window (c->win0, c->win_cnt)
     const uint32_t ns_all = (uint32_t)c->cfg.n_streams, ns = c->win_cnt, w0 = c->win0;
@@ -335,9 +362,29 @@ int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, si
     for (int s = 0; s < nsub; s++) max_chunks = std::max(max_chunks, sub_geom(c, d_bytes, nbytes, s).n_chunks);
     if (!c->offs.reserve((size_t)ns_all * 2 * std::max<uint32_t>(max_chunks, 1) * 4)) return CARIBOU_CUDA_ERR;
     // first_bad <- INT_MAX (0x7f7f7f7f is large enough) for the window; counters <- 0 at the first window
-    CBL_CHECK(cudaMemsetAsync(c->d_first_bad + (size_t)w0 * 2, 0x7f, (size_t)ns * 2 * 4, c->stream));
-    if (w0 == 0) CBL_CHECK(cudaMemsetAsync(c->d_counters, 0, sizeof(Counters), c->stream));
-    if (with_gates) CBL_CHECK(cudaMemsetAsync(c->d_sflags + 2 * (size_t)ns_all + w0, 0, (size_t)ns * 4, c->stream));
+    PrepParams pp;
+    memset(&pp, 0, sizeof(pp));
+    pp.first_bad = c->d_first_bad + (size_t)w0 * 2; pp.n_first_bad = ns * 2;
+    if (w0 == 0) { pp.counters = reinterpret_cast<uint32_t*>(c->d_counters); pp.n_counters = (uint32_t)(sizeof(Counters) / 4); }
+    if (with_gates) { pp.nmis = c->d_sflags + 2 * (size_t)ns_all + w0; pp.n_nmis = ns; }
+    c->precleared_ptr = nullptr;
+    if (iir_n > 0 && c->has_filter) {
+        const FilterPlan& P = pick_plan(c, iir_n);
+        const uint64_t n_runs = iir_n / (size_t)P.LT, total = (n_runs + 31) / 32 * ns;
+        DevBuf& desc = P.chained ? c->desc_incl : c->desc_agg;
+        if (n_runs > 0 && total * 2 * P.S < (1ull << 31)) {
+            if (!desc.reserve(total * 2 * P.S * 8)) return CARIBOU_CUDA_ERR;
+            pp.desc = desc.as<unsigned long long>(); pp.n_desc = (uint32_t)(total * 2 * P.S);
+            pp.ticket = c->d_ticket;
+            c->precleared_ptr = desc.p; c->precleared_doubles = total * 2 * P.S;
+        }
+    }
+    {
+        const uint32_t work = std::max<uint32_t>(std::max(pp.n_first_bad, pp.n_desc), 256);
+        const unsigned grid = (unsigned)std::min<uint32_t>((work + 1023) / 1024, (uint32_t)c->num_sms * 2);
+        ctrl_prep_kernel<<<grid, 256, 0, c->stream>>>(pp);
+        c->launches++;
+    }
     for (int s = 0; s < nsub; s++) {
         const SubGeom g = sub_geom(c, d_bytes, nbytes, s);
         OffsetsParams p;
@@ -984,7 +1031,7 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
                 CBL_CHECK(cudaEventRecord(c->pipe_ev[2 * g], c->h2d_stream));
                 CBL_CHECK(cudaStreamWaitEvent(c->stream, c->pipe_ev[2 * g], 0));
                 c->win0 = (uint32_t)s0; c->win_cnt = (uint32_t)cnt;
-                const int mcg = run_find_offsets(c, db + s0 * stride_bytes, nbytes, stride_bytes, true);
+                const int mcg = run_find_offsets(c, db + s0 * stride_bytes, nbytes, stride_bytes, true, n);
                 if (mcg < 0) { rc = mcg; break; }
                 rc = run_iir(c, IN_WORDS, db + s0 * stride_bytes, n, stride_bytes / 4, dob + s0 * filt_stride * c->out_elem, filt_stride,
                              gates + s0, 1, true, 0, nullptr);
@@ -1008,7 +1055,7 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
         CBL_CHECK(cudaMemcpyAsync(c->stage_in.p, bytes, in_span, cudaMemcpyHostToDevice, c->stream));
     }
     q.d_bytes = d_bytes; q.d_out = d_out;
-    const int mc = run_find_offsets(c, d_bytes, nbytes, stride_bytes, true);
+    const int mc = run_find_offsets(c, d_bytes, nbytes, stride_bytes, true, n);
     if (mc < 0) return mc;
     // optimistic fused launch: captures whose gate the search just raised are skipped on the device
     if (run_iir(c, IN_WORDS, d_bytes, n, stride_bytes / 4, d_out, filt_stride, gates, 1, true, 0, nullptr) != CARIBOU_CUDA_OK)

@@ -67,7 +67,7 @@ int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t
             double* state);
 // alignment search of the window's streams; returns the chunk count (>= 0) or an error code.
 // with_gates: also raise the sticky per-stream gates the fused launches look at
-int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes, bool with_gates);
+int run_find_offsets(caribou_cuda_ctx* c, const void* d_bytes, size_t nbytes, size_t stride_bytes, bool with_gates, size_t iir_n = 0);
 // the plan run_iir takes for a submit of n samples per stream (the short-run plan when the long-run one would leave most
 // of the GPU without a tile)
 const FilterPlan& pick_plan(const caribou_cuda_ctx* c, size_t n);
@@ -117,7 +117,8 @@ struct caribou_cuda_ctx {
     cbl::DevBuf desc_inv, desc_syn;
     uint8_t* d_ctrl = nullptr;        // control block: counters, first bad chunks, per-stream flags (pointers below)
     uint8_t* h_ctrl = nullptr;        // its page-locked mirror
-    bool desc_precleared = false;     // the next run_iir finds its descriptors and ticket already emptied (shard.cu)
+    const void* precleared_ptr = nullptr;   // descriptors (and the ticket) an earlier kernel of the submit has emptied for
+    uint64_t precleared_doubles = 0;        // the next run_iir: it skips its memsets when they are exactly the ones it needs
     size_t ctrl_bytes = 0;
     cbl::Counters* d_counters = nullptr;
     cbl::Counters* h_counters = nullptr;   // pinned

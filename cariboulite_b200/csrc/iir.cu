@@ -39,89 +39,101 @@ int launch_iir(int K, int D, int in_kind, bool par, bool y32, const CUtensorMap&
     return fn(tmap, p, t, num_sms, st);
 }
 
-// ------------------------------------------------------------------ sequential tail
-// One warp per stream; lanes 0 and 1 (rails I and Q: same coefficients, never shared state) walk samples [first, n)
-// with the same (normalised) arithmetic, starting from and updating the stream state.  Used for the < one-run
-// remainder of a submit.  Pure latency: the whole warp first brings up to kTailChunk samples into shared memory with
-// one round of coalesced loads (a thread fetching its own samples 16 at a time paid a global round trip per 16
-// samples: 16 us for C4's 96-sample remainders), K and the realisation are compile-time so the state lives in
-// registers, and the decimation phase is carried instead of divided.
+// ------------------------------------------------------------------ sequential tail (and state commit)
+// One warp per stream walks samples [first, n) - the < one-run remainder of a submit - with the same (normalised)
+// arithmetic, starting from and updating the stream state; with state_src it starts from the state the scan kernel
+// left in its scratch array, so that the commit of a submit is this kernel too (first == n: commit only).
+// Pure latency, so everything that is not the recurrence is taken off the walkers: the whole warp brings up to
+// kTailChunk samples in with one round of coalesced loads and converts them (both rails) into shared memory; lanes 0
+// and 1 (rails I and Q: same coefficients, never shared state) run the recurrence over those doubles - K and the
+// realisation are compile-time, the state lives in registers, the decimation phase is carried instead of divided - and
+// leave the kept outputs in shared memory; the whole warp converts and stores them.
 constexpr int kTailWarps = 4;        // streams per block
 constexpr int kTailChunk = 256;      // samples staged per round
+__device__ __forceinline__ void tail_store(const IirTailParams& P, uint64_t o, double yi, double yq)
+{
+    if (P.out_mode == OUT_F32) {
+        reinterpret_cast<float2*>(P.out)[o] = make_float2((float)yi, (float)yq);
+    } else if (P.out_mode == OUT_F64) {
+        reinterpret_cast<double2*>(P.out)[o] = make_double2(yi, yq);
+    } else {
+        const int qi = (int)(int16_t)__float2int_rz((float)yi), qq = (int)(int16_t)__float2int_rz((float)yq);
+        if (P.out_mode == OUT_Q16_CS16) reinterpret_cast<uint32_t*>(P.out)[o] = ((uint32_t)qi & 0xFFFFu) | ((uint32_t)qq << 16);
+        else if (P.out_mode == OUT_Q16_CF32) reinterpret_cast<float2*>(P.out)[o] = make_float2((float)qi * (1.0f / 4096.0f), (float)qq * (1.0f / 4096.0f));
+        else if (P.out_mode == OUT_Q16_CF64) reinterpret_cast<double2*>(P.out)[o] = make_double2((double)qi * (1.0 / 4096.0), (double)qq * (1.0 / 4096.0));
+        else reinterpret_cast<uint16_t*>(P.out)[o] = (uint16_t)(((uint32_t)(qi >> 5) & 0xFFu) | (((uint32_t)(qq >> 5) & 0xFFu) << 8));
+    }
+}
 template <int K, bool PAR>
 __global__ void __launch_bounds__(kTailWarps * 32) iir_tail_kernel(const __grid_constant__ IirTailParams P)
 {
-    __shared__ uint32_t s_buf[kTailWarps][kTailChunk * 2];
+    __shared__ double s_x[kTailWarps][2][kTailChunk];      // converted samples per rail
+    __shared__ double s_y[kTailWarps][2][kTailChunk];      // kept outputs per rail
+    __shared__ uint32_t s_kept[kTailWarps];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t stream = blockIdx.x * kTailWarps + warp, rail = lane & 1u;          // rail 0 = I, 1 = Q
     if (stream >= P.n_streams) return;
     if (P.gate != nullptr && P.gate[(size_t)stream * P.gate_stride] != 0) return;
     const bool walker = lane < 2;
-    uint32_t* const buf = s_buf[warp];
     constexpr int S = 2 * K;
     double v[K][2];
     double* sp = P.state + (size_t)stream * (2 * S) + rail * S;
+    const double* sp_in = (P.state_src != nullptr ? P.state_src : P.state) + (size_t)stream * (2 * S) + rail * S;
 #pragma unroll
-    for (int k = 0; k < K; k++) { v[k][0] = sp[2 * k]; v[k][1] = sp[2 * k + 1]; }
+    for (int k = 0; k < K; k++) { v[k][0] = sp_in[2 * k]; v[k][1] = sp_in[2 * k + 1]; }
     uint32_t ph = (uint32_t)(P.first % (uint64_t)P.D);
-    uint64_t o = ((uint64_t)stream * P.out_stride + (P.first + (uint64_t)P.D - 1) / (uint64_t)P.D) * 2 + rail;   // next kept sample's component
-    // one filter step + the kept-output store
-    auto step = [&](double x) {
-        double in = x;
-#pragma unroll
-        for (int k = 0; k < K; k++) {
-            if (PAR) {      // all sections see x; the output taps the state before the update
-                in = fma(P.c2[k], v[k][1], fma(P.c1[k], v[k][0], in));
-                const double w = fma(-P.a1[k], v[k][0], fma(-P.a2[k], v[k][1], x));
-                v[k][1] = v[k][0]; v[k][0] = w;
-            } else {
-                const double tt = fma(-P.a2[k], v[k][1], in), w = fma(-P.a1[k], v[k][0], tt);
-                in = fma(P.c2[k], v[k][1], fma(P.c1[k], v[k][0], w));
-                v[k][1] = v[k][0]; v[k][0] = w;
-            }
-        }
-        const bool kept = ph == 0;
-        if (++ph == (uint32_t)P.D) ph = 0;
-        if (kept) {
-            const double y = in * P.gain;
-            if (P.out_mode == OUT_F32) {
-                reinterpret_cast<float*>(P.out)[o] = (float)y;
-            } else if (P.out_mode == OUT_F64) {
-                reinterpret_cast<double*>(P.out)[o] = y;
-            } else {
-                const int q = (int)(int16_t)__float2int_rz((float)y);
-                if (P.out_mode == OUT_Q16_CS16) reinterpret_cast<int16_t*>(P.out)[o] = (int16_t)q;
-                else if (P.out_mode == OUT_Q16_CF32) reinterpret_cast<float*>(P.out)[o] = (float)q * (1.0f / 4096.0f);
-                else if (P.out_mode == OUT_Q16_CF64) reinterpret_cast<double*>(P.out)[o] = (double)q * (1.0 / 4096.0);
-                else reinterpret_cast<uint8_t*>(P.out)[o] = (uint8_t)((uint32_t)(q >> 5) & 0xFFu);
-            }
-            o += 2;
-        }
-    };
-    constexpr int CH = 8;
+    uint64_t o = (uint64_t)stream * P.out_stride + (P.first + (uint64_t)P.D - 1) / (uint64_t)P.D;      // next kept sample
     const uint64_t base = (uint64_t)stream * P.in_stride;
-    const uint32_t wps = P.in_kind == IN_CF32 ? 2u : 1u;         // 32-bit words per sample
-    // which half of a word / element this rail reads
-    const bool upper = P.in_kind == IN_WORDS ? (rail == 0) != (P.layout != 0) : rail == 1;    // words: I = hi13 unless HiF
+    const bool a_upper = P.in_kind == IN_WORDS && P.layout == 0;     // words: rail A (I) = hi13 unless HiF
+    const double* __restrict__ const xs = s_x[warp][rail];
+    double* __restrict__ const ys = s_y[warp][rail];
     for (uint64_t n0 = P.first; n0 < P.n; n0 += kTailChunk) {
         const uint32_t cnt = (uint32_t)((P.n - n0) < (uint64_t)kTailChunk ? (P.n - n0) : (uint64_t)kTailChunk);
-        const uint32_t* src = reinterpret_cast<const uint32_t*>(P.in) + (base + n0) * wps;
-        for (uint32_t i = lane; i < cnt * wps; i += 32) buf[i] = __ldg(src + i);
-        __syncwarp();
-        if (walker) {
-            for (uint32_t k0 = 0; k0 < cnt; k0 += CH) {
-                uint32_t w[CH];
-#pragma unroll
-                for (int k = 0; k < CH; k++) w[k] = k0 + k < cnt ? buf[(k0 + k) * wps + (wps == 2 ? rail : 0u)] : 0u;
-#pragma unroll
-                for (int k = 0; k < CH; k++) {
-                    if (k0 + k >= cnt) break;
-                    if (P.in_kind == IN_CF32) step((double)__uint_as_float(w[k]));
-                    else if (P.in_kind == IN_WORDS) step((double)(upper ? hi13(w[k]) : lo13(w[k])));
-                    else step(upper ? (double)((int32_t)w[k] >> 16) : (double)(int)(int16_t)(w[k] & 0xFFFFu));
+        for (uint32_t i = lane; i < cnt; i += 32) {
+            double xa, xb;
+            if (P.in_kind == IN_CF32) {
+                const float2 f = __ldg(reinterpret_cast<const float2*>(P.in) + base + n0 + i);
+                xa = (double)f.x; xb = (double)f.y;
+            } else {
+                const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(P.in) + base + n0 + i);
+                if (P.in_kind == IN_WORDS) {
+                    const double h = (double)hi13(w), l = (double)lo13(w);
+                    xa = a_upper ? h : l; xb = a_upper ? l : h;
+                } else {
+                    xa = (double)(int)(int16_t)(w & 0xFFFFu); xb = (double)((int32_t)w >> 16);
                 }
             }
+            s_x[warp][0][i] = xa; s_x[warp][1][i] = xb;
         }
+        __syncwarp();
+        if (walker) {
+            uint32_t nk = 0;
+#pragma unroll 4
+            for (uint32_t i = 0; i < cnt; i++) {
+                const double x = xs[i];
+                double in = x;
+#pragma unroll
+                for (int k = 0; k < K; k++) {
+                    if (PAR) {      // all sections see x; the output taps the state before the update
+                        in = fma(P.c2[k], v[k][1], fma(P.c1[k], v[k][0], in));
+                        const double w = fma(-P.a1[k], v[k][0], fma(-P.a2[k], v[k][1], x));
+                        v[k][1] = v[k][0]; v[k][0] = w;
+                    } else {
+                        const double tt = fma(-P.a2[k], v[k][1], in), w = fma(-P.a1[k], v[k][0], tt);
+                        in = fma(P.c2[k], v[k][1], fma(P.c1[k], v[k][0], w));
+                        v[k][1] = v[k][0]; v[k][0] = w;
+                    }
+                }
+                const bool kept = ph == 0;
+                if (++ph == (uint32_t)P.D) ph = 0;
+                if (kept) ys[nk++] = in * P.gain;
+            }
+            if (lane == 0) s_kept[warp] = nk;
+        }
+        __syncwarp();
+        const uint32_t nk = s_kept[warp];
+        for (uint32_t j = lane; j < nk; j += 32) tail_store(P, o + j, s_y[warp][0][j], s_y[warp][1][j]);
+        o += nk;
         __syncwarp();
     }
     if (walker) {
@@ -132,7 +144,7 @@ __global__ void __launch_bounds__(kTailWarps * 32) iir_tail_kernel(const __grid_
 
 void launch_iir_tail(const IirTailParams& p, cudaStream_t st)
 {
-    if (p.n_streams == 0 || p.first >= p.n) return;
+    if (p.n_streams == 0 || (p.first >= p.n && p.state_src == nullptr)) return;
     const unsigned grid = (p.n_streams + kTailWarps - 1) / kTailWarps;      // one warp per stream
     switch (p.K * 2 + (p.par ? 1 : 0)) {
         case 2: iir_tail_kernel<1, false><<<grid, kTailWarps * 32, 0, st>>>(p); break;

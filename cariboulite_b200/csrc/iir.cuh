@@ -112,7 +112,8 @@ struct IirTailParams {
     int in_kind, layout, out_mode, K, D, par;
     double a1[kMaxK], a2[kMaxK], c1[kMaxK], c2[kMaxK];
     double gain;
-    double* state;                          // [n_streams][2S] kernel coordinates, updated in place
+    double* state;                          // [n_streams][2S] kernel coordinates, updated in place ...
+    const double* state_src;                // ... or, when set, read from here and written to `state` (the commit of a submit)
     const int32_t* gate;                    // optional: stream s is skipped when gate[s * gate_stride] != 0
     uint32_t gate_stride;
 };

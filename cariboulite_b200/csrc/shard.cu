@@ -377,7 +377,7 @@ static int shard_begin(caribou_cuda_ctx* c, int in_kind, const void* in, size_t 
     const int32_t* gate = nullptr;
     if (in_kind == IN_WORDS) {
         const size_t es = 4;
-        const int mc = run_find_offsets(c, in, n * es, in_stride * es, false);
+        const int mc = run_find_offsets(c, in, n * es, in_stride * es, false, n);
         if (mc < 0) return mc;
         gate = &c->d_counters->any_misaligned;
         if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
@@ -421,7 +421,7 @@ static int shard_fixup(caribou_cuda_ctx* c)
         if (run_iir(c, s->in_kind, s->in, s->n, s->in_stride, s->out, s->out_stride, gate, 0, true, 0, s->d_work) != CARIBOU_CUDA_OK)
             return CARIBOU_CUDA_ERR;
     } else {
-        c->desc_precleared = s->precleared;     // consumed by this run_iir
+        // (the composition kernel has emptied this launch's descriptors and ticket: c->precleared_ptr, consumed by run_iir)
         if (run_iir(c, s->in_kind, s->in, s->n, s->in_stride, s->out, s->out_stride, gate, 0, false, fp.max_tiles, s->d_sin) != CARIBOU_CUDA_OK)
             return CARIBOU_CUDA_ERR;
     }
@@ -473,6 +473,7 @@ static int shard_compose(caribou_cuda_ctx* c, bool peer = false)
             p.clear_n = (uint32_t)doubles;
             p.clear_ticket = c->d_ticket;
             s->precleared = true;
+            c->precleared_ptr = desc.p; c->precleared_doubles = doubles;
         }
     }
     const unsigned threads = 128, grid = (unsigned)std::min<size_t>((s->per_rank + threads - 1) / threads, 64);
