@@ -16,62 +16,74 @@
 namespace cbl {
 
 // ------------------------------------------------------------------ alignment search (A2)
-// One small CTA per chunk (thousands of chunks per submit, and the aligned common case is four loads by one
-// thread: many CTAs per SM keep that latency-bound pass short).  Candidate 0 is tested first; otherwise the CTA
-// sweeps the chunk 4 * blockDim candidates at a time and stops at the first hit.
-constexpr int kFindThreads = 64;
+// A CTA takes kFindChunks consecutive chunks of one stream.  The aligned common case is four loads: warp w tests
+// candidate 0 of chunk w with its first four lanes (one CTA per chunk was 8192 CTAs of which one thread each did that:
+// 7.5 us for C4's 8192 chunks, launch- and latency-bound).  A chunk that fails is swept by the whole CTA,
+// 4 * blockDim candidates at a time, stopping at the first hit.
+constexpr int kFindChunks = 8;
+constexpr int kFindThreads = kFindChunks * 32;
 __global__ void __launch_bounds__(kFindThreads) find_offsets_kernel(OffsetsParams p)
 {
+    __shared__ int s_res[kFindChunks];
     __shared__ int s_found;
-    const uint32_t c = blockIdx.x;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t c0 = blockIdx.x * kFindChunks;
     p.sv.words = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(p.sv.words) +
                                                    (uint64_t)blockIdx.y * p.stream_stride_bytes);
-    const uint64_t start = (uint64_t)c * p.chunk_bytes;
-    const uint64_t rem = p.sv.nbytes - start;
-    const uint32_t len = rem < p.chunk_bytes ? (uint32_t)rem : p.chunk_bytes;
-    int result;
-    if (len <= 16) {                       // caribou_smi.c:240-243
-        result = 0;
-    } else {
-        if (threadIdx.x == 0) {
-            bool ok = true;
-            for (int k = 0; k < 4; k++) ok = ok && hdr_ok(sv_u32_at(p.sv, start + 4 * k));
-            s_found = ok ? 0 : INT_MAX;
+    auto chunk_len = [&](uint32_t c) {
+        const uint64_t rem = p.sv.nbytes - (uint64_t)c * p.chunk_bytes;
+        return rem < p.chunk_bytes ? (uint32_t)rem : p.chunk_bytes;
+    };
+    {
+        const uint32_t c = c0 + warp;
+        int res = 0;
+        if (c < p.n_chunks && chunk_len(c) > 16) {             // len <= 16: caribou_smi.c:240-243
+            const bool ok = lane < 4 ? hdr_ok(sv_u32_at(p.sv, (uint64_t)c * p.chunk_bytes + 4 * lane)) : true;
+            res = __all_sync(0xffffffffu, ok) ? 0 : INT_MAX;
         }
+        if (lane == 0) s_res[warp] = res;
+    }
+    __syncthreads();
+    for (int w = 0; w < kFindChunks; w++) {
+        if (s_res[w] != INT_MAX) continue;                     // the same for every thread of the CTA
+        const uint32_t c = c0 + (uint32_t)w;
+        const uint64_t start = (uint64_t)c * p.chunk_bytes;
+        const uint32_t ncand = chunk_len(c) - 16;              // candidates offs in [0, len-16), caribou_smi.c:248
+        if (threadIdx.x == 0) s_found = INT_MAX;
         __syncthreads();
-        result = s_found;
-        if (result != 0) {
-            const uint32_t ncand = len - 16;        // candidates offs in [0, len-16), caribou_smi.c:248
-            for (uint32_t base = 0; base < ncand; base += 4 * kFindThreads) {
-                // this thread: candidates base + 4*tid + {0,1,2,3}; they share aligned words w[0..4]
-                const uint32_t o0 = base + 4 * threadIdx.x;
-                if (o0 < ncand) {
-                    uint32_t w[5];
-                    const uint64_t wi = (start + o0) >> 2;   // start is a multiple of 4 (chunk_bytes % 16 == 0)
+        int result = INT_MAX;
+        for (uint32_t base = 0; base < ncand; base += 4 * kFindThreads) {
+            // this thread: candidates base + 4*tid + {0,1,2,3}; they share aligned words w[0..4]
+            const uint32_t o0 = base + 4 * threadIdx.x;
+            if (o0 < ncand) {
+                uint32_t wd[5];
+                const uint64_t wi = (start + o0) >> 2;   // start is a multiple of 4 (chunk_bytes % 16 == 0)
 #pragma unroll
-                    for (int k = 0; k < 5; k++) w[k] = sv_word(p.sv, wi + k);
+                for (int k = 0; k < 5; k++) wd[k] = sv_word(p.sv, wi + k);
 #pragma unroll
-                    for (int b = 0; b < 4; b++) {
-                        if (o0 + b < ncand) {
-                            bool ok = true;
+                for (int b = 0; b < 4; b++) {
+                    if (o0 + b < ncand) {
+                        bool ok = true;
 #pragma unroll
-                            for (int k = 0; k < 4; k++) {
-                                const uint32_t u = b ? __funnelshift_r(w[k], w[k + 1], 8 * b) : w[k];
-                                ok = ok && hdr_ok(u);
-                            }
-                            if (ok) { atomicMin(&s_found, (int)(o0 + b)); break; }
+                        for (int k = 0; k < 4; k++) {
+                            const uint32_t u = b ? __funnelshift_r(wd[k], wd[k + 1], 8 * b) : wd[k];
+                            ok = ok && hdr_ok(u);
                         }
+                        if (ok) { atomicMin(&s_found, (int)(o0 + b)); break; }
                     }
                 }
-                __syncthreads();
-                result = s_found;
-                __syncthreads();
-                if (result != INT_MAX) break;
             }
-            if (result == INT_MAX) result = -1;    // caribou_smi.c:285-289
+            __syncthreads();
+            result = s_found;
+            __syncthreads();
+            if (result != INT_MAX) break;
         }
+        if (threadIdx.x == 0) s_res[w] = result == INT_MAX ? -1 : result;    // caribou_smi.c:285-289
+        __syncthreads();
     }
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < kFindChunks && c0 + threadIdx.x < p.n_chunks) {
+        const uint32_t c = c0 + threadIdx.x;
+        const int result = s_res[threadIdx.x];
         p.offs[(size_t)blockIdx.y * p.offs_stride + c] = result;
         if (result < 0) {
             atomicMin(p.first_bad + (size_t)blockIdx.y * p.first_bad_stride, (int)c);
@@ -94,7 +106,7 @@ __global__ void __launch_bounds__(kFindThreads) find_offsets_kernel(OffsetsParam
 void launch_find_offsets(const OffsetsParams& p, cudaStream_t st)
 {
     if (p.n_chunks == 0 || p.n_streams == 0) return;
-    find_offsets_kernel<<<dim3(p.n_chunks, p.n_streams), kFindThreads, 0, st>>>(p);
+    find_offsets_kernel<<<dim3((p.n_chunks + kFindChunks - 1) / kFindChunks, p.n_streams), kFindThreads, 0, st>>>(p);
 }
 
 // ------------------------------------------------------------------ decode helpers (A3)
