@@ -959,6 +959,9 @@ int caribou_cuda_shard_matrix(caribou_cuda_ctx* c, uint64_t n_samples, double* m
 }
 
 // ------------------------------------------------------------------ fused rx path
+#ifndef CBL_RX_GROUPS
+#define CBL_RX_GROUPS 32         // groups of streams a page-locked host batch is pipelined in (fill and drain are 1/groups)
+#endif
 // Every capture of a batch is an independent read.  The fused kernel is launched optimistically for all of
 // them; the alignment search that runs just before it raises a per-capture gate (sticky until the queue is
 // resolved) for a capture with a misaligned or un-alignable chunk, and the fused kernel, the state commit and
@@ -1005,7 +1008,7 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
         if (mem == CARIBOU_CUDA_MEM_HOST_PINNED && ns >= 4) {
             // ---- pipelined: the batch goes through in groups of streams; group g+1 is on its way up while
             // group g is being filtered and group g-1 is on its way down (both copy engines and the SMs busy)
-            const int kGroups = 8;
+            const int kGroups = CBL_RX_GROUPS;
             const size_t per = (ns + kGroups - 1) / kGroups;
             const int ng = (int)((ns + per - 1) / per);
             if (!c->h2d_stream) {
