@@ -976,6 +976,7 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
     if (!c->has_filter || !filt_out) { set_error("rx_submit needs a filter and an output buffer; use unpack_submit otherwise"); return CARIBOU_CUDA_ERR; }
     const size_t n = nbytes / 4;
     if (check_filter_args(c, n) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (shard_flush(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     if (ensure_scale(c, IN_WORDS) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     if (c->queue.size() >= kMaxQueuedRx && resolve_queue(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     const FilterPlan& P = c->plan;
@@ -1143,6 +1144,7 @@ static int rx_replay_stream(caribou_cuda_ctx* c, const PendingRx& q, size_t s, c
 
 int resolve_queue(caribou_cuda_ctx* c)
 {
+    if (shard_flush(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     if (c->queue.empty()) return CARIBOU_CUDA_OK;
     CBL_CHECK(cudaStreamSynchronize(c->stream));
     const size_t ns = (size_t)c->cfg.n_streams;
@@ -1195,7 +1197,8 @@ extern "C" {
 int64_t caribou_cuda_wait(caribou_cuda_ctx* c, caribou_cuda_result* res)
 {
     if (!c) { set_error("null context"); return CARIBOU_CUDA_ERR; }
-    if (!cuda_ok(cudaSetDevice(c->device), "cudaSetDevice") || !cuda_ok(cudaStreamSynchronize(c->stream), "cudaStreamSynchronize"))
+    if (!cuda_ok(cudaSetDevice(c->device), "cudaSetDevice") || shard_flush(c) != CARIBOU_CUDA_OK ||
+        !cuda_ok(cudaStreamSynchronize(c->stream), "cudaStreamSynchronize"))
         return CARIBOU_CUDA_ERR;
     if (resolve_queue(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     int64_t ret = c->last_ret, ret_b = 0;

@@ -56,6 +56,7 @@ constexpr size_t kMaxQueuedRx = 64;   // rx submits queued without a wait; the n
 
 struct Shard;                     // multi-GPU time sharding (shard.cu)
 void shard_release(Shard* s);
+int shard_flush(caribou_cuda_ctx* c);   // enqueue the hand-off a peer-mode sharded call left for later (no-op otherwise)
 
 // ---- launch sequences shared by api.cu, compat.cu and shard.cu
 // Filters n samples per stream (device memory) of the streams in the context's window.  `state` is the buffer

@@ -89,6 +89,10 @@ static bool nccl_ok(NcclApi* a, ncclResult_t r, const char* what)
     } while (0)
 
 // ------------------------------------------------------------------ per-context sharding state
+struct ShardCall {                  // what one sharded call filters, and its sequence number (peer mode)
+    int in_kind = 0; const void* in = nullptr; size_t n = 0, in_stride = 0; void* out = nullptr; size_t out_stride = 0;
+    unsigned long long seq = 0;
+};
 struct Shard {
     int rank = 0, world = 1, mode = 0;
     ncclComm_t comm = nullptr;
@@ -113,7 +117,13 @@ struct Shard {
     bool ev_valid = false;
     // the call between begin and finish
     bool open = false;
-    int in_kind = 0; const void* in = nullptr; size_t n = 0, in_stride = 0; void* out = nullptr; size_t out_stride = 0;
+    ShardCall cur;
+    // peer mode: the composition and the fix-up of a call are enqueued one call late, after the pass over the NEXT
+    // shard - by then every peer's end vector has long arrived, so no rank waits for the slowest one's pass any more
+    // (caribou_cuda_wait and every other entry point flush the pending hand-off first)
+    bool deferred = false;
+    ShardCall pend;
+    int32_t* d_gate2 = nullptr;     // [2] per call parity: the "shard was misaligned" verdict of that call's alignment search
 };
 
 void shard_release(Shard* s)
@@ -128,6 +138,7 @@ void shard_release(Shard* s)
     for (void* m : s->peer_maps) if (m) cudaIpcCloseMemHandle(m);
     if (s->d_px) cudaFree(s->d_px);
     if (s->d_peers) cudaFree(s->d_peers);
+    if (s->d_gate2) cudaFree(s->d_gate2);
     for (cudaEvent_t e : s->ev) if (e) cudaEventDestroy(e);
     delete s;
 }
@@ -187,6 +198,15 @@ __device__ __forceinline__ void shard_push(double* const* peers, const double* f
     __syncthreads();
     for (int j = threadIdx.x; j < world; j += blockDim.x)
         st_release_sys(reinterpret_cast<unsigned long long*>(peers[j] + flag_off) + rank, seq);
+}
+
+// peer mode with the hand-off one call late: the push right after the pass, and the verdict of the call's alignment search
+// put aside (the next call's search resets the context's flag before this call's composition and fix-up run)
+__global__ void shard_push_kernel(double* const* peers, const double* f_own, uint32_t n_comp, int world, int rank,
+                                  size_t par_off, size_t flag_off, unsigned long long seq, const int32_t* gate_src, int32_t* gate_dst)
+{
+    if (threadIdx.x == 0 && gate_dst != nullptr) *gate_dst = gate_src != nullptr ? *gate_src : 0;
+    shard_push(peers, f_own, n_comp, world, rank, par_off, flag_off, seq);
 }
 
 // The whole hand-off in one launch: push (peer mode), wait for the peers' vectors, compose s_in and the carry, empty
@@ -289,6 +309,8 @@ static int shard_peer_setup(caribou_cuda_ctx* c)
     CBL_CHECK(cudaMalloc(&s->d_px, doubles * 8));
     CBL_CHECK(cudaMemsetAsync(s->d_px, 0, doubles * 8, c->stream));
     CBL_CHECK(cudaMalloc(&s->d_peers, (size_t)s->world * sizeof(double*)));
+    CBL_CHECK(cudaMalloc(&s->d_gate2, 2 * sizeof(int32_t)));
+    CBL_CHECK(cudaMemsetAsync(s->d_gate2, 0, 2 * sizeof(int32_t), c->stream));
     // handles: [world] x (64-byte handle + 1 int "ok so far")
     struct Slot { cudaIpcMemHandle_t h; int ok; int pad[15]; };
     static_assert(sizeof(Slot) == 128, "slot layout");
@@ -358,6 +380,7 @@ static int shard_begin(caribou_cuda_ctx* c, int in_kind, const void* in, size_t 
     if (n % (size_t)P.D != 0) { set_error("n_samples must be a multiple of the decimation factor"); return CARIBOU_CUDA_ERR; }
     if (!c->queue.empty() && resolve_queue(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     if (ensure_scale(c, in_kind) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (s->mpow_n != n && shard_flush(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;     // a pending hand-off needs the old powers
     if (shard_powers(c, n) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     const size_t ns = (size_t)c->cfg.n_streams;
     if (ns == 1) { in_stride = (n + 3) & ~size_t(3); out_stride = n / P.D; }
@@ -388,41 +411,48 @@ static int shard_begin(caribou_cuda_ctx* c, int in_kind, const void* in, size_t 
     if (run_iir(c, in_kind, in, n, in_stride, out, out_stride, gate, 0, true, 0, f_own) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     if (prof) CBL_CHECK(cudaEventRecord(s->ev[1], c->stream));
     s->open = true;
-    s->in_kind = in_kind; s->in = in; s->n = n; s->in_stride = in_stride; s->out = out; s->out_stride = out_stride;
+    s->cur.in_kind = in_kind; s->cur.in = in; s->cur.n = n; s->cur.in_stride = in_stride; s->cur.out = out; s->cur.out_stride = out_stride;
     return CARIBOU_CUDA_OK;
 }
 
-// what the fix-up of this call launches: the leading tiles only (partial), or the whole shard again
+// what the fix-up of a call launches: the leading tiles only (partial), or the whole shard again
 struct FixPlan { bool partial; uint32_t max_tiles; };
-static FixPlan shard_fix_plan(caribou_cuda_ctx* c)
+static FixPlan shard_fix_plan(caribou_cuda_ctx* c, const ShardCall& k)
 {
-    Shard* s = c->shard;
-    const size_t fix = caribou_cuda_fixup_samples(c, s->n);
-    const int LTn = pick_plan(c, s->n).LT;               // the plan run_iir will take for this shard
+    const size_t fix = caribou_cuda_fixup_samples(c, k.n);
+    const int LTn = pick_plan(c, k.n).LT;               // the plan run_iir will take for this shard
     const uint32_t tile_samples = 32u * (uint32_t)LTn;
     const uint32_t max_tiles = (uint32_t)((fix + tile_samples - 1) / tile_samples);
-    const uint64_t tiles_ps = (s->n / LTn + 31) / 32;
+    const uint64_t tiles_ps = (k.n / LTn + 31) / 32;
     FixPlan f;
     f.partial = !(max_tiles == 0 || max_tiles >= tiles_ps);
     f.max_tiles = max_tiles;
     return f;
 }
 
-// fix-up from d_sin and the new carry into the context's state
-static int shard_fixup(caribou_cuda_ctx* c)
+// the "shard was misaligned" flag the kernels of call k look at: the context's own, or the copy put aside for a
+// hand-off that runs one call late
+static const int32_t* shard_gate(caribou_cuda_ctx* c, const ShardCall& k, bool late)
+{
+    if (k.in_kind != IN_WORDS) return nullptr;
+    return late ? c->shard->d_gate2 + (k.seq & 1) : &c->d_counters->any_misaligned;
+}
+
+// fix-up of call k from d_sin and the new carry into the context's state
+static int shard_fixup(caribou_cuda_ctx* c, const ShardCall& k, bool late)
 {
     Shard* s = c->shard;
     const FilterPlan& P = c->plan;
-    const int32_t* gate = s->in_kind == IN_WORDS ? &c->d_counters->any_misaligned : nullptr;
-    const FixPlan fp = shard_fix_plan(c);
+    const int32_t* gate = shard_gate(c, k, late);
+    const FixPlan fp = shard_fix_plan(c, k);
     if (!fp.partial) {
         // no useful contraction, or a short shard: the whole shard again (tail included) from a scratch copy of s_in
         CBL_CHECK(cudaMemcpyAsync(s->d_work, s->d_sin, s->per_rank * 8, cudaMemcpyDeviceToDevice, c->stream));
-        if (run_iir(c, s->in_kind, s->in, s->n, s->in_stride, s->out, s->out_stride, gate, 0, true, 0, s->d_work) != CARIBOU_CUDA_OK)
+        if (run_iir(c, k.in_kind, k.in, k.n, k.in_stride, k.out, k.out_stride, gate, 0, true, 0, s->d_work) != CARIBOU_CUDA_OK)
             return CARIBOU_CUDA_ERR;
     } else {
         // (the composition kernel has emptied this launch's descriptors and ticket: c->precleared_ptr, consumed by run_iir)
-        if (run_iir(c, s->in_kind, s->in, s->n, s->in_stride, s->out, s->out_stride, gate, 0, false, fp.max_tiles, s->d_sin) != CARIBOU_CUDA_OK)
+        if (run_iir(c, k.in_kind, k.in, k.n, k.in_stride, k.out, k.out_stride, gate, 0, false, fp.max_tiles, s->d_sin) != CARIBOU_CUDA_OK)
             return CARIBOU_CUDA_ERR;
     }
     s->precleared = false;
@@ -431,14 +461,22 @@ static int shard_fixup(caribou_cuda_ctx* c)
         launch_commit_state(c->d_state, s->d_carry, (size_t)c->cfg.n_streams, (size_t)2 * P.S, gate, 0, c->stream);
         c->launches++;
     }
-    c->pos += s->n * (uint64_t)s->world;
-    if (c->profiling) { CBL_CHECK(cudaEventRecord(s->ev[2], c->stream)); s->ev_valid = true; }
-    s->open = false;
+    c->pos += k.n * (uint64_t)s->world;
     CBL_CHECK(cudaGetLastError());
     return CARIBOU_CUDA_OK;
 }
 
-static int shard_compose(caribou_cuda_ctx* c, bool peer = false)
+// end of a call's device work as the profile sees it
+static int shard_mark_end(caribou_cuda_ctx* c)
+{
+    Shard* s = c->shard;
+    if (c->profiling) { CBL_CHECK(cudaEventRecord(s->ev[2], c->stream)); s->ev_valid = true; }
+    s->open = false;
+    return CARIBOU_CUDA_OK;
+}
+
+// peer: the end vectors come through the exchange buffers (flags); push: this launch also sends this rank's own
+static int shard_compose(caribou_cuda_ctx* c, const ShardCall& k, bool peer = false, bool push = false, bool late = false)
 {
     Shard* s = c->shard;
     const size_t ns = (size_t)c->cfg.n_streams;
@@ -451,21 +489,23 @@ static int shard_compose(caribou_cuda_ctx* c, bool peer = false)
     p.err = c->d_sflags + 3 * ns + 1;
     p.err_host = s->err_host;
     if (peer) {
-        const size_t par = (size_t)(s->seq & 1);
+        const size_t par = (size_t)(k.seq & 1);
         p.f = s->d_px + par * s->world * s->per_rank;
         p.flags = reinterpret_cast<const unsigned long long*>(s->d_px + 2 * (size_t)s->world * s->per_rank) + par * s->world;
-        p.seq = s->seq;
-        p.peers = s->d_peers;
-        p.f_own = s->d_f + (size_t)s->rank * s->per_rank;
-        p.par_off = par * s->world * s->per_rank;
-        p.flag_off = 2 * (size_t)s->world * s->per_rank + par * s->world;
+        p.seq = k.seq;
+        if (push) {
+            p.peers = s->d_peers;
+            p.f_own = s->d_f + (size_t)s->rank * s->per_rank;
+            p.par_off = par * s->world * s->per_rank;
+            p.flag_off = 2 * (size_t)s->world * s->per_rank + par * s->world;
+        }
     }
     // a fix-up of a few leading tiles: its descriptors and ticket are emptied here (pass 1 used more tiles of the same
     // plan, so the buffers exist and are large enough)
     s->precleared = false;
-    const FixPlan fp = shard_fix_plan(c);
+    const FixPlan fp = shard_fix_plan(c, k);
     if (fp.partial) {
-        const FilterPlan& P = pick_plan(c, s->n);
+        const FilterPlan& P = pick_plan(c, k.n);
         DevBuf& desc = P.chained ? c->desc_incl : c->desc_agg;
         const uint64_t doubles = (uint64_t)fp.max_tiles * c->win_cnt * 2 * P.S;
         if (desc.p && doubles * 8 <= desc.cap && doubles <= (1u << 16)) {
@@ -478,12 +518,22 @@ static int shard_compose(caribou_cuda_ctx* c, bool peer = false)
     }
     const unsigned threads = 128, grid = (unsigned)std::min<size_t>((s->per_rank + threads - 1) / threads, 64);
     p.commit = grid == 1 ? c->d_state : nullptr;
-    p.gate = s->in_kind == IN_WORDS ? &c->d_counters->any_misaligned : nullptr;
+    p.gate = shard_gate(c, k, late);
     s->committed = grid == 1;
     shard_compose_kernel<<<grid, threads, 0, c->stream>>>(p);
     c->launches++;
     CBL_CHECK(cudaGetLastError());
     return CARIBOU_CUDA_OK;
+}
+
+// the hand-off a peer-mode call left for later (composition + fix-up of that call), now
+int shard_flush(caribou_cuda_ctx* c)
+{
+    Shard* s = c ? c->shard : nullptr;
+    if (!s || !s->deferred) return CARIBOU_CUDA_OK;
+    s->deferred = false;
+    if (shard_compose(c, s->pend, true, false, true) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    return shard_fixup(c, s->pend, true);
 }
 
 }  // namespace cbl
@@ -531,6 +581,7 @@ int caribou_cuda_shard_set_mode(caribou_cuda_ctx* c, int mode)
 {
     if (!c || !c->shard || mode < 0 || mode > 2) { set_error("bad argument"); return CARIBOU_CUDA_ERR; }
     if (mode == 2 && !c->shard->peer_ok) { set_error("peer exchange is not available on this communicator"); return CARIBOU_CUDA_ERR; }
+    if (shard_flush(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     c->shard->mode = mode;
     return CARIBOU_CUDA_OK;
 }
@@ -557,8 +608,9 @@ int caribou_cuda_shard_finish(caribou_cuda_ctx* c)
 {
     if (!c || !c->shard || !c->shard->open) { set_error("caribou_cuda_shard_finish without caribou_cuda_shard_begin"); return CARIBOU_CUDA_ERR; }
     CBL_CHECK(cudaSetDevice(c->device));
-    if (shard_compose(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
-    return shard_fixup(c);
+    if (shard_compose(c, c->shard->cur) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (shard_fixup(c, c->shard->cur, false) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    return shard_mark_end(c);
 }
 
 int caribou_cuda_shard_submit(caribou_cuda_ctx* c, int in_kind, const void* in, size_t n, size_t in_stride, void* out, size_t out_stride)
@@ -566,23 +618,40 @@ int caribou_cuda_shard_submit(caribou_cuda_ctx* c, int in_kind, const void* in, 
     if (!c || !c->shard) { set_error("call caribou_cuda_shard_init first"); return CARIBOU_CUDA_ERR; }
     Shard* s = c->shard;
     if (s->world > 1 && !s->comm) { set_error("no communicator: use caribou_cuda_shard_begin / _finish and move the end vectors yourself"); return CARIBOU_CUDA_ERR; }
+    if (s->mode != 2 && shard_flush(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;       // (the mode was switched)
     if (shard_begin(c, in_kind, in, n, in_stride, out, out_stride) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     if (s->world == 1) {
-        if (shard_compose(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
-        return shard_fixup(c);
+        if (shard_compose(c, s->cur) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        if (shard_fixup(c, s->cur, false) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        return shard_mark_end(c);
     }
     NcclApi* a = nccl_api();
     if (!a) return CARIBOU_CUDA_ERR;
     double* f_own = s->d_f + (size_t)s->rank * s->per_rank;
     if (s->mode == 2) {
+        // pass 1 of this call is queued; now the hand-off of the PREVIOUS call (every peer's vector of that call arrived a
+        // whole pass ago), then this call's push.  Order matters for the two-deep exchange buffers: a rank pushes call
+        // k + 2 into the slots of call k only after its composition of call k + 1, which waited for the peers' pushes of
+        // call k + 1, which they make after their compositions of call k.
+        if (shard_flush(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
         s->seq++;
-        if (shard_compose(c, true) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;     // push + wait + compose in one launch
-        return shard_fixup(c);
+        s->cur.seq = s->seq;
+        const size_t par = (size_t)(s->seq & 1);
+        shard_push_kernel<<<1, 128, 0, c->stream>>>(s->d_peers, f_own, (uint32_t)s->per_rank, s->world, s->rank,
+                                                    par * s->world * s->per_rank,
+                                                    2 * (size_t)s->world * s->per_rank + par * s->world, s->seq,
+                                                    in_kind == IN_WORDS ? &c->d_counters->any_misaligned : nullptr, s->d_gate2 + par);
+        c->launches++;
+        CBL_CHECK(cudaGetLastError());
+        s->pend = s->cur;
+        s->deferred = true;
+        return shard_mark_end(c);
     }
     if (s->mode == 0) {
         CBL_NCCL(a, a->AllGather(f_own, s->d_f, s->per_rank, ncclDouble, s->comm, c->stream));
-        if (shard_compose(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
-        return shard_fixup(c);
+        if (shard_compose(c, s->cur) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        if (shard_fixup(c, s->cur, false) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+        return shard_mark_end(c);
     }
     // chain: s_in travels rank to rank, the last rank broadcasts the state after its shard
     const int S = c->plan.S;
@@ -594,7 +663,8 @@ int caribou_cuda_shard_submit(caribou_cuda_ctx* c, int in_kind, const void* in, 
     if (s->rank < s->world - 1) CBL_NCCL(a, a->Send(s->d_carry, s->per_rank, ncclDouble, s->rank + 1, s->comm, c->stream));
     CBL_NCCL(a, a->Broadcast(s->d_carry, s->d_carry, s->per_rank, ncclDouble, s->world - 1, s->comm, c->stream));
     s->committed = false;
-    return shard_fixup(c);
+    if (shard_fixup(c, s->cur, false) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    return shard_mark_end(c);
 }
 
 // `world` contexts of ONE process (one per GPU, or several on one GPU): every context's end vector is copied
@@ -639,6 +709,7 @@ int caribou_cuda_shard_profile(caribou_cuda_ctx* c, float* pass_ms, float* hando
 {
     if (!c || !c->shard || !c->shard->ev_valid) { set_error("no profiled sharded call (caribou_cuda_set_profiling)"); return CARIBOU_CUDA_ERR; }
     CBL_CHECK(cudaSetDevice(c->device));
+    if (shard_flush(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     CBL_CHECK(cudaStreamSynchronize(c->stream));
     float a = 0, b = 0;
     CBL_CHECK(cudaEventElapsedTime(&a, c->shard->ev[0], c->shard->ev[1]));

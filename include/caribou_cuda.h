@@ -258,6 +258,10 @@ int    caribou_cuda_filter_fixup(caribou_cuda_ctx* ctx, int in_kind, const void*
  *                                         from device memory
  * Nothing on that path touches the host: no stream synchronisation, no host copy.  caribou_cuda_wait returns
  * n_samples (or -3 if a chunk of the shard lost word alignment: shards must consist of aligned chunks).
+ * With the peer exchange (mode 2) the composition and the fix-up of a call are queued one call late - after the pass
+ * of the next call, when every peer's vector has long arrived - so `in` and `out` of a sharded call must stay valid
+ * until the next caribou_cuda_shard_submit has returned or caribou_cuda_wait (or any other call on the context) has
+ * flushed the pending hand-off; the outputs are final after caribou_cuda_wait, as for every asynchronous submit.
  *
  * NCCL is bound at run time (dlopen of libnccl.so.2, so that a process that already carries an NCCL - PyTorch's -
  * shares it): caribou_cuda_shard_unique_id wraps ncclGetUniqueId (rank 0 calls it and ships the 128 bytes to the
