@@ -11,7 +11,9 @@
 //               peer (default when the GPUs can map each other's memory): every rank's exchange buffer is opened in
 //                   every other rank's process (CUDA IPC, handles all-gathered once through NCCL); a one-CTA kernel
 //                   stores f_g straight into all peers' buffers over NVLink and releases a sequence flag, the
-//                   composition kernel acquires the flags - no collective launch on the path at all
+//                   composition kernel acquires the flags - no collective launch on the path at all.  The
+//                   composition and the fix-up of a call are queued one call late (after the pass over the next
+//                   shard): nobody waits for the slowest rank's pass
 //             M = A^n in kernel coordinates; its powers are computed on the host once per shard length
 //   fix-up    the leading tiles a non-zero incoming state can still change above 2^-60 are filtered again from
 //             s_in(g), read from device memory; the context's state becomes carry', so calls chain like on one GPU
@@ -162,10 +164,6 @@ struct ComposeParams {
     // unless *gate says the shard was misaligned
     double* commit;
     const int32_t* gate;
-    // peer mode: the push of this rank's end vector is the first thing the kernel does (peers == nullptr: no push)
-    double* const* peers;
-    const double* f_own;
-    size_t par_off, flag_off;
     // the fix-up launch that follows needs its look-back descriptors empty and its ticket zero: done here instead of
     // by two memsets on the stream (clear_n doubles of kDescEmpty; nullptr: the launch clears them itself)
     unsigned long long* clear_desc;
@@ -209,12 +207,10 @@ __global__ void shard_push_kernel(double* const* peers, const double* f_own, uin
     shard_push(peers, f_own, n_comp, world, rank, par_off, flag_off, seq);
 }
 
-// The whole hand-off in one launch: push (peer mode), wait for the peers' vectors, compose s_in and the carry, empty
-// the descriptors and the ticket of the fix-up launch, commit the carry (single-CTA launches).
+// The hand-off in one launch: wait for the peers' vectors (peer mode), compose s_in and the carry, empty the descriptors
+// and the ticket of the fix-up launch, commit the carry (single-CTA launches).
 __global__ void shard_compose_kernel(const ComposeParams p)
 {
-    if (p.peers != nullptr && blockIdx.x == 0)
-        shard_push(p.peers, p.f_own, p.n_comp, p.world, p.rank, p.par_off, p.flag_off, p.seq);
     if (p.clear_desc != nullptr) {
         for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < p.clear_n; t += gridDim.x * blockDim.x) p.clear_desc[t] = kDescEmpty;
         if (blockIdx.x == 0 && threadIdx.x == 0) *p.clear_ticket = 0;
@@ -475,8 +471,8 @@ static int shard_mark_end(caribou_cuda_ctx* c)
     return CARIBOU_CUDA_OK;
 }
 
-// peer: the end vectors come through the exchange buffers (flags); push: this launch also sends this rank's own
-static int shard_compose(caribou_cuda_ctx* c, const ShardCall& k, bool peer = false, bool push = false, bool late = false)
+// peer: the end vectors come through the exchange buffers (flags); late: the hand-off of an earlier call (shard_flush)
+static int shard_compose(caribou_cuda_ctx* c, const ShardCall& k, bool peer = false, bool late = false)
 {
     Shard* s = c->shard;
     const size_t ns = (size_t)c->cfg.n_streams;
@@ -493,12 +489,6 @@ static int shard_compose(caribou_cuda_ctx* c, const ShardCall& k, bool peer = fa
         p.f = s->d_px + par * s->world * s->per_rank;
         p.flags = reinterpret_cast<const unsigned long long*>(s->d_px + 2 * (size_t)s->world * s->per_rank) + par * s->world;
         p.seq = k.seq;
-        if (push) {
-            p.peers = s->d_peers;
-            p.f_own = s->d_f + (size_t)s->rank * s->per_rank;
-            p.par_off = par * s->world * s->per_rank;
-            p.flag_off = 2 * (size_t)s->world * s->per_rank + par * s->world;
-        }
     }
     // a fix-up of a few leading tiles: its descriptors and ticket are emptied here (pass 1 used more tiles of the same
     // plan, so the buffers exist and are large enough)
@@ -532,7 +522,7 @@ int shard_flush(caribou_cuda_ctx* c)
     Shard* s = c ? c->shard : nullptr;
     if (!s || !s->deferred) return CARIBOU_CUDA_OK;
     s->deferred = false;
-    if (shard_compose(c, s->pend, true, false, true) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (shard_compose(c, s->pend, true, true) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     return shard_fixup(c, s->pend, true);
 }
 
