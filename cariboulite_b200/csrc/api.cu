@@ -264,6 +264,18 @@ int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t
             Tl.gain = L.gain;
             Tl.out_bias = L.out_bias;
         }
+        // rerun kernel: phase 1 takes the boxes that will stay in the ring last (iir_rerun.cuh); the end vectors of its
+        // two parts combine through A^(samples of the first part)
+        if (P.rerun && CBL_RR_RESIDENT) {
+            const int nb = (int)p.rr_boxes, keep = rerun_keep(nb, rerun_ring(P.K, p.ap != 0), p.ap != 0);
+            if (keep > 0 && keep < nb) {
+                const uint64_t len_a = (uint64_t)(nb - keep) * (in_kind == IN_CF32 ? 16 : 32);
+                auto& rp = c->rr_pow[small ? 1 : 0];
+                if (rp.len != len_a) { plan_power_kernel(P, len_a, rp.m); rp.len = len_a; }
+                for (int i = 0; i < P.S; i++)
+                    for (int k = 0; k < P.S; k++) Tl.R[kRrPowRow + i][k] = rp.m[i * P.S + k];
+            }
+        }
         prof_mark(c, 0);
         const int kin = (in_kind == IN_WORDS && layout) ? IN_WORDS_HIF : in_kind;
         const int e = launch_iir(P.K, P.D, kin, P.par, y32, tm, p, Tl, c->num_sms, c->stream);

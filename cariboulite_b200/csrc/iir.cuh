@@ -181,6 +181,23 @@ __host__ __device__ constexpr int iir_run_len(int K, int D, bool y32)
 #ifndef CBL_RR_P3U
 #define CBL_RR_P3U 1             // chunks of four outputs per iteration of the rerun kernel's phase-3 loop
 #endif
+#ifndef CBL_RR_RESIDENT
+#define CBL_RR_RESIDENT 1        // the boxes of a tile still in the ring after phase 1 are not fetched a second time
+#endif
+#ifndef CBL_RR_RING
+#define CBL_RR_RING 4            // 4 KiB boxes in a warp's ring
+#endif
+#ifndef CBL_RR_AP_WARPS
+#define CBL_RR_AP_WARPS 16       // warps per SM of the AP form up to three sections (its serial section chain wants more
+#endif                           // warps to hide behind; 128 registers each), with a ring of three boxes so that they fit
+__host__ __device__ constexpr bool rerun_wide(int K, bool ap) { return ap && K <= 3 && CBL_RR_AP_WARPS > 12; }
+__host__ __device__ constexpr int rerun_ring(int K, bool ap) { return rerun_wide(K, ap) ? 3 : CBL_RR_RING; }
+// boxes of a tile of `boxes` boxes that stay in a ring of `ring` slots between the two passes (iir_rerun.cuh)
+__host__ __device__ constexpr int rerun_keep(int boxes, int ring, bool ap)
+{
+    return CBL_RR_RESIDENT == 0 ? 0 : (boxes <= ring ? boxes : (ap ? 0 : ring));
+}
+constexpr int kRrPowRow = 16;             // IirTables::R rows kRrPowRow.. hold A^(samples of phase 1's first part), S x S
 __host__ __device__ constexpr int iir_rerun_len(int K) { return K <= 2 ? CBL_RR_LT12 : CBL_RR_LT; }
 constexpr int kRerunSmallLT = 64;       // run length of the second plan a context keeps for submits too small to fill the GPU
 constexpr int kRerunP3Unroll = CBL_RR_P3U;

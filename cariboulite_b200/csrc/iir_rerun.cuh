@@ -35,22 +35,12 @@ namespace cbl {
 #ifndef CBL_RR_L2HINT
 #define CBL_RR_L2HINT 0          // L2 eviction-priority hints on the two requests of a box (sweeps 29 and 40: no gain)
 #endif
-#ifndef CBL_RR_RESIDENT
-#define CBL_RR_RESIDENT 1        // tiles that fit the ring are not fetched a second time
-#endif
-#ifndef CBL_RR_RING
-#define CBL_RR_RING 4            // 4 KiB boxes in a warp's ring
-#endif
-
-#ifndef CBL_RR_AP_WARPS
-#define CBL_RR_AP_WARPS 16       // warps per SM of the AP form up to three sections (its serial section chain wants more
-#endif                           // warps to hide behind; 128 registers each), with a ring of three boxes so that they fit
 template <int K, int D, int IN, bool AP = false>
 struct RerunCfg {
     static constexpr int S     = 2 * K;
     static constexpr int SPS   = (IN == IN_CF32) ? 16 : 32;   // samples per 128-byte row step = per box
-    static constexpr bool WIDE = AP && K <= 3 && CBL_RR_AP_WARPS > 12;
-    static constexpr int R     = WIDE ? 3 : CBL_RR_RING;      // ring slots (a tile of fewer boxes uses as many as it has)
+    static constexpr bool WIDE = rerun_wide(K, AP);
+    static constexpr int R     = rerun_ring(K, AP);           // ring slots (a tile of fewer boxes uses as many as it has)
     // the run length is a launch parameter (IirParams::rr_boxes boxes of SPS samples): the plan fixes it
     static constexpr int RING_BYTES    = R * 4096;
     static constexpr int SCRATCH_BYTES = 2 * S * 8 * 2;
@@ -152,9 +142,17 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     constexpr bool INJECT = IN != IN_CF32;
     const int N = (int)P.rr_boxes;                              // boxes per tile
     const uint32_t R = N < C::R ? (uint32_t)N : (uint32_t)C::R;  // ring slots in use
-    // a tile that fits the ring stays in shared memory between the passes: no second fetch (the ring slot of box b is
-    // handed to box b of the warp's next tile when phase 3 is done with it)
-    const bool resident = CBL_RR_RESIDENT != 0 && (uint32_t)N == R;
+    // The last `keep` boxes phase 1 looks at stay in the ring for phase 3, which starts with them: phase 1 takes the
+    // boxes in the order keep .. N-1, 0 .. keep-1 (two parts, each from the steady state; their end vectors combine as
+    // f = A^len(first part) f_second + f_first) and only boxes keep .. N-1 are fetched a second time.  keep = the ring
+    // size; a tile that fits the ring (keep = N) is not fetched twice at all.
+    // (the AP kernels only keep whole tiles: with their 16 warps and 128 registers the split costs what the saved
+    // fetches bring - profiles/r2_sweeps.txt, sweep 42)
+    const int keep = rerun_keep(N, (int)C::R, AP);
+    constexpr bool SPLIT = !AP;                                  // whether phase 1 can come in two parts at all
+    const int LEN = 2 * N - keep;                                // box requests of a tile
+    // request idx of a tile's sequence -> box: phase 1's order, then the second requests
+    auto seq_box = [&](int idx) { return idx < N ? (idx + keep < N ? idx + keep : idx + keep - N) : keep + (idx - N); };
     extern __shared__ uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -193,7 +191,8 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         return lds128((box_u32 + lane * 128 + ((lane & 7) << 4)) ^ (uint32_t)(c << 4));
     };
 
-    uint32_t slot = 0, par = 0;    // ring slot of the next box to consume and the parity its barrier completes with
+    uint32_t slot = 0, pm = 0;     // ring slot of the next box to consume; bit s of pm = parity the pending request of slot s
+                                   // completes its barrier with (flipped whenever a slot is handed to a new request)
     uint32_t tile = 0xFFFFFFFFu;
     uint32_t* const ticket = P.ticket + __ldg(P.ticket + 32 + lane);      // words 32..63 of the ticket block stay zero
     if (lane == 0) {
@@ -202,7 +201,7 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     tile = __shfl_sync(0xffffffffu, tile, 0);
     uint32_t stream = tile / tps, tis = tile - stream * tps;
     if (lane == 0 && tile < P.total_tiles) {
-        for (uint32_t s = 0; s < R; s++) issue_box(stream, tis, (int)s, s);
+        for (uint32_t s = 0; s < R; s++) issue_box(stream, tis, seq_box((int)s), s);
     }
 
     while (tile < P.total_tiles) {
@@ -220,10 +219,22 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 va[k][0] = vb[k][0] = T.sbias[2 * k];
                 va[k][1] = vb[k][1] = T.sbias[2 * k + 1];
             }
+            int li = (int)R;                 // next request of this tile's sequence (R are out when the tile starts)
+            double fa[2][S];                 // end vector of the first part (boxes keep .. N-1)
 #pragma unroll 1
-            for (int b = 0; b < N; b++) {
+            for (int j = 0; j < N; j++) {
+                if (SPLIT && j == N - keep && j != 0) {
+                    // second part (boxes 0 .. keep-1, the ones that stay): from the steady state again
+#pragma unroll
+                    for (int k = 0; k < K; k++) {
+                        fa[0][2 * k] = va[k][0] - T.sbias[2 * k]; fa[0][2 * k + 1] = va[k][1] - T.sbias[2 * k + 1];
+                        fa[1][2 * k] = vb[k][0] - T.sbias[2 * k]; fa[1][2 * k + 1] = vb[k][1] - T.sbias[2 * k + 1];
+                        va[k][0] = vb[k][0] = T.sbias[2 * k];
+                        va[k][1] = vb[k][1] = T.sbias[2 * k + 1];
+                    }
+                }
                 const uint32_t st = slot;
-                mbar_wait(bar_u32 + 8 * st, par);
+                mbar_wait(bar_u32 + 8 * st, (pm >> st) & 1u);
                 const uint32_t box = ring_u32 + st * 4096;
                 // the 128-byte row in two groups of four pieces: the loops of a tile have to share the instruction
                 // cache of the SM with eleven other warps in other phases
@@ -246,30 +257,48 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                     }
                 }
                 __syncwarp();
-                // the box R ahead in this tile's sequence: the rest of phase 1, then (live tiles) the same boxes again
-                if (lane == 0) {
-                    const int nb = b + (int)R;
-                    if (nb < N) issue_box(stream, tis, nb, st);
-                    else if (live && !resident) issue_box(stream, tis, nb - N, st, true);
+                // a box of the first part is done with: its slot goes to the next request of the tile's sequence (the
+                // rest of phase 1, then the second requests).  A gated tile has no phase 3: every box is done with and
+                // only first requests go out.
+                const bool frees = !live || j < N - keep;
+                if (frees && li < (live ? LEN : N)) {
+                    if (lane == 0) issue_box(stream, tis, seq_box(li), st, li >= N);
+                    li++;
+                    pm ^= 1u << st;
                 }
-                if (++slot == R) { slot = 0; par ^= 1u; }
+                if (++slot == R) slot = 0;
             }
-            // resident tile: its boxes were not requested again, phase 3 looks at the barrier phases phase 1 saw
-            if (resident && live) par ^= 1u;
+            if (SPLIT && keep > 0 && keep < N) {
+                // f = A^(samples of the first part) f_second + f_first (the first part is the later one in time)
 #pragma unroll
-            for (int k = 0; k < K; k++) {
-                f[0][2 * k] = va[k][0] - T.sbias[2 * k]; f[0][2 * k + 1] = va[k][1] - T.sbias[2 * k + 1];
-                f[1][2 * k] = vb[k][0] - T.sbias[2 * k]; f[1][2 * k + 1] = vb[k][1] - T.sbias[2 * k + 1];
+                for (int row = 0; row < S; row++) {
+                    double ea = fa[0][row], eb = fa[1][row];
+#pragma unroll
+                    for (int col = col_lo<PAR>(row); col < col_hi(row); col++) {
+                        const double m = T.R[kRrPowRow + row][col];
+                        ea = fma(m, (col & 1 ? va[col / 2][1] : va[col / 2][0]) - T.sbias[col], ea);
+                        eb = fma(m, (col & 1 ? vb[col / 2][1] : vb[col / 2][0]) - T.sbias[col], eb);
+                    }
+                    f[0][row] = ea; f[1][row] = eb;
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < K; k++) {
+                    f[0][2 * k] = va[k][0] - T.sbias[2 * k]; f[0][2 * k + 1] = va[k][1] - T.sbias[2 * k + 1];
+                    f[1][2 * k] = vb[k][0] - T.sbias[2 * k]; f[1][2 * k + 1] = vb[k][1] - T.sbias[2 * k + 1];
+                }
             }
         }
 
         if (!live) {
-            // nothing of this tile's is in flight any more; the next tile's first boxes go out after its ticket
+            // nothing of this tile's is in flight any more and every slot is free; the next tile's first requests go out
+            // after its ticket
             if (lane == 0) next = take_ticket(ticket);
             const uint32_t ns_ = next / tps, nt_ = next - ns_ * tps;
             if (lane == 0 && next < P.total_tiles) {
-                for (uint32_t s = 0; s < R; s++) issue_box(ns_, nt_, (int)s, (slot + s) % R);
+                for (uint32_t s = 0; s < R; s++) issue_box(ns_, nt_, seq_box((int)s), (slot + s) % R);
             }
+            pm ^= (1u << R) - 1u;
             tile = __shfl_sync(0xffffffffu, next, 0);
             stream = __shfl_sync(0xffffffffu, ns_, 0);
             tis = __shfl_sync(0xffffffffu, nt_, 0);
@@ -463,10 +492,11 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             constexpr int CPB = 8 / PP;                       // chunks of four kept outputs per box
             static_assert(PP >= 1 && 8 % PP == 0, "a box holds whole chunks");
             const bool fast_f32 = P.out_mode == OUT_F32 && P.out_vec != 0;
+            int li = (int)R + N - keep;       // where phase 1 left the tile's request sequence
 #pragma unroll 1
             for (int b = 0; b < N; b++) {
                 const uint32_t st = slot;
-                mbar_wait(bar_u32 + 8 * st, par);
+                mbar_wait(bar_u32 + 8 * st, (pm >> st) & 1u);      // (a box that stayed: completed long ago)
                 const uint32_t box = ring_u32 + st * 4096;
                 if (mine) {
                     // chunks of four kept outputs, kRerunP3Unroll per iteration (one copy of the format switch in
@@ -549,18 +579,20 @@ iir_rerun_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                     }
                 }
                 __syncwarp();
-                // the box R ahead: the rest of this tile, then the first boxes of the next one
+                // the slot goes to the next request: the rest of this tile's second requests, then the first requests
+                // of the next tile
                 if (lane == 0) {
-                    const int nb = b + (int)R;
-                    if (nb < N) {
-                        issue_box(stream, tis, nb, st, true);
+                    if (li < LEN) {
+                        issue_box(stream, tis, seq_box(li), st, true);
                     } else {
                         nstream = next / tps;
                         ntis = next - nstream * tps;
-                        if (next < P.total_tiles) issue_box(nstream, ntis, nb - N, st);
+                        if (next < P.total_tiles) issue_box(nstream, ntis, seq_box(li - LEN), st);
                     }
                 }
-                if (++slot == R) { slot = 0; par ^= 1u; }
+                li++;
+                pm ^= 1u << st;
+                if (++slot == R) slot = 0;
             }
         }
         tile = __shfl_sync(0xffffffffu, next, 0);
