@@ -9,24 +9,30 @@
 // run again from its true entry state s0 - now in exactly the reference's sample order - producing the outputs
 // straight into 32-byte stores.  FP64 work per complex sample at D = 1: 4K + 8K + 2.
 //
-// The input is FETCHED twice as well: a tile goes through phase 1, the scan and its look-back, and is then
-// requested a second time for phase 3 - a few microseconds after the first request, so the second one is an L2
-// hit (ncu: DRAM read traffic = the input once).  Shared memory therefore holds only a small ring of 4 KiB TMA
-// boxes per warp, the run length is not tied to it (256 samples; 64 fitted when two whole tiles had to stay
-// resident), and the per-tile work - warp scan, look-back, entry states, tickets - which was a third of the time
-// at 64-sample runs is spread over four times as many samples; the look-back window shrinks with it (2 tiles
-// instead of 6 for the narrowest reference filter) and CF32 input is no longer held to 7 warps by its 8-byte samples.
+// The input is FETCHED twice as well - except for what is still in the ring: a tile goes through phase 1, the scan and
+// its look-back, and its boxes are then requested a second time for phase 3, a few microseconds after the first request
+// (about half of those are L2 hits).  Shared memory therefore holds only a small ring of 4 KiB TMA boxes per warp, the
+// run length is not tied to it (256 samples; 64 fitted when two whole tiles had to stay resident), and the per-tile
+// work - warp scan, look-back, entry states, tickets - which was a third of the time at 64-sample runs is spread over
+// four times as many samples; the look-back window shrinks with it (2 tiles instead of 6 for the narrowest reference
+// filter) and CF32 input is no longer held to 7 warps by its 8-byte samples.  Phase 1 takes the boxes in the order
+// keep .. N-1, 0 .. keep-1 so that the `keep` boxes the ring holds when it ends are the ones phase 3 starts with: those
+// are not requested again (rerun_keep(); a tile that fits the ring is not fetched twice at all).
 //
 // Phase 3 follows the look-back at once (the first version ran it one tile late, like the staged kernel, to keep
 // a warp from idling on a predecessor that is a little behind; the second fetch then came a whole tile later and
 // missed L2 every time - ncu: 8.6 GB read for 4.3 GB of input).  A tile is ~35k cycles long now and its predecessor
 // was claimed a ticket earlier: the aggregate it waits for is practically always there.
 //
-//   one tile of a warp:   phase 1 out of the ring (box b + R requested when box b is done; from box N - R on the
-//                         requests are the tile's own boxes again, for phase 3)
+// Integer inputs of filters whose zeros all sit at z = -1 take the AP form of phase 3 (template parameter AP, see the
+// phase-3 block): the numerator on the integer samples, an all-pole cascade on the FP64 pipe - 4K + 2 FMAs per
+// complex sample instead of 8K + 2.
+//
+//   one tile of a warp:   phase 1 out of the ring (a slot whose box is done with goes to the next request of the
+//                         tile's sequence: the rest of phase 1's order, then the second requests of boxes keep .. N-1)
 //                         phase 2, aggregate out, look-back, entry states
 //                         ticket for the next tile (its round trip hides behind phase 3)
-//                         phase 3 out of the ring (from box N - R on the requests are the next tile's first boxes)
+//                         phase 3 out of the ring (after the tile's last second request: the next tile's first boxes)
 #pragma once
 #include "iir_kernel.cuh"
 
