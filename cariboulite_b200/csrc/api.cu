@@ -298,6 +298,12 @@ int run_iir(caribou_cuda_ctx* c, int in_kind, const void* d_in, size_t n, size_t
         t.gain = T.gain;
         t.state = state + st_off;
         t.state_src = need_commit ? c->d_state_next + st_off : nullptr;
+        if (c->mirror_in_tail && c->h_ctrl_dev != nullptr && c->win0 == 0 && c->win_cnt == (uint32_t)c->cfg.n_streams) {
+            t.mirror_src = reinterpret_cast<const uint32_t*>(c->d_ctrl);
+            t.mirror_dst = reinterpret_cast<uint32_t*>(c->h_ctrl_dev);
+            t.mirror_words = (uint32_t)(c->ctrl_bytes / 4);
+            c->mirror_in_tail = false;          // done: the caller skips its copy
+        }
         t.gate = gate;
         t.gate_stride = gate_stride;
         launch_iir_tail(t, c->stream);
@@ -559,6 +565,11 @@ caribou_cuda_ctx* caribou_cuda_create(const caribou_cuda_config* cfg_in)
         !cuda_ok(cudaMalloc(&c->d_ctrl, c->ctrl_bytes), "cudaMalloc") ||
         !cuda_ok(cudaMallocHost(&c->h_ctrl, c->ctrl_bytes), "cudaMallocHost")) return fail();
     c->d_counters = reinterpret_cast<Counters*>(c->d_ctrl);
+    {
+        void* dp = nullptr;
+        if (cudaHostGetDevicePointer(&dp, c->h_ctrl, 0) == cudaSuccess) c->h_ctrl_dev = static_cast<uint8_t*>(dp);
+        else cudaGetLastError();                // no device view: the mirror stays a copy operation
+    }
     c->h_counters = reinterpret_cast<Counters*>(c->h_ctrl);
     c->d_first_bad = reinterpret_cast<int32_t*>(c->d_ctrl + sizeof(Counters));
     c->h_first_bad = reinterpret_cast<int32_t*>(c->h_ctrl + sizeof(Counters));
@@ -1074,13 +1085,17 @@ int caribou_cuda_rx_submit(caribou_cuda_ctx* c, const void* bytes, size_t nbytes
     const int mc = run_find_offsets(c, d_bytes, nbytes, stride_bytes, true, n);
     if (mc < 0) return mc;
     // optimistic fused launch: captures whose gate the search just raised are skipped on the device
+    c->mirror_in_tail = uo == nullptr;          // the submit's last launch also mirrors the control block
     if (run_iir(c, IN_WORDS, d_bytes, n, stride_bytes / 4, d_out, filt_stride, gates, 1, true, 0, nullptr) != CARIBOU_CUDA_OK)
         return CARIBOU_CUDA_ERR;
     if (uo) {
         const size_t ostride = ns > 1 ? ((n + 3) & ~size_t(3)) : 0;
         if (run_unpack(c, d_bytes, nbytes, stride_bytes, *uo, (uint32_t)mc, ostride) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     }
-    if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (c->mirror_in_tail || uo) {              // (no tail launch happened, or the unpack kernels counted after it)
+        c->mirror_in_tail = false;
+        if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    }
     if (mem != CARIBOU_CUDA_MEM_DEVICE)
         CBL_CHECK(cudaMemcpyAsync(filt_out, d_out, ((ns - 1) * filt_stride + nout) * c->out_elem, cudaMemcpyDeviceToHost, c->stream));
     c->queue.push_back(q);

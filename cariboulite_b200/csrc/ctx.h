@@ -118,6 +118,8 @@ struct caribou_cuda_ctx {
     cbl::DevBuf desc_inv, desc_syn;
     uint8_t* d_ctrl = nullptr;        // control block: counters, first bad chunks, per-stream flags (pointers below)
     uint8_t* h_ctrl = nullptr;        // its page-locked mirror
+    uint8_t* h_ctrl_dev = nullptr;    // the mirror as the device sees it (kernels may write it directly)
+    bool mirror_in_tail = false;      // request: the tail launch of the next run_iir copies d_ctrl into the mirror
     struct RrPow { uint64_t len = 0; double m[cbl::kMaxS * cbl::kMaxS]; } rr_pow[2];   // A^len of the main / short-run plan (rerun kernel, run_iir)
     const void* precleared_ptr = nullptr;   // descriptors (and the ticket) an earlier kernel of the submit has emptied for
     uint64_t precleared_doubles = 0;        // the next run_iir: it skips its memsets when they are exactly the ones it needs

@@ -72,6 +72,8 @@ __global__ void __launch_bounds__(kTailWarps * 32) iir_tail_kernel(const __grid_
     __shared__ uint32_t s_kept[kTailWarps];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t stream = blockIdx.x * kTailWarps + warp, rail = lane & 1u;          // rail 0 = I, 1 = Q
+    if (blockIdx.x == 0 && P.mirror_dst != nullptr)        // (the verdicts of the submit's alignment search are final by now)
+        for (uint32_t i = threadIdx.x; i < P.mirror_words; i += blockDim.x) P.mirror_dst[i] = P.mirror_src[i];
     if (stream >= P.n_streams) return;
     if (P.gate != nullptr && P.gate[(size_t)stream * P.gate_stride] != 0) return;
     const bool walker = lane < 2;
@@ -111,21 +113,29 @@ __global__ void __launch_bounds__(kTailWarps * 32) iir_tail_kernel(const __grid_
 #pragma unroll 4
             for (uint32_t i = 0; i < cnt; i++) {
                 const double x = xs[i];
+                const bool kept = ph == 0;
+                if (++ph == (uint32_t)P.D) ph = 0;
                 double in = x;
+                if (PAR) {
+                    // all sections see x; the output taps the state before the update and is only worked out where
+                    // it is kept (both walkers of a warp are at the same phase)
+                    if (kept) {
 #pragma unroll
-                for (int k = 0; k < K; k++) {
-                    if (PAR) {      // all sections see x; the output taps the state before the update
-                        in = fma(P.c2[k], v[k][1], fma(P.c1[k], v[k][0], in));
+                        for (int k = 0; k < K; k++) in = fma(P.c2[k], v[k][1], fma(P.c1[k], v[k][0], in));
+                    }
+#pragma unroll
+                    for (int k = 0; k < K; k++) {
                         const double w = fma(-P.a1[k], v[k][0], fma(-P.a2[k], v[k][1], x));
                         v[k][1] = v[k][0]; v[k][0] = w;
-                    } else {
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < K; k++) {
                         const double tt = fma(-P.a2[k], v[k][1], in), w = fma(-P.a1[k], v[k][0], tt);
                         in = fma(P.c2[k], v[k][1], fma(P.c1[k], v[k][0], w));
                         v[k][1] = v[k][0]; v[k][0] = w;
                     }
                 }
-                const bool kept = ph == 0;
-                if (++ph == (uint32_t)P.D) ph = 0;
                 if (kept) ys[nk++] = in * P.gain;
             }
             if (lane == 0) s_kept[warp] = nk;

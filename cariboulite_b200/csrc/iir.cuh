@@ -114,6 +114,9 @@ struct IirTailParams {
     double gain;
     double* state;                          // [n_streams][2S] kernel coordinates, updated in place ...
     const double* state_src;                // ... or, when set, read from here and written to `state` (the commit of a submit)
+    // optional: the context's control block (device) copied into its page-locked host mirror by this launch, the last
+    // one of a submit - instead of a D2H copy operation on the stream
+    const uint32_t* mirror_src; uint32_t* mirror_dst; uint32_t mirror_words;
     const int32_t* gate;                    // optional: stream s is skipped when gate[s * gate_stride] != 0
     uint32_t gate_stride;
 };

@@ -399,12 +399,15 @@ static int shard_begin(caribou_cuda_ctx* c, int in_kind, const void* in, size_t 
         const int mc = run_find_offsets(c, in, n * es, in_stride * es, false, n);
         if (mc < 0) return mc;
         gate = &c->d_counters->any_misaligned;
-        if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     } else {
         CBL_CHECK(cudaMemsetAsync(c->d_counters, 0, sizeof(Counters), c->stream));
+    }
+    c->mirror_in_tail = true;                   // pass 1's last launch mirrors the control block
+    if (run_iir(c, in_kind, in, n, in_stride, out, out_stride, gate, 0, true, 0, f_own) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
+    if (c->mirror_in_tail) {
+        c->mirror_in_tail = false;
         if (mirror_counters(c) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     }
-    if (run_iir(c, in_kind, in, n, in_stride, out, out_stride, gate, 0, true, 0, f_own) != CARIBOU_CUDA_OK) return CARIBOU_CUDA_ERR;
     if (prof) CBL_CHECK(cudaEventRecord(s->ev[1], c->stream));
     s->open = true;
     s->cur.in_kind = in_kind; s->cur.in = in; s->cur.n = n; s->cur.in_stride = in_stride; s->cur.out = out; s->cur.out_stride = out_stride;
