@@ -1,0 +1,111 @@
+"""Seeded random configurations of the fused rx path against the CPU oracle: filter order, decimation, channel,
+number of captures, capture lengths around run / tile / chunk boundaries, one to three submits queued before the wait
+(state and decimation phase carried), device or page-locked host memory, and now and then a misaligned or un-alignable
+chunk in one capture.  Every kernel on the path sees shapes the hand-written cases do not list: the control-block
+preparation, the alignment search over partial CTAs, the scan / rerun kernels with partial tiles and gated captures,
+the tail kernel as remainder walker and as commit, the slow path for the gated capture.  Runs through the C ABI."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5
+CHUNK = 16384            # bytes: 4096 samples per chunk
+
+
+def rel_rms(a, b):
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    d = np.sqrt(np.mean((a - b) ** 2, axis=0))
+    s = np.sqrt(np.mean(b ** 2, axis=0))
+    return d / np.maximum(s, 1e-30)
+
+
+def _oracle_calls(po, sos, D, channel, calls):
+    """One capture over several reads as the reference delivers it (test_gpu_batch.py: caribou_smi_read into a zeroed
+    buffer, the never-reset filter pair over what the read returned; on -3 the chunks before the un-alignable one)."""
+    ci, cq = po.Cascade(sos), po.Cascade(sos)
+    outs = []
+    for w in calls:
+        n = w.size
+        ret, cs16, _, _ = po.smi_read(w.view(np.uint8), n, channel, CHUNK)
+        deliver = n
+        if ret == -3:
+            spc = CHUNK // 4
+            nch = (n + spc - 1) // spc
+            bad = next(c for c in range(nch) if po.find_buffer_offset(w[c * spc:(c + 1) * spc].view(np.uint8)) < 0)
+            deliver = bad * spc
+        deliver -= deliver % D
+        outs.append((ret, deliver, po.filter_cf32_f32(sos, po.cs16_to_cf32(cs16[:deliver]), ci, cq)[::D]))
+    return outs
+
+
+CASES = list(range(72))
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_random_rx_configurations(cb, po, torch_cuda, case):
+    torch = torch_cuda
+    rng = np.random.default_rng(1000 + case)
+    order, fc = [(2, 100e3), (3, 50e3), (4, 250e3), (6, 10e3), (6, 50e3), (5, 100e3), (8, 400e3)][rng.integers(7)]
+    D = int([1, 1, 2, 8, 8, 4, 16][rng.integers(7)])
+    channel = int(rng.integers(2))
+    ns = int([1, 1, 2, 3, 5][rng.integers(5)])
+    n_calls = int(rng.integers(1, 4))
+    pinned = bool(rng.integers(2))
+    # lengths: multiples of 32 * D (whole words, decimation phase 0 at every submit), from shorter than a run to a
+    # few tiles, not multiples of the chunk in general
+    unit = 32 * D
+    n = unit * int(rng.integers(1, max(2, (3 * 32 * 256 + 5000) // unit)))
+    if rng.integers(4) == 0:
+        n = unit * int(rng.integers(1, 6))                     # tiny: no whole run at all
+    sos = po.butter_lowpass_sos(order, 4e6, fc)
+    ws = [[po.gen_words(n, n0=c * n, channel=channel, seed=case * 100 + s) for s in range(ns)] for c in range(n_calls)]
+    spc = CHUNK // 4
+    flaw = int(rng.integers(4))                                 # 0, 1: clean; 2: a misaligned chunk; 3: an un-alignable one
+    fs, fcall = int(rng.integers(ns)), int(rng.integers(n_calls))
+    nch = (n + spc - 1) // spc
+    fch = int(rng.integers(nch))
+    lo, hi = fch * spc, min((fch + 1) * spc, n)
+    if flaw == 2 and hi - lo > 64:
+        ws[fcall][fs][lo] ^= 0x80000000                          # the chunk starts with a bad header: offs = 4
+    elif flaw == 3 and hi - lo > 64:
+        ws[fcall][fs][lo:hi] = 0                                 # no valid header anywhere in the chunk
+    else:
+        flaw = 0
+    stride = (n * 4 + 15) & ~15
+    nout = n // D
+    bufs, outs = [], []
+    for c in range(n_calls):
+        raw = np.zeros((ns, stride // 4), np.uint32)
+        for s in range(ns):
+            raw[s, :n] = ws[c][s]
+        t = torch.from_numpy(raw.view(np.int32))
+        o = torch.full((ns, nout, 2), 7.0, dtype=torch.float32)
+        if pinned:
+            bufs.append(t.pin_memory()); outs.append(o.pin_memory())
+        else:
+            bufs.append(t.to("cuda:0")); outs.append(o.to("cuda:0"))
+    with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32, n_streams=ns, chunk_bytes=CHUNK, channel=channel) as ctx:
+        for c in range(n_calls):
+            ctx.rx_submit(bufs[c], n * 4, outs[c], stride_bytes=stride, filt_stride=nout,
+                          mem=cb.MEM_HOST_PINNED if pinned else cb.MEM_DEVICE)
+        ret, res = ctx.wait()
+        sr = ctx.stream_results()
+    got = [o.cpu().numpy() if not pinned else o.numpy() for o in outs]
+    what = dict(case=case, order=order, fc=fc, D=D, channel=channel, ns=ns, n=n, calls=n_calls, pinned=pinned, flaw=flaw,
+                at=(fs, fcall, fch))
+    for s in range(ns):
+        ref = _oracle_calls(po, sos, D, channel, [ws[c][s] for c in range(n_calls)])
+        for c in range(n_calls):
+            r_ret, deliver, y = ref[c]
+            m = deliver // D
+            if m:
+                assert np.all(rel_rms(got[c][s, :m], y) <= TOL), (what, s, c)
+            if r_ret != -3:
+                assert m == nout, (what, s, c)
+        # the per-capture verdict of the LAST submit is what stream_results reports
+        last_ret = ref[-1][0]
+        assert sr[s].n_samples == (cb.ERR_SYNC if last_ret == -3 else n), (what, s)
+    any_lost_last = any(_oracle_calls(po, sos, D, channel, [ws[c][s] for c in range(n_calls)])[-1][0] == -3 for s in range(ns))
+    assert ret == (cb.ERR_SYNC if any_lost_last else n), what
