@@ -109,3 +109,57 @@ def test_random_rx_configurations(cb, po, torch_cuda, case):
         assert sr[s].n_samples == (cb.ERR_SYNC if last_ret == -3 else n), (what, s)
     any_lost_last = any(_oracle_calls(po, sos, D, channel, [ws[c][s] for c in range(n_calls)])[-1][0] == -3 for s in range(ns))
     assert ret == (cb.ERR_SYNC if any_lost_last else n), what
+
+
+@pytest.mark.parametrize("case", list(range(40)))
+def test_random_filter_configurations(cb, po, torch_cuda, case):
+    """caribou_cuda_filter_submit on CS16 / CF32 device input: both parity modes, every output format of the reference's
+    ordering, random decimation and length, the stream cut into one to three calls (carried state), end state against
+    the oracle's cascades."""
+    torch = torch_cuda
+    rng = np.random.default_rng(5000 + case)
+    order, fc = [(1, 100e3), (2, 100e3), (3, 50e3), (4, 250e3), (6, 10e3), (6, 25e3), (7, 200e3), (8, 400e3)][rng.integers(8)]
+    D = int([1, 1, 2, 4, 8, 32][rng.integers(6)])
+    q16 = bool(rng.integers(2))
+    kind = "cs16" if q16 else ["cs16", "cf32"][rng.integers(2)]
+    fmt = ["CS16", "CF32", "CF64", "CS8"][rng.integers(4)] if q16 else ["CF32", "CF64"][rng.integers(2)]
+    n_calls = int(rng.integers(1, 4))
+    unit = 32 * D
+    per = unit * int(rng.integers(1, max(2, 40000 // unit)))
+    n = per * n_calls
+    sos = po.butter_lowpass_sos(order, 4e6, fc)
+    _, cs16, _, _ = po.smi_read(po.gen_words(n, seed=case).view(np.uint8), n)
+    cs16 = cs16[:n]
+    ci, cq = po.Cascade(sos), po.Cascade(sos)
+    code = {"CS16": cb.FMT_CS16, "CF32": cb.FMT_CF32, "CF64": cb.FMT_CF64, "CS8": cb.FMT_CS8}[fmt]
+    if q16:
+        q = po.filter_cs16_q16(sos, cs16, ci, cq)[::D]
+        ref = {"CS16": q, "CF32": po.cs16_to_cf32(q), "CF64": po.cs16_to_cf64(q), "CS8": po.cs16_to_cs8(q)}[fmt]
+    else:
+        y = po.filter_cf32_f32(sos, po.cs16_to_cf32(cs16), ci, cq)[::D]
+        ref = y if fmt == "CF32" else None
+    x_dev = _dev_t(torch, cs16 if kind == "cs16" else po.cs16_to_cf32(cs16))
+    out = torch.zeros((n // D, 2), dtype=getattr(torch, np.dtype(cb.FMT_DTYPE[code]).name), device="cuda:0")
+    with cb.Context(sos=sos, decimation=D, parity=cb.PARITY_Q16 if q16 else cb.PARITY_F32, out_format=code) as ctx:
+        for c in range(n_calls):
+            ctx.filter_submit(cb.IN_CS16 if kind == "cs16" else cb.IN_CF32, x_dev[c * per:(c + 1) * per], per,
+                              out[c * per // D:(c + 1) * per // D])
+        assert ctx.wait()[0] == per
+        state = ctx.get_state()
+    got = out.cpu().numpy()
+    what = dict(case=case, order=order, fc=fc, D=D, q16=q16, kind=kind, fmt=fmt, calls=n_calls, per=per)
+    if q16:
+        diff = np.abs(got.astype(np.float64) - ref.astype(np.float64))
+        lsb = {"CS16": 1, "CF32": 1 / 4096, "CF64": 1 / 4096, "CS8": 1}[fmt]
+        assert diff.max() <= lsb * 1.0001 and np.mean(diff > 0) < 1e-3, what      # an LSB may flip at a truncation boundary
+    elif ref is not None:
+        assert np.all(rel_rms(got, ref) <= TOL), what
+    else:       # CF64 of the F32 ordering: the unrounded doubles; their float image is the CF32 output
+        assert np.all(rel_rms(got, y) <= TOL), what
+    # end state in the reference's (v1, v2) coordinates; Q16 feeds int16-scale samples, F32 samples / 4096
+    st = np.concatenate([ci.state, cq.state])
+    np.testing.assert_allclose(state, st, rtol=1e-7, atol=1e-9 * max(1.0, np.abs(st).max()), err_msg=str(what))
+
+
+def _dev_t(torch, a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to("cuda:0")
