@@ -163,3 +163,30 @@ def test_random_filter_configurations(cb, po, torch_cuda, case):
 
 def _dev_t(torch, a):
     return torch.from_numpy(np.ascontiguousarray(a)).to("cuda:0")
+
+
+@pytest.mark.parametrize("case", list(range(40)))
+def test_random_unpack_configurations(cb, po, torch_cuda, case):
+    """Kernel (a) on single-channel captures with random damage: dropped and inserted bytes (every chunk after one is
+    misaligned by a different amount), corrupted headers, garbage stretches (lost sync), sync bits, ragged byte counts,
+    chunk sizes from 64 bytes to 64 KiB - CS16, meta, CF32 (untouched slots included), flag counts and index lists and
+    the return code, bit for bit against the oracle (tests/test_gpu_unpack.py::_check_single)."""
+    from tests.test_gpu_unpack import _check_single
+    rng = np.random.default_rng(9000 + case)
+    channel = int(rng.integers(2))
+    chunk = int([64, 256, 4096, 16384, 65536][rng.integers(5)])
+    n = int(rng.integers(1, 60000 if chunk >= 4096 else 6000))
+    w = po.gen_words(n, channel=channel, seed=case)
+    w[rng.integers(0, n, size=max(1, n // 500))] |= 1                          # sync bits
+    for _ in range(int(rng.integers(0, 4))):                                    # corrupted headers
+        w[int(rng.integers(n))] ^= [0x80000000, 0x40000000, 0x00008000, 0x00004000, 0x00010000][rng.integers(5)]
+    if rng.integers(5) == 0 and n > 3000:                                       # a garbage stretch
+        a = int(rng.integers(n - 2000))
+        w[a:a + int(rng.integers(500, 2000))] = rng.integers(0, 2**32, dtype=np.uint64, size=1).astype(np.uint32)[0]
+    raw = w.view(np.uint8).copy()
+    for _ in range(int(rng.integers(0, 3))):                                    # dropped / inserted bytes
+        p = int(rng.integers(raw.size))
+        k = int(rng.integers(1, 8))
+        raw = np.concatenate([raw[:p], raw[p + k:]]) if rng.integers(2) else np.concatenate([raw[:p], np.zeros(k, np.uint8), raw[p:]])
+    raw = raw[: raw.size - int(rng.integers(0, 4))]                            # ragged end
+    _check_single(cb, po, torch_cuda, np.ascontiguousarray(raw), channel, chunk)
