@@ -99,16 +99,32 @@ bool stage_reserve(caribou_cuda_smi* d, size_t n)
     return true;
 }
 
+// Does candidate offset 0 of a chunk carry four valid headers (caribou_smi.c:248-262, the aligned case)?  A look at 16
+// bytes of what read(2) just delivered: it decides where a segment ends, nothing else - the alignment search itself
+// runs on the device.
+bool chunk_starts_aligned(const uint8_t* p, size_t len)
+{
+    if (len <= 16) return true;                                // caribou_smi.c:240-243
+    for (int k = 0; k < 4; k++) {
+        uint32_t w;
+        memcpy(&w, p + 4 * k, 4);
+        if (!hdr_ok(w)) return false;
+    }
+    return true;
+}
+
 // The reference's read loop (caribou_smi.c:632-682).  read(2) results are gathered into segments
 // (a run of full chunks closed by at most one short chunk) and each segment is handed to `flush`
 // (segment bytes, byte count, index of its first output sample), which returns 0 or an error code.
 // *got receives the samples handed to flush so far, also when the loop ends in an error: like the reference,
 // which has decoded every chunk it read before the failing read(2) (caribou_smi.c:653-664).
-// Where this differs: the reference stops reading at the first chunk without alignment; here the rest of the
-// request has been read from the descriptor by the time the device reports it (a read-ahead bounded by the
-// request), because the verdict is not waited for chunk by chunk.
+// The reference stops reading at the first chunk without alignment (caribou_smi.c:665-668), so the descriptor must
+// not be read past such a chunk: a chunk that does not start aligned closes its segment as well, and the device's
+// verdict on it is waited for before the next read(2) - `flush` returns it (CARIBOU_CUDA_ERR_SYNC) or, where the
+// flush only queues work, `lost_now` synchronises and tells.  Aligned captures never take that turn.
 int read_loop(caribou_cuda_smi* d, size_t length_samples,
-              const std::function<int(const uint8_t*, size_t, size_t)>& flush, size_t* got)
+              const std::function<int(const uint8_t*, size_t, size_t)>& flush, size_t* got,
+              const std::function<bool()>& lost_now = std::function<bool()>())
 {
     size_t left = length_samples * CARIBOU_CUDA_BYTES_PER_SAMPLE;
     size_t read_so_far = 0, seg_bytes = 0, seg_first = 0;
@@ -126,14 +142,16 @@ int read_loop(caribou_cuda_smi* d, size_t length_samples,
             return CARIBOU_CUDA_ERR;
         }
         if (ret == 0) break;                                   // timeout: deliver what we have
+        const bool aligned0 = chunk_starts_aligned(d->h_stage + seg_bytes, (size_t)ret);
         seg_bytes += (size_t)ret;
         read_so_far += (size_t)ret / CARIBOU_CUDA_BYTES_PER_SAMPLE;
         left -= (size_t)ret;
-        if ((size_t)ret != nbl) {                              // short chunk closes the segment
+        if ((size_t)ret != nbl || !aligned0) {                 // a short chunk closes the segment; so does a suspect one
             const int rc = flush(d->h_stage, seg_bytes, seg_first);
             if (rc < 0) return rc;
             if (got) *got = read_so_far;
             seg_bytes = 0; seg_first = read_so_far;
+            if (!aligned0 && lost_now && lost_now()) break;    // no alignment in that chunk: nothing is read after it
         }
     }
     if (seg_bytes) {
@@ -173,7 +191,12 @@ int read_to_device(caribou_cuda_smi* d, caribou_cuda_ctx* c, uint32_t* d_cs16, u
     auto flush = [&](const uint8_t* h, size_t nbytes, size_t first) -> int {
         return unpack_segment_to_device(d, c, h, nbytes, d_cs16, d_meta, first);
     };
-    return read_loop(d, n, flush, got);
+    auto lost_now = [&]() -> bool {                            // (only after a chunk that did not start aligned)
+        if (mirror_counters(c) != CARIBOU_CUDA_OK || !cuda_ok(cudaStreamSynchronize(c->stream), "cudaStreamSynchronize")) return true;
+        d->stage_busy = false;
+        return lost_seen(c);
+    };
+    return read_loop(d, n, flush, got, lost_now);
 }
 
 }  // namespace

@@ -190,3 +190,97 @@ def test_random_unpack_configurations(cb, po, torch_cuda, case):
         raw = np.concatenate([raw[:p], raw[p + k:]]) if rng.integers(2) else np.concatenate([raw[:p], np.zeros(k, np.uint8), raw[p:]])
     raw = raw[: raw.size - int(rng.integers(0, 4))]                            # ragged end
     _check_single(cb, po, torch_cuda, np.ascontiguousarray(raw), channel, chunk)
+
+
+@pytest.mark.parametrize("case", list(range(24)))
+def test_random_smi_read_sequences(cb, po, torch_cuda, case):
+    """The caribou_smi_read-shaped shim (caribou_smi.h:96-97) over a damaged capture in a memfd: a random sequence of
+    read sizes (one sample to several native batches), random native batch length, both channels; return codes, CS16,
+    meta and the caller's untouched bytes against the oracle's read loop, call by call, until the data runs out."""
+    from tests.test_gpu_compat import Smi
+    rng = np.random.default_rng(13000 + case)
+    channel = int(rng.integers(2))
+    nbl = int([4096, 16384, 65536, 524288][rng.integers(4)])
+    n = int(rng.integers(2000, 300000))
+    w = po.gen_words(n, channel=channel, seed=case)
+    w[rng.integers(0, n, size=max(1, n // 700))] |= 1
+    raw = w.view(np.uint8).copy()
+    for _ in range(int(rng.integers(0, 3))):
+        p = int(rng.integers(raw.size))
+        k = int(rng.integers(1, 6))
+        raw = np.concatenate([raw[:p], raw[p + k:]])
+    if rng.integers(6) == 0:
+        a = int(rng.integers(max(1, raw.size - 70000)))
+        raw[a:a + int(rng.integers(20000, 70000))] = 0                    # a stretch with no header: -3 somewhere
+    raw = np.ascontiguousarray(raw)
+    s = Smi(cb, raw, nbl=nbl)
+    cursor = 0
+    try:
+        for step in range(12):
+            req = int([1, 7, 100, nbl // 4, nbl // 4 + 1, 3 * (nbl // 4), 5000, 131072][rng.integers(8)])
+            got_r, got_cs16, got_meta = s.read(req, channel)
+            ref_cs16 = np.full((req + 1, 2), 0x1234, dtype=np.int16)
+            ref_meta = np.full(req + 1, 0x5A, dtype=np.uint8)
+            ref_r, _, _, cursor = po.smi_read(raw, req, channel, nbl, cursor, cs16=ref_cs16, meta=ref_meta)
+            what = dict(case=case, step=step, req=req, nbl=nbl, channel=channel, n=n)
+            assert got_r == ref_r, (what, got_r, ref_r)
+            np.testing.assert_array_equal(got_cs16, ref_cs16, err_msg=str(what))
+            np.testing.assert_array_equal(got_meta, ref_meta, err_msg=str(what))
+            if ref_r <= 0 and ref_r != -3:
+                break
+    finally:
+        s.close()
+
+
+@pytest.mark.parametrize("case", list(range(24)))
+def test_random_stream_read_sequences(cb, po, torch_cuda, case):
+    """Stream::ReadSamplesGen through the shim (CaribouliteStream.cpp:370-382) over a damaged capture: random format,
+    filter, native batch length and read sizes (above and below the MTU), dropped bytes and now and then a stretch
+    with no header at all (a read that hits it delivers nothing and leaves the filters alone).  Call by call against
+    the oracle's Stream: same element counts, unfiltered formats bit for bit, filtered ones within an LSB on a few
+    samples, nothing written beyond what was delivered."""
+    from tests.test_gpu_compat import Smi, FMT
+    L = cb.lib()
+    rng = np.random.default_rng(17000 + case)
+    fmt = ["CS16", "CF32", "CF64", "CS8"][rng.integers(4)]
+    filt = int(rng.integers(4))
+    nbl = int([65536, 524288][rng.integers(2)])
+    n = int(rng.integers(150000, 600000))
+    w = po.gen_words(n, seed=case)
+    raw = w.view(np.uint8).copy()
+    for _ in range(int(rng.integers(0, 2))):
+        p = int(rng.integers(raw.size))
+        raw = np.concatenate([raw[:p], raw[p + int(rng.integers(1, 6)):]])
+    if rng.integers(4) == 0:
+        a = int(rng.integers(max(1, raw.size - 300000)))
+        raw[a:a + int(rng.integers(nbl, 3 * nbl))] = 0
+    raw = np.ascontiguousarray(raw)
+    so = po.StreamOracle(raw, native_batch_len=nbl)
+    so.set_format(fmt)
+    so.set_filter(filt)
+    s = Smi(cb, raw, nbl=nbl)
+    st = L.caribou_cuda_rxstream_create(s.h, 0)
+    assert st, cb.last_error()
+    try:
+        assert L.caribou_cuda_rxstream_set_format(st, fmt.encode()) == 0
+        L.caribou_cuda_rxstream_set_filter(st, filt)
+        dt, _ = FMT[fmt]
+        mtu = nbl // 4
+        for step in range(8):
+            req = int([1, 1000, mtu - 1, mtu, mtu + 1, 2 * mtu + 17, 50000][rng.integers(7)])
+            buf = np.zeros((req + 1, 2), dtype=dt)
+            r = L.caribou_cuda_rxstream_read(st, buf.ctypes.data, req, 100000)
+            ref_r, ref = so.read(req)
+            what = dict(case=case, step=step, fmt=fmt, filt=filt, nbl=nbl, req=req)
+            assert r == ref_r, (what, r, ref_r)
+            got = buf[:r]
+            assert np.all(buf[r:] == 0), what
+            if filt == 0:
+                np.testing.assert_array_equal(got, ref, err_msg=str(what))
+            elif r:
+                lsb = {"CS16": 1, "CS8": 1, "CF32": 1 / 4096, "CF64": 1 / 4096}[fmt]
+                dd = np.abs(got.astype(np.float64) - ref.astype(np.float64))
+                assert dd.max() <= lsb * 1.0001 and np.mean(dd > 0) < 1e-3, what
+    finally:
+        L.caribou_cuda_rxstream_destroy(st)
+        s.close()
