@@ -284,3 +284,83 @@ def test_random_stream_read_sequences(cb, po, torch_cuda, case):
     finally:
         L.caribou_cuda_rxstream_destroy(st)
         s.close()
+
+
+@pytest.mark.parametrize("case", list(range(16)))
+def test_random_radio_read_sequences(cb, po, torch_cuda, case):
+    """CaribouLiteRadio::ReadSamples(std::complex<float>*, n, meta) through the shim (LC/CaribouLiteRadioCpp.cpp:72-130)
+    over a damaged capture, random read sizes up to the radio's persistent buffer: CF32, metadata, return codes, and the
+    slots a misaligned chunk leaves unwritten (they carry the previous read's value)."""
+    from tests.test_gpu_compat import Smi
+    L = cb.lib()
+    rng = np.random.default_rng(21000 + case)
+    channel = int(rng.integers(2))
+    nbl = int([16384, 65536, 524288][rng.integers(3)])
+    n = int(rng.integers(50000, 500000))
+    raw = po.gen_words(n, channel=channel, seed=case).view(np.uint8).copy()
+    for _ in range(int(rng.integers(0, 3))):
+        p = int(rng.integers(raw.size))
+        raw = np.concatenate([raw[:p], raw[p + int(rng.integers(1, 6)):]])
+    if rng.integers(4) == 0:
+        a = int(rng.integers(max(1, raw.size - 3 * nbl)))
+        raw[a:a + int(rng.integers(nbl, 2 * nbl))] = 0
+    raw = np.ascontiguousarray(raw)
+    s = Smi(cb, raw, nbl=nbl)
+    cap = 131072 * 2
+    p_cs16 = np.zeros((cap + 1, 2), dtype=np.int16)      # the radio's _read_samples / _read_metadata
+    p_meta = np.zeros(cap + 1, dtype=np.uint8)
+    cursor = 0
+    try:
+        first = True
+        for step in range(8):
+            req = cap if first else int([1, 777, nbl // 4, nbl // 4 + 3, 70000, cap][rng.integers(6)])
+            first = False
+            cf = np.full((req, 2), 5.0, dtype=np.float32)
+            meta = np.full(req, 0x77, dtype=np.uint8)
+            r = L.caribou_cuda_radio_read_cf32(s.h, channel, cf.ctypes.data, meta.ctypes.data, req)
+            ref_r, _, _, cursor = po.smi_read(raw, req, channel, nbl, cursor, cs16=p_cs16, meta=p_meta)
+            what = dict(case=case, step=step, req=req, nbl=nbl, channel=channel)
+            assert r == ref_r, (what, r, ref_r)
+            if r > 0:
+                np.testing.assert_array_equal(cf[:r], po.cs16_to_cf32(p_cs16[:r]), err_msg=str(what))
+                np.testing.assert_array_equal(meta[:r], p_meta[:r], err_msg=str(what))
+            assert np.all(cf[max(r, 0):] == 5.0) and np.all(meta[max(r, 0):] == 0x77), what
+            if ref_r == 0:
+                break
+    finally:
+        s.close()
+
+
+@pytest.mark.parametrize("case", list(range(24)))
+def test_random_dual_channel_unpack(cb, po, torch_cuda, case):
+    """Dual-channel captures with random interleave block, chunk size, length, corrupted headers and sync
+    bits: each sub-stream against the oracle's demux + read, the flag counts and lists against the oracle's scan."""
+    from tests.test_gpu_unpack import _unpack_dev, _oracle
+    rng = np.random.default_rng(25000 + case)
+    B = int([1, 8, 64, 4096][rng.integers(4)])
+    chunk = int([4096, 32768, 65536][rng.integers(3)])
+    n = int(rng.integers(2 * B, 120000))
+    a = po.gen_words(n, channel=0, seed=case)
+    b = po.gen_words(n, channel=1, seed=case + 500)
+    w = np.empty(n, np.uint32)
+    blk = np.arange(n) // B % 2
+    w[blk == 0] = a[: int(np.sum(blk == 0))]
+    w[blk == 1] = b[: int(np.sum(blk == 1))]
+    w[rng.integers(0, n, size=max(1, n // 900))] |= 1
+    for _ in range(int(rng.integers(0, 4))):
+        w[int(rng.integers(n))] ^= [0x80000000, 0x40000000, 0x00008000, 0x00004000][rng.integers(4)]
+    g = _unpack_dev(cb, torch_cuda, w.view(np.uint8), 0, chunk, B=B)
+    what = dict(case=case, B=B, chunk=chunk, n=n)
+    for sub, suf in ((0, ""), (1, "_b")):
+        sw = po.demux_gather(w, B, sub)
+        ret, cs16, meta = _oracle(po, sw.view(np.uint8), sub, chunk)
+        assert (g["ret"] if sub == 0 else g["res"].n_samples_b) == ret, (what, sub)
+        m = max(ret, 0)
+        k = cs16.shape[0]
+        np.testing.assert_array_equal(g["cs16" + suf][:k], cs16, err_msg=str((what, sub)))      # untouched slots included
+        np.testing.assert_array_equal(g["meta" + suf][:k], meta, err_msg=str((what, sub)))
+        np.testing.assert_array_equal(g["cf32" + suf][:m], po.cs16_to_cf32(cs16[:m]))
+    ni, inv, ns_, syn = po.flag_scan(w, cap=4096)
+    assert g["res"].n_invalid == ni and g["res"].n_sync == ns_, what
+    np.testing.assert_array_equal(g["inv"][: len(inv)], inv)
+    np.testing.assert_array_equal(g["syn"][: len(syn)], syn)
