@@ -364,3 +364,52 @@ def test_random_dual_channel_unpack(cb, po, torch_cuda, case):
     assert g["res"].n_invalid == ni and g["res"].n_sync == ns_, what
     np.testing.assert_array_equal(g["inv"][: len(inv)], inv)
     np.testing.assert_array_equal(g["syn"][: len(syn)], syn)
+
+
+@pytest.mark.parametrize("case", list(range(16)))
+def test_random_sharded_streams(cb, po, torch_cuda, case):
+    """One stream time-chunked over `world` contexts of one GPU (tests/test_gpu_shard.py: pass 1 from zero state, the
+    end vectors exchanged, composition and fix-up on the device): random world, filter, decimation, shard length (from
+    shorter than the fix-up window to several tiles) and number of calls, against the sequential oracle over the whole
+    stream and with a look at every shard boundary; every rank ends with the same state."""
+    torch = torch_cuda
+    rng = np.random.default_rng(29000 + case)
+    order, fc = [(2, 100e3), (4, 250e3), (6, 10e3), (6, 50e3), (8, 400e3), (3, 50e3)][rng.integers(6)]
+    D = int([1, 2, 8, 8, 4][rng.integers(5)])
+    world = int(rng.integers(2, 6))
+    calls = int(rng.integers(1, 4))
+    unit = 32 * D
+    n = unit * int(rng.integers(1, 60000 // unit))
+    total = n * world * calls
+    sos = po.butter_lowpass_sos(order, 4e6, fc)
+    w = po.gen_words(total, seed=case)
+    ref = po.rx_path_f32(w, sos, D)
+    d_w = torch.from_numpy(w.view(np.int32)).to("cuda:0")
+    out = torch.zeros((total // D, 2), dtype=torch.float32, device="cuda:0")
+    ctxs = [cb.Context(sos=sos, decimation=D, parity=cb.PARITY_F32) for _ in range(world)]
+    what = dict(case=case, order=order, fc=fc, D=D, world=world, calls=calls, n=n)
+    try:
+        for g, c in enumerate(ctxs):
+            c.shard_init(g, world)
+        for call in range(calls):
+            for g, c in enumerate(ctxs):
+                lo = (call * world + g) * n
+                c.shard_begin(cb.IN_WORDS, d_w[lo:lo + n], n, out[lo // D:(lo + n) // D])
+            cb.shard_exchange_local(ctxs)
+            for c in ctxs:
+                c.shard_finish()
+        for c in ctxs:
+            assert c.wait()[0] == n, what
+        states = [c.get_state() for c in ctxs]
+    finally:
+        for c in ctxs:
+            c.close()
+    got = out.cpu().numpy()
+    assert np.all(rel_rms(got, ref) <= TOL), what
+    for b in range(1, world * calls):
+        c0 = b * n // D
+        seg = slice(max(c0 - 16, 0), min(c0 + 4096 // D + 16, total // D))
+        if np.sqrt(np.mean(ref[seg].astype(np.float64) ** 2)) > 1e-3:
+            assert np.all(rel_rms(got[seg], ref[seg]) <= TOL), (what, b)
+    for st in states[1:]:
+        np.testing.assert_array_equal(st, states[0])

@@ -145,3 +145,51 @@ def test_noalloc_entry_point_takes_no_device_memory_and_rejects_oversize(cb, po,
     assert r.n_samples == ret and (r.n_invalid, r.n_sync) == (res.n_invalid, res.n_sync)
     for name in ("cs16", "meta", "cf32"):
         assert torch.equal(o_big[name], want[name]), name
+
+
+@pytest.mark.parametrize("case", list(range(16)))
+def test_random_noalloc_unpack(cb, po, torch_cuda, case):
+    """caribou_cuda_unpack_noalloc against caribou_cuda_unpack_submit on the same damaged capture (random channel, chunk
+    size, length up to a few MiB, dropped bytes, corrupted headers), back to back on the shared scratch array."""
+    import ctypes as C
+    torch = torch_cuda
+    rng = np.random.default_rng(33000 + case)
+    dev = torch.device("cuda:0")
+    for rep in range(3):
+        channel = int(rng.integers(2))
+        chunk = int([256, 4096, 65536, 0][rng.integers(4)])
+        n = int(rng.integers(1, 400000 if chunk != 256 else 300000))
+        w = po.gen_words(n, channel=channel, seed=case * 7 + rep)
+        w[rng.integers(0, n, size=max(1, n // 800))] |= 1
+        for _ in range(int(rng.integers(0, 3))):
+            w[int(rng.integers(n))] ^= 0x80000000
+        raw = w.view(np.uint8).copy()
+        if rng.integers(2):
+            p = int(rng.integers(raw.size))
+            raw = np.concatenate([raw[:p], raw[p + int(rng.integers(1, 4)):]])
+        if (raw.size + max(chunk, 1) - 1) // max(chunk or 524288, 1) > cb.NOALLOC_MAX_CHUNKS:
+            continue
+        m = raw.size // 4 + 2
+        d_raw = torch.from_numpy(np.concatenate([raw, np.zeros((-raw.size) % 16 + 16, np.uint8)])).to(dev)
+
+        def bufs():
+            return dict(cs16=torch.full((m, 2), 0x5A5A, dtype=torch.int16, device=dev),
+                        meta=torch.full((m,), 0x5A, dtype=torch.uint8, device=dev),
+                        cf32=torch.full((m, 2), -7.0, dtype=torch.float32, device=dev),
+                        invalid_idx=torch.full((1024,), -1, dtype=torch.int32, device=dev),
+                        sync_idx=torch.full((1024,), -1, dtype=torch.int32, device=dev))
+        want = bufs()
+        with cb.Context(channel=channel, chunk_bytes=chunk) as ctx:
+            ctx.unpack_submit(d_raw, nbytes=raw.size, **want)
+            ret, res = ctx.wait()
+        got = bufs()
+        d_res = torch.zeros(C.sizeof(cb.Result), dtype=torch.uint8, device=dev)
+        cb.unpack_noalloc(d_raw, raw.size, result=d_res, channel=channel, chunk_bytes=chunk, **got)
+        torch.cuda.synchronize()
+        r = cb.Result()
+        C.memmove(C.byref(r), d_res.cpu().numpy().tobytes(), C.sizeof(r))
+        what = dict(case=case, rep=rep, channel=channel, chunk=chunk, n=n)
+        assert (r.n_samples, r.n_invalid, r.n_sync, r.first_bad_chunk, r.n_misaligned_chunks) == \
+               (ret, res.n_invalid, res.n_sync, res.first_bad_chunk, res.n_misaligned_chunks), what
+        for name in want:
+            assert torch.equal(got[name], want[name]), (what, name)
