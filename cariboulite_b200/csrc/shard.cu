@@ -112,7 +112,6 @@ struct Shard {
     double** d_peers = nullptr;     // [world] every rank's d_px in this process's address space
     std::vector<void*> peer_maps;   // what cudaIpcOpenMemHandle returned (to close)
     int* err_host = nullptr;        // device view of the control block's "a peer never arrived" slot in page-locked host memory
-    bool precleared = false;        // this call's composition kernel has emptied the fix-up launch's descriptors and ticket
     unsigned long long seq = 0;     // sharded calls so far
     bool committed = false;         // the composition kernel of this call has written the carry into the context's state
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};   // profiling: start, after pass 1, end
@@ -454,7 +453,6 @@ static int shard_fixup(caribou_cuda_ctx* c, const ShardCall& k, bool late)
         if (run_iir(c, k.in_kind, k.in, k.n, k.in_stride, k.out, k.out_stride, gate, 0, false, fp.max_tiles, s->d_sin) != CARIBOU_CUDA_OK)
             return CARIBOU_CUDA_ERR;
     }
-    s->precleared = false;
     // the stream's state after this call: every rank holds the same carry
     if (!s->committed) {
         launch_commit_state(c->d_state, s->d_carry, (size_t)c->cfg.n_streams, (size_t)2 * P.S, gate, 0, c->stream);
@@ -495,7 +493,6 @@ static int shard_compose(caribou_cuda_ctx* c, const ShardCall& k, bool peer = fa
     }
     // a fix-up of a few leading tiles: its descriptors and ticket are emptied here (pass 1 used more tiles of the same
     // plan, so the buffers exist and are large enough)
-    s->precleared = false;
     const FixPlan fp = shard_fix_plan(c, k);
     if (fp.partial) {
         const FilterPlan& P = pick_plan(c, k.n);
@@ -505,7 +502,6 @@ static int shard_compose(caribou_cuda_ctx* c, const ShardCall& k, bool peer = fa
             p.clear_desc = desc.as<unsigned long long>();
             p.clear_n = (uint32_t)doubles;
             p.clear_ticket = c->d_ticket;
-            s->precleared = true;
             c->precleared_ptr = desc.p; c->precleared_doubles = doubles;
         }
     }
