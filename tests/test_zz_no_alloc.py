@@ -153,7 +153,7 @@ def test_random_noalloc_unpack(cb, po, torch_cuda, case):
     size, length up to a few MiB, dropped bytes, corrupted headers), back to back on the shared scratch array."""
     import ctypes as C
     torch = torch_cuda
-    rng = np.random.default_rng(33000 + case)
+    rng = np.random.default_rng(33000 + case + 100000 * int(__import__("os").environ.get("CARIBOU_FUZZ_SEED", "0")))
     dev = torch.device("cuda:0")
     for rep in range(3):
         channel = int(rng.integers(2))
