@@ -780,12 +780,12 @@ def config_legs(a, cb, torch, dev, stream, peak, with_cpu):
         ctx.close()
         del o16
     # words in, CF32 out at full rate (12 B/sample): the fused form of the same filters
-    for fc, name in ((10e3, "fused_d1_order6_fc10k"), (50e3, "fused_d1_order6_fc50k")):
-        ctx = cb.Context(device=dev.index, sos=cb.butter_lowpass(6, 4e6, fc), decimation=1, parity=cb.PARITY_F32,
+    for order, fc, name in ((6, 10e3, "fused_d1_order6_fc10k"), (6, 50e3, "fused_d1_order6_fc50k"), (4, 250e3, "fused_d1_order4_fc250k")):
+        ctx = cb.Context(device=dev.index, sos=cb.butter_lowpass(order, 4e6, fc), decimation=1, parity=cb.PARITY_F32,
                          cuda_stream=stream.cuda_stream)
         of = torch.zeros((n, 2), dtype=torch.float32, device=dev)
         mean_ms, best_ms = time_launches(torch, stream, lambda: ctx.filter_submit(cb.IN_WORDS, d_w, n, of), lambda: ctx.wait(), reps=6, warm=2)
-        rec(name, "2^28 words -> order-6 fc = %g kHz at full rate -> CF32" % (fc / 1e3), n, 12.0, mean_ms, best_ms)
+        rec(name, "2^28 words -> order-%d fc = %g kHz at full rate -> CF32" % (order, fc / 1e3), n, 12.0, mean_ms, best_ms)
         ctx.close()
         del of
     del d_w, cs
